@@ -1,0 +1,157 @@
+/* libssl4gie_b200 — C ABI of the B200-native (sm_100a) ViT-B/16 + DPT training hot path.
+ *
+ * The reference (ESandML/SSL4GIE) has no FFI/plugin interface: the path sits behind ordinary PyTorch
+ * nn.Modules.  This header is therefore the boundary we define UNDER those modules; each entry
+ * point names the reference code it replaces (paths relative to the reference repository root).
+ * The Python side (ssl4gie_b200/_C.py, ctypes) passes tensor.data_ptr() and
+ * torch.cuda.current_stream().cuda_stream; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless stated otherwise
+ *   - every call enqueues on `stream` (a cudaStream_t passed as void*), never synchronises, never allocates
+ *     device memory, never frees caller memory; the caller owns every buffer
+ *   - return 0 on success, negative S4G_ERR_* otherwise; message via s4g_last_error() (thread-local)
+ *   - token matrices are row-major [rows, C]; feature maps are NHWC; dtype 0 = fp32 validation mode,
+ *     dtype 1 = bf16 activations / fp32 accumulate (parameters, gradients and the residual stream are fp32 in both)
+ */
+#ifndef SSL4GIE_B200_H
+#define SSL4GIE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define S4G_OK 0
+#define S4G_ERR_SHAPE (-1)
+#define S4G_ERR_ALIGN (-2)
+#define S4G_ERR_WORKSPACE (-3)
+#define S4G_ERR_ARCH (-4)
+#define S4G_ERR_CUDA (-5)
+#define S4G_ERR_STATE (-6)
+#define S4G_ERR_NAME (-7)
+
+#define S4G_DTYPE_F32 0
+#define S4G_DTYPE_BF16 1
+
+#define S4G_DENSE_NONE 0  /* classification branch, Models/models.py:348-354 */
+#define S4G_DENSE_SEG 1   /* dense="seg"   */
+#define S4G_DENSE_DEPTH 2 /* dense="depth" */
+
+#define S4G_BACKEND_SIMT 0    /* FFMA kernels: fp32 validation mode / cross-check */
+#define S4G_BACKEND_TENSOR 1  /* tcgen05 + TMEM + TMA contractions, tensor-core attention (bf16 only) */
+
+int s4g_version(void);
+const char* s4g_last_error(void);
+/* Checks the device is sm_100 and prepares per-device state. */
+int s4g_init(int device);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Whole-model schedule: replaces VisionTransformer_from_Any.forward / ViT_from_MAE.forward /
+ * ViT_from_MoCoV3.forward (Models/models.py:340-357, :458-475, :560-578), DPT_decoder.forward
+ * (Models/DPT_decoder.py:501-539) and their autograd backward (train_segmentation.py:45-47).
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct S4GModel S4GModel;
+
+typedef struct {
+  int batch;          /* images per call on this GPU */
+  int dense;          /* S4G_DENSE_* */
+  int dtype;          /* S4G_DTYPE_* */
+  int backend;        /* S4G_BACKEND_* */
+  int frozen;         /* encoder under no_grad (Models/models.py:341-343) */
+  int world_size;     /* ranks sharing BatchNorm statistics (SyncBatchNorm, train_segmentation.py:199); 1 = local BN */
+  int num_classes;    /* lin_head width for S4G_DENSE_NONE (0 = no head) */
+  int out_token;      /* 0 = "cls", 1 = "spatial" (Models/models.py:349-352) */
+  float dropout_p;    /* seg head nn.Dropout(0.1) (Models/DPT_decoder.py:494) */
+} S4GModelDesc;
+
+int s4g_model_create(const S4GModelDesc* desc, S4GModel** out);
+void s4g_model_destroy(S4GModel* m);
+/* Bind one state_dict entry by its reference name (e.g. "blocks.0.attn.qkv.weight",
+ * "decoder.refinenet1.resConfUnit2.bn1.running_mean").  `grad` may be NULL (buffers, frozen parameters).
+ * All float entries are fp32; num_batches_tracked is int64.  May be called again to re-point storage. */
+int s4g_model_bind(S4GModel* m, const char* name, void* data, void* grad, long long numel);
+/* Optional: tells the library that all bound gradients live in [grads, grads + bytes) so backward can clear them
+ * with one memset. */
+int s4g_model_set_grad_arena(S4GModel* m, void* grads, size_t bytes);
+size_t s4g_model_workspace_bytes(S4GModel* m);
+int s4g_model_set_workspace(S4GModel* m, void* workspace, size_t bytes);
+/* images [B,3,224,224] fp32 NCHW -> out: seg logits / depth sigmoid [B,1,224,224] fp32, or [B,num_classes].
+ * training != 0: batch statistics + running-stat update + dropout(seed) and activations kept for backward.
+ * dropout_mask: optional [B*112*112*256] bytes (NHWC) overriding the RNG (parity tests); NULL = RNG. */
+int s4g_model_forward(S4GModel* m, const float* images, float* out, int training, uint64_t seed,
+                      const uint8_t* dropout_mask, void* stream);
+/* dout: gradient w.r.t. `out`.  Writes (overwrites) the gradient of every bound parameter that has one. */
+int s4g_model_backward(S4GModel* m, const float* dout, void* stream);
+/* Cross-rank sum used by SyncBatchNorm statistics (forward: sum/sumsq, backward: sum dy / sum dy*xhat).  Called
+ * on the host while enqueueing; must enqueue an in-place sum-all-reduce of `count` doubles on `stream`. */
+typedef int (*s4g_allreduce_fn)(void* user, void* device_doubles, int count, void* stream);
+int s4g_model_set_allreduce(S4GModel* m, s4g_allreduce_fn fn, void* user);
+/* Gradient-bucket boundaries for overlapping the data-parallel all-reduce with backward (DDP reducer,
+ * train_segmentation.py:203).  The library records events[i] (cudaEvent_t) on `stream` during backward once every
+ * parameter gradient of bucket i is final: bucket 0 = DPT decoder, buckets 1..n-1 = encoder blocks from the last
+ * to the first, split evenly, the final bucket also covering patch_embed / cls_token / pos_embed. */
+int s4g_model_set_bucket_events(S4GModel* m, void** events, int n);
+/* Name list of the parameters whose gradients belong to bucket i, as a '\n'-separated string (host memory owned by
+ * the library, valid until the next call). */
+const char* s4g_model_bucket_params(S4GModel* m, int bucket, int n_buckets);
+/* number of kernels the last forward / backward call enqueued */
+int s4g_model_last_launches(S4GModel* m);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Operator-level entry points (used by the parity tests and by the loss / optimizer modules)
+ * ---------------------------------------------------------------------------------------------------------- */
+/* nn.Linear / 1x1 Conv2d: out[M,N] = epilogue(A[M,K] . W[N,K]^T + bias).  act: 0 none, 1 GELU(erf) (timm Mlp),
+ * 3 ReLU.  residual: optional fp32 [M,N] added after the activation (timm Block residual).  A, W are `dtype`;
+ * out is fp32 if out_f32 else `dtype`. */
+int s4g_linear_fwd(const void* A, const void* W, const float* bias, const float* residual, void* out, long long M,
+                   int N, int K, int act, int out_f32, int dtype, int backend, void* stream);
+/* dW[N,K] (fp32) = dY[M,N]^T . X[M,K] */
+int s4g_linear_wgrad(const void* dY, const void* X, float* dW, long long M, int N, int K, int dtype, int backend,
+                     void* scratch, size_t scratch_bytes, void* stream);
+/* nn.Conv2d 3x3 stride 1 pad 1 on NHWC: X [B,H,W,Cin], Wp [Cout][3*3][Cin] (packed), out [B,H,W,Cout] */
+int s4g_conv3x3_fwd(const void* X, const void* Wp, const float* bias, void* out, int B, int H, int W, int Cin,
+                    int Cout, int dtype, int backend, void* stream);
+/* dWp [Cout][9][Cin] fp32 */
+int s4g_conv3x3_wgrad(const void* dY, const void* X, float* dWp, int B, int H, int W, int Cin, int Cout, int dtype,
+                      int backend, void* scratch, size_t scratch_bytes, void* stream);
+size_t s4g_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps);
+/* nn.LayerNorm(C, eps) on fp32 rows -> `dtype` output; saves mean/rstd */
+int s4g_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                      int rows, int C, float eps, int dtype, void* stream);
+int s4g_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                      const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, int dtype,
+                      void* stream);
+/* timm Attention core: qkv [B*N, 3*H*64] -> o [B*N, H*64], lse [B,H,N] */
+int s4g_attention_fwd(const void* qkv, void* o, float* lse, int B, int N, int H, int dtype, int backend, void* stream);
+int s4g_attention_bwd(const void* qkv, const void* o, const void* dout, const float* lse, void* dqkv, int B, int N,
+                      int H, int dtype, int backend, void* stream);
+/* F.interpolate(scale_factor=2, mode="bilinear", align_corners=True) on NHWC (Models/DPT_decoder.py:295-297) */
+int s4g_bilinear2x_fwd(const void* x, void* y, int B, int H, int W, int C, int dtype, void* stream);
+int s4g_bilinear2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, int dtype, void* stream);
+
+/* SoftDiceLoss.forward (Binary_segmentation/Metrics/losses.py:10-24) and its gradient.
+ * scratch: >= s4g_dice_scratch_bytes(B) bytes, kept between fwd and bwd. */
+size_t s4g_dice_scratch_bytes(int B);
+int s4g_dice_fwd(const float* logits, const float* targets, void* scratch, float* loss, int B, int HW, float smooth,
+                 void* stream);
+int s4g_dice_bwd(const float* logits, const float* targets, const void* scratch, const float* grad_out,
+                 float* dlogits, int B, int HW, float smooth, void* stream);
+/* ScaleAndShiftInvariantLoss.forward (Depth_estimation/Metrics/losses.py:130-146), batch-based reduction.
+ * ssi_out: optional [B,H,W] prediction_ssi (losses.py:138,148-151). */
+size_t s4g_ssi_scratch_bytes(int B);
+int s4g_ssi_fwd(const float* pred, const float* target, void* scratch, float* loss, float* ssi_out, int B, int H,
+                int W, float alpha, int scales, void* stream);
+int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const float* grad_out, float* dpred, int B,
+                int H, int W, float alpha, int scales, void* stream);
+
+/* torch.optim.AdamW step over a flat fp32 arena (train_segmentation.py:204). grad_scale multiplies g first
+ * (1/world_size after a sum-all-reduce). step counts from 1. */
+int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                   float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

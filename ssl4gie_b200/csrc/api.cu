@@ -1,0 +1,137 @@
+// C-ABI plumbing: error state, device check, operator-level entry points declared in include/ssl4gie_b200.h.
+#include "kernels.h"
+
+static thread_local std::string g_err;
+void s4g_set_error(const std::string& msg) { g_err = msg; }
+int s4g_cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof(buf), "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+  g_err = buf;
+  return S4G_ERR_CUDA;
+}
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+#define DISPATCH(dtype, expr_f, expr_h)                      \
+  do {                                                       \
+    if ((dtype) == S4G_DTYPE_F32) { typedef float T; return (expr_f); } \
+    if ((dtype) == S4G_DTYPE_BF16) { typedef bf16 T; return (expr_h); } \
+    s4g_set_error("bad dtype");                              \
+    return S4G_ERR_SHAPE;                                    \
+  } while (0)
+
+extern "C" {
+
+int s4g_version(void) { return 100; }
+const char* s4g_last_error(void) { return g_err.c_str(); }
+
+int s4g_init(int device) {
+  cudaDeviceProp prop;
+  S4G_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    char buf[128];
+    snprintf(buf, sizeof(buf), "libssl4gie_b200 is built for sm_100a only; device %d is sm_%d%d", device, prop.major, prop.minor);
+    g_err = buf;
+    return S4G_ERR_ARCH;
+  }
+  S4G_CUDA(cudaSetDevice(device));
+  return umma_init();
+}
+
+static int check_backend(int dtype, int backend) {
+  if (backend == S4G_BACKEND_TENSOR && dtype != S4G_DTYPE_BF16) {
+    s4g_set_error("tensor-core backend needs bf16");
+    return S4G_ERR_STATE;
+  }
+  return 0;
+}
+
+int s4g_linear_fwd(const void* A, const void* W, const float* bias, const float* residual, void* out, long long M, int N,
+                   int K, int act, int out_f32, int dtype, int backend, void* stream) {
+  S4G_TRY(check_backend(dtype, backend));
+  EpiParams e{};
+  e.bias = bias; e.out = out; e.ldo = N; e.mode = act; e.out_f32 = out_f32; e.alpha = 1.f;
+  e.res = residual; e.res_f32 = 1; e.ldr = N;
+  const ConvGeom g = linear_geom(M, N, K);
+  if (backend == S4G_BACKEND_TENSOR) return umma_conv_fprop(g, (const bf16*)A, (const bf16*)W, e, ST(stream));
+  DISPATCH(dtype, simt_conv_fprop<T>(g, (const T*)A, (const T*)W, e, ST(stream)), simt_conv_fprop<T>(g, (const T*)A, (const T*)W, e, ST(stream)));
+}
+int s4g_linear_wgrad(const void* dY, const void* X, float* dW, long long M, int N, int K, int dtype, int backend,
+                     void* scratch, size_t scratch_bytes, void* stream) {
+  S4G_TRY(check_backend(dtype, backend));
+  const ConvGeom g = linear_geom(M, N, K);
+  if (backend == S4G_BACKEND_TENSOR) return umma_conv_wgrad(g, (const bf16*)dY, (const bf16*)X, dW, (float*)scratch, scratch_bytes, ST(stream));
+  DISPATCH(dtype, simt_conv_wgrad<T>(g, (const T*)dY, (const T*)X, dW, ST(stream)), simt_conv_wgrad<T>(g, (const T*)dY, (const T*)X, dW, ST(stream)));
+}
+int s4g_conv3x3_fwd(const void* X, const void* Wp, const float* bias, void* out, int B, int H, int W, int Cin, int Cout,
+                    int dtype, int backend, void* stream) {
+  S4G_TRY(check_backend(dtype, backend));
+  EpiParams e{};
+  e.bias = bias; e.out = out; e.ldo = Cout; e.alpha = 1.f;
+  const ConvGeom g = conv3_geom(B, H, W, Cin, Cout);
+  if (backend == S4G_BACKEND_TENSOR) return umma_conv_fprop(g, (const bf16*)X, (const bf16*)Wp, e, ST(stream));
+  DISPATCH(dtype, simt_conv_fprop<T>(g, (const T*)X, (const T*)Wp, e, ST(stream)), simt_conv_fprop<T>(g, (const T*)X, (const T*)Wp, e, ST(stream)));
+}
+int s4g_conv3x3_wgrad(const void* dY, const void* X, float* dWp, int B, int H, int W, int Cin, int Cout, int dtype,
+                      int backend, void* scratch, size_t scratch_bytes, void* stream) {
+  S4G_TRY(check_backend(dtype, backend));
+  const ConvGeom g = conv3_geom(B, H, W, Cin, Cout);
+  if (backend == S4G_BACKEND_TENSOR) return umma_conv_wgrad(g, (const bf16*)dY, (const bf16*)X, dWp, (float*)scratch, scratch_bytes, ST(stream));
+  DISPATCH(dtype, simt_conv_wgrad<T>(g, (const T*)dY, (const T*)X, dWp, ST(stream)), simt_conv_wgrad<T>(g, (const T*)dY, (const T*)X, dWp, ST(stream)));
+}
+size_t s4g_wgrad_scratch_bytes(int B, int H, int W, int Cin, int Cout, int taps) {
+  ConvGeom g = taps == 9 ? conv3_geom(B, H, W, Cin, Cout) : linear_geom((long long)B * H * W, Cout, Cin);
+  return umma_wgrad_scratch_bytes(g);
+}
+int s4g_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd, int rows,
+                      int C, float eps, int dtype, void* stream) {
+  DISPATCH(dtype, k_layernorm_fwd<T>(x, gamma, beta, (T*)y, mean, rstd, rows, C, eps, ST(stream)),
+           k_layernorm_fwd<T>(x, gamma, beta, (T*)y, mean, rstd, rows, C, eps, ST(stream)));
+}
+int s4g_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                      const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, int dtype, void* stream) {
+  S4G_CUDA(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, ST(stream)));
+  S4G_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, ST(stream)));
+  DISPATCH(dtype, k_layernorm_bwd<T>((const T*)dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, C, ST(stream)),
+           k_layernorm_bwd<T>((const T*)dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, C, ST(stream)));
+}
+int s4g_attention_fwd(const void* qkv, void* o, float* lse, int B, int N, int H, int dtype, int backend, void* stream) {
+  S4G_TRY(check_backend(dtype, backend));
+  if (backend == S4G_BACKEND_TENSOR) return attn_fwd_mma((const bf16*)qkv, (bf16*)o, lse, B, N, H, ST(stream));
+  DISPATCH(dtype, attn_fwd_simt<T>((const T*)qkv, (T*)o, lse, B, N, H, ST(stream)), attn_fwd_simt<T>((const T*)qkv, (T*)o, lse, B, N, H, ST(stream)));
+}
+int s4g_attention_bwd(const void* qkv, const void* o, const void* dout, const float* lse, void* dqkv, int B, int N, int H,
+                      int dtype, int backend, void* stream) {
+  S4G_TRY(check_backend(dtype, backend));
+  if (backend == S4G_BACKEND_TENSOR) return attn_bwd_mma((const bf16*)qkv, (const bf16*)o, (const bf16*)dout, lse, (bf16*)dqkv, B, N, H, ST(stream));
+  DISPATCH(dtype, attn_bwd_simt<T>((const T*)qkv, (const T*)o, (const T*)dout, lse, (T*)dqkv, B, N, H, ST(stream)),
+           attn_bwd_simt<T>((const T*)qkv, (const T*)o, (const T*)dout, lse, (T*)dqkv, B, N, H, ST(stream)));
+}
+int s4g_bilinear2x_fwd(const void* x, void* y, int B, int H, int W, int C, int dtype, void* stream) {
+  DISPATCH(dtype, k_bilinear2x_fwd<T>((const T*)x, (T*)y, B, H, W, C, ST(stream)), k_bilinear2x_fwd<T>((const T*)x, (T*)y, B, H, W, C, ST(stream)));
+}
+int s4g_bilinear2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, int dtype, void* stream) {
+  DISPATCH(dtype, k_bilinear2x_bwd<T>((const T*)dy, (T*)dx, B, H, W, C, ST(stream)), k_bilinear2x_bwd<T>((const T*)dy, (T*)dx, B, H, W, C, ST(stream)));
+}
+size_t s4g_dice_scratch_bytes(int B) { return sizeof(double) * 3 * (size_t)B; }
+int s4g_dice_fwd(const float* logits, const float* targets, void* scratch, float* loss, int B, int HW, float smooth, void* stream) {
+  return k_dice_fwd(logits, targets, (float*)scratch, loss, B, HW, smooth, ST(stream));
+}
+int s4g_dice_bwd(const float* logits, const float* targets, const void* scratch, const float* grad_out, float* dlogits, int B,
+                 int HW, float smooth, void* stream) {
+  return k_dice_bwd(logits, targets, (const float*)scratch, grad_out, dlogits, B, HW, smooth, ST(stream));
+}
+size_t s4g_ssi_scratch_bytes(int B) { return sizeof(float) * ssi_scratch_floats(B); }
+int s4g_ssi_fwd(const float* pred, const float* target, void* scratch, float* loss, float* ssi_out, int B, int H, int W,
+                float alpha, int scales, void* stream) {
+  return k_ssi_fwd(pred, target, (float*)scratch, loss, ssi_out, B, H, W, alpha, scales, ST(stream));
+}
+int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const float* grad_out, float* dpred, int B, int H,
+                int W, float alpha, int scales, void* stream) {
+  return k_ssi_bwd(pred, target, (const float*)scratch, grad_out, dpred, B, H, W, alpha, scales, ST(stream));
+}
+int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
+  return k_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, grad_scale, ST(stream));
+}
+
+}  // extern "C"

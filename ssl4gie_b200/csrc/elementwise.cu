@@ -1,0 +1,1052 @@
+// HBM-bound kernels of the ViT-B/16 + DPT path: patchify, token assembly, LayerNorm, GELU', ReLU, residual
+// adds, pixel (un)shuffle for k==s transposed convs, stride-2 im2col, bilinear x2 (align_corners=True),
+// BatchNorm (train) statistics / apply / backward, the two head tails, weight packing.
+// All NHWC kernels move 8 channels per thread (16 B bf16 / 32 B fp32), coalesced along C.
+#include "kernels.h"
+
+#define GRID1D(n, bs) dim3((unsigned)min((long long)cdiv((n), (bs)), (long long)148 * 32)), dim3(bs)
+#define FOR_GRID(i, n) \
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < (n); i += (long long)gridDim.x * blockDim.x)
+
+// ------------------------------------------------------------------------------------------ patch embed
+// timm PatchEmbed (reference Models/models.py:326): Conv2d(3,768,k16,s16) == GEMM over k = c*256 + i*16 + j
+template <typename T>
+__global__ void patchify_kernel(const float* __restrict__ img, T* __restrict__ out, int B) {
+  const long long n = (long long)B * 196 * 96;  // 768/8 groups per patch
+  FOR_GRID(t, n) {
+    const int g = (int)(t % 96);
+    const long long pidx = t / 96;
+    const int p = (int)(pidx % 196), b = (int)(pidx / 196);
+    const int c = g / 32, i = (g % 32) / 2, j0 = (g % 2) * 8;
+    const int ph = p / 14, pw = p % 14;
+    const float* src = img + (((long long)b * 3 + c) * 224 + ph * 16 + i) * 224 + pw * 16 + j0;
+    Vec8<T> v;
+    float4 a = *reinterpret_cast<const float4*>(src), bq = *reinterpret_cast<const float4*>(src + 4);
+    v.v[0] = a.x; v.v[1] = a.y; v.v[2] = a.z; v.v[3] = a.w; v.v[4] = bq.x; v.v[5] = bq.y; v.v[6] = bq.z; v.v[7] = bq.w;
+    v.store(out + pidx * 768 + g * 8);
+  }
+}
+template <typename T> int k_patchify(const float* img, T* out, int B, cudaStream_t st) {
+  const long long n = (long long)B * 196 * 96;
+  patchify_kernel<T><<<GRID1D(n, 256), 0, st>>>(img, out, B);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// _pos_embed (Models/models.py:330 / :445-448): x[b,0] = cls + pos[0]; x[b,1+p] = pe[b,p] + pos[1+p]
+__global__ void assemble_tokens_kernel(const float* __restrict__ pe, const float* __restrict__ cls,
+                                       const float* __restrict__ pos, float* __restrict__ x, int B) {
+  const long long n = (long long)B * 197 * 192;
+  FOR_GRID(t, n) {
+    const int c4 = (int)(t % 192);
+    const long long row = t / 192;
+    const int tok = (int)(row % 197), b = (int)(row / 197);
+    const float4 pz = reinterpret_cast<const float4*>(pos)[tok * 192 + c4];
+    float4 v = tok == 0 ? reinterpret_cast<const float4*>(cls)[c4]
+                        : reinterpret_cast<const float4*>(pe)[((long long)b * 196 + tok - 1) * 192 + c4];
+    v.x += pz.x; v.y += pz.y; v.z += pz.z; v.w += pz.w;
+    reinterpret_cast<float4*>(x)[t] = v;
+  }
+}
+int k_assemble_tokens(const float* pe, const float* cls, const float* pos, float* x, int B, cudaStream_t st) {
+  assemble_tokens_kernel<<<GRID1D((long long)B * 197 * 192, 256), 0, st>>>(pe, cls, pos, x, B);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// dpos[tok] = sum_b dx[b,tok]; dcls = sum_b dx[b,0]  (either may be null)
+__global__ void assemble_tokens_bwd_kernel(const float* __restrict__ dx, float* __restrict__ dcls,
+                                           float* __restrict__ dpos, int B) {
+  const int n = 197 * 768;
+  FOR_GRID(t, n) {
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += dx[(long long)b * n + t];
+    if (dpos) dpos[t] = s;
+    if (dcls && t < 768) dcls[t] = s;
+  }
+}
+int k_assemble_tokens_bwd(const float* dx, float* dpe, float* dcls, float* dpos, int B, cudaStream_t st) {
+  (void)dpe;
+  assemble_tokens_bwd_kernel<<<GRID1D(197 * 768, 256), 0, st>>>(dx, dcls, dpos, B);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ LayerNorm
+// one warp per token row, fp32 statistics (two-pass in registers), T output
+template <typename T, int C>
+__global__ void __launch_bounds__(256) layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, T* __restrict__ y,
+                                                            float* __restrict__ mean, float* __restrict__ rstd, int rows,
+                                                            float eps) {
+  constexpr int V = C / 128;  // float4 per lane
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * C);
+  float4 v[V];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < V; ++i) { v[i] = xr[lane + 32 * i]; s += v[i].x + v[i].y + v[i].z + v[i].w; }
+  const float mu = warp_sum(s) * (1.0f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const float a = v[i].x - mu, b = v[i].y - mu, c = v[i].z - mu, d = v[i].w - mu;
+    q += a * a + b * b + c * c + d * d;
+  }
+  const float rs = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
+  if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c4 = lane + 32 * i;
+    const float4 g = reinterpret_cast<const float4*>(gamma)[c4], b = reinterpret_cast<const float4*>(beta)[c4];
+    T* o = y + (long long)row * C + c4 * 4;
+    o[0] = from_f<T>((v[i].x - mu) * rs * g.x + b.x);
+    o[1] = from_f<T>((v[i].y - mu) * rs * g.y + b.y);
+    o[2] = from_f<T>((v[i].z - mu) * rs * g.z + b.z);
+    o[3] = from_f<T>((v[i].w - mu) * rs * g.w + b.w);
+  }
+}
+template <typename T>
+int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y, float* mean, float* rstd, int rows,
+                    int C, float eps, cudaStream_t st) {
+  if (C == 768) layernorm_fwd_kernel<T, 768><<<cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, y, mean, rstd, rows, eps);
+  else if (C == 512) layernorm_fwd_kernel<T, 512><<<cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, y, mean, rstd, rows, eps);
+  else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// each block owns ROWS_PER_BLOCK rows; warps stride over them; dgamma/dbeta partials reduced in smem, one atomic
+// per column per block
+template <typename T, int C>
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
+                                                            const float* __restrict__ gamma,
+                                                            const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                            const float* __restrict__ dres, float* __restrict__ dx,
+                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                            int rows, int rows_per_block) {
+  constexpr int V = C / 128;
+  __shared__ float sg[C], sb[C];
+  for (int i = threadIdx.x; i < C; i += 256) { sg[i] = 0.f; sb[i] = 0.f; }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float4 ag[V], ab[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) { ag[i] = make_float4(0, 0, 0, 0); ab[i] = make_float4(0, 0, 0, 0); }
+  for (int row = r0 + warp; row < r1; row += 8) {
+    const float mu = mean[row], rs = rstd[row];
+    const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * C);
+    const T* dyr = dy + (long long)row * C;
+    float4 xh[V], g[V];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const int c4 = lane + 32 * i;
+      const float4 xv = xr[c4];
+      const float4 gm = reinterpret_cast<const float4*>(gamma)[c4];
+      const float d0 = to_f(dyr[c4 * 4]), d1 = to_f(dyr[c4 * 4 + 1]), d2 = to_f(dyr[c4 * 4 + 2]), d3 = to_f(dyr[c4 * 4 + 3]);
+      xh[i] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
+      g[i] = make_float4(d0 * gm.x, d1 * gm.y, d2 * gm.z, d3 * gm.w);
+      s1 += g[i].x + g[i].y + g[i].z + g[i].w;
+      s2 += g[i].x * xh[i].x + g[i].y * xh[i].y + g[i].z * xh[i].z + g[i].w * xh[i].w;
+      ag[i].x += d0 * xh[i].x; ag[i].y += d1 * xh[i].y; ag[i].z += d2 * xh[i].z; ag[i].w += d3 * xh[i].w;
+      ab[i].x += d0; ab[i].y += d1; ab[i].z += d2; ab[i].w += d3;
+    }
+    s1 = warp_sum(s1) * (1.0f / C);
+    s2 = warp_sum(s2) * (1.0f / C);
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const int c4 = lane + 32 * i;
+      float4 o = make_float4(rs * (g[i].x - s1 - xh[i].x * s2), rs * (g[i].y - s1 - xh[i].y * s2),
+                             rs * (g[i].z - s1 - xh[i].z * s2), rs * (g[i].w - s1 - xh[i].w * s2));
+      if (dres) {
+        const float4 r = reinterpret_cast<const float4*>(dres + (long long)row * C)[c4];
+        o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+      }
+      reinterpret_cast<float4*>(dx + (long long)row * C)[c4] = o;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c = (lane + 32 * i) * 4;
+    atomicAdd(&sg[c], ag[i].x); atomicAdd(&sg[c + 1], ag[i].y); atomicAdd(&sg[c + 2], ag[i].z); atomicAdd(&sg[c + 3], ag[i].w);
+    atomicAdd(&sb[c], ab[i].x); atomicAdd(&sb[c + 1], ab[i].y); atomicAdd(&sb[c + 2], ab[i].z); atomicAdd(&sb[c + 3], ab[i].w);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += 256) { atomicAdd(&dgamma[i], sg[i]); atomicAdd(&dbeta[i], sb[i]); }
+}
+template <typename T>
+int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                    const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st) {
+  const int rpb = max(8, cdiv(rows, 148 * 4));
+  if (C == 768)
+    layernorm_bwd_kernel<T, 768><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb);
+  else if (C == 512)
+    layernorm_bwd_kernel<T, 512><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb);
+  else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ small elementwise
+template <typename T> __global__ void dgelu_mul_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out, long long n8) {
+  FOR_GRID(i, n8) {
+    Vec8<T> a, b;
+    a.load(dy + i * 8); b.load(u + i * 8);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a.v[k] *= dgelu_f(b.v[k]);
+    a.store(out + i * 8);
+  }
+}
+template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st) {
+  dgelu_mul_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(dy, u, out, n / 8);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// column sums of a [M, N] matrix (bias gradients); out must be zeroed; 32 cols x 8 row-lanes per block
+template <typename T> __global__ void colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, long long M, int N, int ld, int rows_per_block) {
+  __shared__ float red[8][33];
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31), rl = threadIdx.x >> 5;
+  const long long r0 = (long long)blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float s = 0.f;
+  if (col < N)
+    for (long long r = r0 + rl; r < r1; r += 8) s += to_f(dy[r * ld + col]);
+  red[rl][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (rl == 0 && col < N) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) s += red[i][threadIdx.x];
+    atomicAdd(&out[col], s);
+  }
+}
+template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st) {
+  const int rpb = (int)max((long long)64, (M + 147) / 148);
+  dim3 grid(cdiv(N, 32), cdiv(M, rpb));
+  colsum_kernel<T><<<grid, 256, 0, st>>>(dy, out, M, N, ld, rpb);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// Slice(1)+Transpose+Unflatten (Models/DPT_decoder.py:503-515): token rows 1..196 ARE the NHWC map
+template <typename T> __global__ void tokens_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ out, int B) {
+  const long long n = (long long)B * 196 * 96;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % 96);
+    const long long pidx = t / 96;
+    const int p = (int)(pidx % 196), b = (int)(pidx / 196);
+    Vec8<float> v;
+    v.load(x + ((long long)b * 197 + 1 + p) * 768 + g * 8);
+    Vec8<T> o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o.v[k] = v.v[k];
+    o.store(out + pidx * 768 + g * 8);
+  }
+}
+template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st) {
+  tokens_to_nhwc_kernel<T><<<GRID1D((long long)B * 196 * 96, 256), 0, st>>>(x, out, B);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap, float* __restrict__ dx, int B, int accumulate) {
+  const long long n = (long long)B * 197 * 96;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % 96);
+    const long long row = t / 96;
+    const int tok = (int)(row % 197), b = (int)(row / 197);
+    float* d = dx + row * 768 + g * 8;
+    Vec8<float> o;
+    if (accumulate) o.load(d);
+    else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o.v[k] = 0.f;
+    }
+    if (tok > 0) {
+      Vec8<T> v;
+      v.load(dtap + ((long long)b * 196 + tok - 1) * 768 + g * 8);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o.v[k] += v.v[k];
+    } else if (accumulate) {
+      continue;
+    }
+    o.store(d);
+  }
+}
+template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st) {
+  tap_grad_kernel<T><<<GRID1D((long long)B * 197 * 96, 256), 0, st>>>(dtap, dx, B, accumulate);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+template <typename T> __global__ void cast_f32_kernel(const float* __restrict__ in, T* __restrict__ out, long long n) {
+  FOR_GRID(i, n) out[i] = from_f<T>(in[i]);
+}
+template <typename T> int k_cast_f32(const float* in, T* out, long long n, cudaStream_t st) {
+  cast_f32_kernel<T><<<GRID1D(n, 256), 0, st>>>(in, out, n);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+template <typename T> __global__ void relu_kernel(const T* __restrict__ x, T* __restrict__ y, long long n8) {
+  FOR_GRID(i, n8) {
+    Vec8<T> a;
+    a.load(x + i * 8);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a.v[k] = fmaxf(a.v[k], 0.f);
+    a.store(y + i * 8);
+  }
+}
+template <typename T> int k_relu(const T* x, T* y, long long n, cudaStream_t st) {
+  relu_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(x, y, n / 8);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T> __global__ void relu_bwd_add_kernel(const T* __restrict__ dr, const T* __restrict__ x, const T* __restrict__ dskip, T* __restrict__ dx, long long n8) {
+  FOR_GRID(i, n8) {
+    Vec8<T> a, b, c;
+    a.load(dr + i * 8); b.load(x + i * 8);
+    if (dskip) c.load(dskip + i * 8);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a.v[k] = (b.v[k] > 0.f ? a.v[k] : 0.f) + (dskip ? c.v[k] : 0.f);
+    a.store(dx + i * 8);
+  }
+}
+template <typename T> int k_relu_bwd_add(const T* dr, const T* x, const T* dskip, T* dx, long long n, cudaStream_t st) {
+  relu_bwd_add_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(dr, x, dskip, dx, n / 8);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T> __global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, long long n8) {
+  FOR_GRID(i, n8) {
+    Vec8<T> u, v;
+    u.load(a + i * 8); v.load(b + i * 8);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) u.v[k] += v.v[k];
+    u.store(y + i * 8);
+  }
+}
+template <typename T> int k_add(const T* a, const T* b, T* y, long long n, cudaStream_t st) {
+  add_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(a, b, y, n / 8);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ConvTranspose2d with kernel == stride (Models/DPT_decoder.py:341-350,365-374) = GEMM to
+// ycol[p][(kh,kw,co)] then this scatter: out[b, h*k+kh, w*k+kw, co] = ycol + bias[co]
+template <typename T> __global__ void pixel_shuffle_kernel(const T* __restrict__ ycol, const float* __restrict__ bias, T* __restrict__ out, int B, int H, int W, int C, int k, int unshuffle) {
+  const int c8 = C / 8;
+  const long long n = (long long)B * H * k * W * k * c8;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % c8);
+    long long r = t / c8;
+    const int ow = (int)(r % (W * k)); r /= (W * k);
+    const int oh = (int)(r % (H * k));
+    const int b = (int)(r / (H * k));
+    const int h = oh / k, kh = oh % k, w = ow / k, kw = ow % k;
+    const long long src = ((((long long)b * H + h) * W + w) * (k * k) + kh * k + kw) * C + g * 8;
+    const long long dst = (((long long)b * H * k + oh) * (W * k) + ow) * C + g * 8;
+    Vec8<T> v;
+    if (unshuffle) { v.load(out + dst); v.store(const_cast<T*>(ycol) + src); }
+    else {
+      v.load(ycol + src);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v.v[i] += bias[g * 8 + i];
+      v.store(out + dst);
+    }
+  }
+}
+template <typename T> int k_pixel_shuffle(const T* ycol, const float* bias, T* out, int B, int H, int W, int C, int k, cudaStream_t st) {
+  const long long n = (long long)B * H * k * W * k * (C / 8);
+  pixel_shuffle_kernel<T><<<GRID1D(n, 256), 0, st>>>(ycol, bias, out, B, H, W, C, k, 0);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T> int k_pixel_unshuffle(const T* dout, T* dycol, int B, int H, int W, int C, int k, cudaStream_t st) {
+  const long long n = (long long)B * H * k * W * k * (C / 8);
+  pixel_shuffle_kernel<T><<<GRID1D(n, 256), 0, st>>>(dycol, nullptr, const_cast<T*>(dout), B, H, W, C, k, 1);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// Conv2d 3x3 stride 2 pad 1 (Models/DPT_decoder.py:403-409) as explicit im2col + GEMM (only one small layer)
+template <typename T> __global__ void im2col_s2_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H, int W, int C) {
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2, c8 = C / 8;
+  const long long n = (long long)B * Ho * Wo * 9 * c8;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % c8);
+    long long r = t / c8;
+    const int tap = (int)(r % 9); r /= 9;
+    const int wo = (int)(r % Wo); r /= Wo;
+    const int ho = (int)(r % Ho);
+    const int b = (int)(r / Ho);
+    const int hi = ho * 2 + tap / 3 - 1, wi = wo * 2 + tap % 3 - 1;
+    Vec8<T> v;
+    if (hi >= 0 && hi < H && wi >= 0 && wi < W) v.load(x + (((long long)b * H + hi) * W + wi) * C + g * 8);
+    else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v.v[i] = 0.f;
+    }
+    v.store(col + t * 8);
+  }
+}
+template <typename T> int k_im2col_s2(const T* x, T* col, int B, int H, int W, int C, cudaStream_t st) {
+  const long long n = (long long)B * ((H + 1) / 2) * ((W + 1) / 2) * 9 * (C / 8);
+  im2col_s2_kernel<T><<<GRID1D(n, 256), 0, st>>>(x, col, B, H, W, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T> __global__ void col2im_s2_kernel(const T* __restrict__ dcol, T* __restrict__ dx, int B, int H, int W, int C) {
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2, c8 = C / 8;
+  const long long n = (long long)B * H * W * c8;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % c8);
+    long long r = t / c8;
+    const int wi = (int)(r % W); r /= W;
+    const int hi = (int)(r % H);
+    const int b = (int)(r / H);
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    for (int kr = 0; kr < 3; ++kr) {
+      const int hn = hi + 1 - kr;
+      if (hn < 0 || (hn & 1) || hn / 2 >= Ho) continue;
+      for (int ks = 0; ks < 3; ++ks) {
+        const int wn = wi + 1 - ks;
+        if (wn < 0 || (wn & 1) || wn / 2 >= Wo) continue;
+        Vec8<T> v;
+        v.load(dcol + ((((long long)b * Ho + hn / 2) * Wo + wn / 2) * 9 + kr * 3 + ks) * C + g * 8);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += v.v[i];
+      }
+    }
+    Vec8<T> o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+    o.store(dx + t * 8);
+  }
+}
+template <typename T> int k_col2im_s2(const T* dcol, T* dx, int B, int H, int W, int C, cudaStream_t st) {
+  col2im_s2_kernel<T><<<GRID1D((long long)B * H * W * (C / 8), 256), 0, st>>>(dcol, dx, B, H, W, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ bilinear x2
+// F.interpolate(scale_factor=2, mode="bilinear", align_corners=True) (Models/DPT_decoder.py:295-297,93-98):
+// src = dst * (H-1)/(2H-1); ATen computes src, floor index and lambda in fp32 — mirrored here.
+__device__ __forceinline__ void bil_src(int o, int in_size, float scale, int& i0, int& i1, float& l0, float& l1) {
+  const float s = scale * o;
+  i0 = (int)s;
+  i1 = i0 + (i0 < in_size - 1 ? 1 : 0);
+  l1 = s - i0;
+  l0 = 1.f - l1;
+}
+template <typename T> __global__ void bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
+  const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
+  const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
+  const long long n = (long long)B * Ho * Wo * c8;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % c8);
+    long long r = t / c8;
+    const int ow = (int)(r % Wo); r /= Wo;
+    const int oh = (int)(r % Ho);
+    const int b = (int)(r / Ho);
+    int h0, h1, w0, w1; float lh0, lh1, lw0, lw1;
+    bil_src(oh, H, sh, h0, h1, lh0, lh1);
+    bil_src(ow, W, sw, w0, w1, lw0, lw1);
+    const T* base = x + (long long)b * H * W * C + g * 8;
+    Vec8<T> a, bq, c, d, o;
+    a.load(base + ((long long)h0 * W + w0) * C); bq.load(base + ((long long)h0 * W + w1) * C);
+    c.load(base + ((long long)h1 * W + w0) * C); d.load(base + ((long long)h1 * W + w1) * C);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = lh0 * (lw0 * a.v[i] + lw1 * bq.v[i]) + lh1 * (lw0 * c.v[i] + lw1 * d.v[i]);
+    o.store(y + t * 8);
+  }
+}
+template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st) {
+  bilinear2x_fwd_kernel<T><<<GRID1D((long long)B * 4 * H * W * (C / 8), 256), 0, st>>>(x, y, B, H, W, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// gather form of the adjoint (deterministic, no atomics): dx[i] = sum_o w(o,i) dy[o]
+__device__ __forceinline__ float bil_w(int o, int i, int in_size, float scale) {
+  int i0, i1; float l0, l1;
+  bil_src(o, in_size, scale, i0, i1, l0, l1);
+  return (i0 == i ? l0 : 0.f) + (i1 == i ? l1 : 0.f);
+}
+__device__ __forceinline__ void bil_range(int i, int in_size, int& lo, int& hi) {
+  // outputs o with floor(o*s) in {i-1, i}: o in ((i-1)/s, (i+1)/s); s = (in-1)/(2in-1) ~ 0.5 => |o - 2i| <= 3
+  lo = max(0, 2 * i - 3);
+  hi = min(2 * in_size - 1, 2 * i + 3);
+}
+template <typename T> __global__ void bilinear2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
+  const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
+  const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
+  const long long n = (long long)B * H * W * c8;
+  FOR_GRID(t, n) {
+    const int g = (int)(t % c8);
+    long long r = t / c8;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    int hlo, hhi, wlo, whi;
+    bil_range(h, H, hlo, hhi);
+    bil_range(w, W, wlo, whi);
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    const T* base = dy + (long long)b * Ho * Wo * C + g * 8;
+    for (int oh = hlo; oh <= hhi; ++oh) {
+      const float wh = bil_w(oh, h, H, sh);
+      if (wh == 0.f) continue;
+      for (int ow = wlo; ow <= whi; ++ow) {
+        const float ww = bil_w(ow, w, W, sw);
+        if (ww == 0.f) continue;
+        Vec8<T> v;
+        v.load(base + ((long long)oh * Wo + ow) * C);
+        const float f = wh * ww;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += f * v.v[i];
+      }
+    }
+    Vec8<T> o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+    o.store(dx + t * 8);
+  }
+}
+template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int W, int C, cudaStream_t st) {
+  bilinear2x_bwd_kernel<T><<<GRID1D((long long)B * H * W * (C / 8), 256), 0, st>>>(dy, dx, B, H, W, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+__global__ void bilinear2x_f32_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int B, int H, int W) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
+  const long long n = (long long)B * Ho * Wo;
+  FOR_GRID(t, n) {
+    const int ow = (int)(t % Wo), oh = (int)((t / Wo) % Ho), b = (int)(t / ((long long)Wo * Ho));
+    int h0, h1, w0, w1; float lh0, lh1, lw0, lw1;
+    bil_src(oh, H, sh, h0, h1, lh0, lh1);
+    bil_src(ow, W, sw, w0, w1, lw0, lw1);
+    const float* p = x + (long long)b * H * W;
+    y[t] = lh0 * (lw0 * p[h0 * W + w0] + lw1 * p[h0 * W + w1]) + lh1 * (lw0 * p[h1 * W + w0] + lw1 * p[h1 * W + w1]);
+  }
+}
+int k_bilinear2x_f32_fwd(const float* x, float* y, int B, int H, int W, cudaStream_t st) {
+  bilinear2x_f32_fwd_kernel<<<GRID1D((long long)B * 4 * H * W, 256), 0, st>>>(x, y, B, H, W);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+__global__ void bilinear2x_f32_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int B, int H, int W) {
+  const int Ho = 2 * H, Wo = 2 * W;
+  const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
+  const long long n = (long long)B * H * W;
+  FOR_GRID(t, n) {
+    const int w = (int)(t % W), h = (int)((t / W) % H), b = (int)(t / ((long long)W * H));
+    int hlo, hhi, wlo, whi;
+    bil_range(h, H, hlo, hhi);
+    bil_range(w, W, wlo, whi);
+    float acc = 0.f;
+    const float* p = dy + (long long)b * Ho * Wo;
+    for (int oh = hlo; oh <= hhi; ++oh) {
+      const float wh = bil_w(oh, h, H, sh);
+      if (wh == 0.f) continue;
+      for (int ow = wlo; ow <= whi; ++ow) acc += wh * bil_w(ow, w, W, sw) * p[oh * Wo + ow];
+    }
+    dx[t] = acc;
+  }
+}
+int k_bilinear2x_f32_bwd(const float* dy, float* dx, int B, int H, int W, cudaStream_t st) {
+  bilinear2x_f32_bwd_kernel<<<GRID1D((long long)B * H * W, 256), 0, st>>>(dy, dx, B, H, W);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ BatchNorm2d (train)
+// nn.BatchNorm2d(256) eps 1e-5 momentum 0.1 (Models/DPT_decoder.py:204-206,492). x is [M, C] NHWC, C <= 256.
+// Block = 256 threads = (C/8) channel groups x (2048/C) row lanes.
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(256) bn_reduce_kernel(const T* __restrict__ a, const T* __restrict__ x,
+                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                        double* __restrict__ sums, int relu, long long M, int C,
+                                                        long long rows_per_block) {
+  // FWD: a = x, sums = {sum x, sum x^2}.  BWD: a = dy, sums = {sum dy', sum dy' * xhat}
+  extern __shared__ float sm[];  // [2][lanes][C]
+  const int c8 = C / 8, lanes = 256 / c8;
+  const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
+  const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float s1[8], s2[8], mu[8], rs[8], gm[8], bt[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    s1[i] = 0.f; s2[i] = 0.f;
+    if (BWD) { mu[i] = mean[g * 8 + i]; rs[i] = rstd[g * 8 + i]; gm[i] = gamma[g * 8 + i]; bt[i] = beta[g * 8 + i]; }
+  }
+  for (long long r = r0 + rl; r < r1; r += lanes) {
+    Vec8<T> v;
+    v.load(a + r * C + g * 8);
+    if (BWD) {
+      Vec8<T> xv;
+      xv.load(x + r * C + g * 8);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float xh = (xv.v[i] - mu[i]) * rs[i];
+        float d = v.v[i];
+        if (relu && xh * gm[i] + bt[i] <= 0.f) d = 0.f;
+        s1[i] += d; s2[i] += d * xh;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { s1[i] += v.v[i]; s2[i] += v.v[i] * v.v[i]; }
+    }
+  }
+  float* p1 = sm + (size_t)rl * C + g * 8;
+  float* p2 = sm + (size_t)(lanes + rl) * C + g * 8;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { p1[i] = s1[i]; p2[i] = s2[i]; }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * C; c += 256) {
+    const int which = c / C, ch = c % C;
+    double s = 0.0;
+    for (int l = 0; l < lanes; ++l) s += (double)sm[(size_t)(which * lanes + l) * C + ch];
+    atomicAdd(&sums[which * C + ch], s);
+  }
+}
+static inline long long bn_rows_per_block(long long M) { return max((long long)32, (M + 148 * 4 - 1) / (148 * 4)); }
+template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st) {
+  if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
+  const long long rpb = bn_rows_per_block(M);
+  bn_reduce_kernel<T, false><<<cdiv(M, rpb), 256, 2 * 2048 * sizeof(float), st>>>(x, nullptr, nullptr, nullptr, nullptr, nullptr, stats, 0, M, C, rpb);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T>
+int k_bn_bwd_reduce(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma,
+                    const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st) {
+  if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
+  const long long rpb = bn_rows_per_block(M);
+  bn_reduce_kernel<T, true><<<cdiv(M, rpb), 256, 2 * 2048 * sizeof(float), st>>>(dy, x, mean, rstd, gamma, beta, sums, relu, M, C, rpb);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, double count, float* mean, float* rstd,
+                                   float* running_mean, float* running_var, long long* nbt, float momentum, float eps, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double mu = stats[c] / count;
+  double var = stats[C + c] / count - mu * mu;
+  var = var < 0.0 ? 0.0 : var;
+  mean[c] = (float)mu;
+  rstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+  if (running_mean) {
+    const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mu;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    if (c == 0 && nbt) *nbt += 1;
+  }
+}
+int k_bn_finalize(const double* stats, double count, float* mean, float* rstd, float* running_mean, float* running_var,
+                  long long* nbt, float momentum, float eps, int C, cudaStream_t st) {
+  bn_finalize_kernel<<<cdiv(C, 256), 256, 0, st>>>(stats, count, mean, rstd, running_mean, running_var, nbt, momentum, eps, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+__global__ void bn_eval_prepare_kernel(const float* rm, const float* rv, float* mean, float* rstd, float eps, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) { mean[c] = rm[c]; rstd[c] = rsqrtf(rv[c] + eps); }
+}
+int k_bn_eval_prepare(const float* rm, const float* rv, float* mean, float* rstd, float eps, int C, cudaStream_t st) {
+  bn_eval_prepare_kernel<<<cdiv(C, 256), 256, 0, st>>>(rm, rv, mean, rstd, eps, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T>
+__global__ void bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
+                                const float* __restrict__ gamma, const float* __restrict__ beta, const T* __restrict__ skip,
+                                T* __restrict__ y, int relu, long long n8, int C) {
+  const int c8 = C / 8;
+  FOR_GRID(t, n8) {
+    const int g = (int)(t % c8);
+    Vec8<T> v, s;
+    v.load(x + t * 8);
+    if (skip) s.load(skip + t * 8);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = g * 8 + i;
+      float o = (v.v[i] - mean[c]) * rstd[c] * gamma[c] + beta[c];
+      if (relu) o = fmaxf(o, 0.f);
+      if (skip) o += s.v[i];
+      v.v[i] = o;
+    }
+    v.store(y + t * 8);
+  }
+}
+template <typename T>
+int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta, const T* skip,
+               T* y, int relu, long long M, int C, cudaStream_t st) {
+  bn_apply_kernel<T><<<GRID1D(M * C / 8, 256), 0, st>>>(x, mean, rstd, gamma, beta, skip, y, relu, M * C / 8, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// dx = gamma*rstd*(dy' - sum1/count - xhat*sum2/count); block 0 also writes dgamma = sum2, dbeta = sum1
+template <typename T>
+__global__ void bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean,
+                                    const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                    const float* __restrict__ beta, const double* __restrict__ sums, double count,
+                                    T* __restrict__ dx, float* dgamma, float* dbeta, int relu, long long n8, int C) {
+  const int c8 = C / 8;
+  if (blockIdx.x == 0 && dgamma)
+    for (int c = threadIdx.x; c < C; c += blockDim.x) { dbeta[c] = (float)sums[c]; dgamma[c] = (float)sums[C + c]; }
+  const float inv = (float)(1.0 / count);
+  FOR_GRID(t, n8) {
+    const int g = (int)(t % c8);
+    Vec8<T> d, xv;
+    d.load(dy + t * 8); xv.load(x + t * 8);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = g * 8 + i;
+      const float xh = (xv.v[i] - mean[c]) * rstd[c];
+      float dd = d.v[i];
+      if (relu && xh * gamma[c] + beta[c] <= 0.f) dd = 0.f;
+      d.v[i] = gamma[c] * rstd[c] * (dd - (float)sums[c] * inv - xh * (float)sums[C + c] * inv);
+    }
+    d.store(dx + t * 8);
+  }
+}
+template <typename T>
+int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                   const double* sums, double count, T* dx, float* dgamma, float* dbeta, int relu, long long M, int C,
+                   cudaStream_t st) {
+  bn_bwd_apply_kernel<T><<<GRID1D(M * C / 8, 256), 0, st>>>(dy, x, mean, rstd, gamma, beta, sums, count, dx, dgamma, dbeta, relu, M * C / 8, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ seg head tail
+// output_conv[1..4] (Models/DPT_decoder.py:492-495): BN -> ReLU -> Dropout(0.1) -> Conv1x1(256->1).
+// One warp per pixel row (C = 256 = 32 lanes x 8 channels).
+__device__ __forceinline__ float drop_scale(const uint8_t* mask, float p, uint64_t seed, long long idx) {
+  if (mask) return mask[idx] ? 1.f / (1.f - p) : 0.f;
+  if (p <= 0.f) return 1.f;
+  return dropout_keep(seed, (uint64_t)idx, p) ? 1.f / (1.f - p) : 0.f;
+}
+template <typename T>
+__global__ void __launch_bounds__(256) seghead_fwd_kernel(const T* __restrict__ x, const float* __restrict__ mean,
+                                                          const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, const float* __restrict__ w,
+                                                          const float* __restrict__ b, const uint8_t* __restrict__ mask,
+                                                          float p, uint64_t seed, float* __restrict__ small, long long M) {
+  const int lane = threadIdx.x & 31;
+  float mu[8], sc[8], bt[8], wv[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane * 8 + i;
+    mu[i] = mean[c]; sc[i] = rstd[c] * gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
+  }
+  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * 8) {
+    Vec8<T> v;
+    v.load(x + row * 256 + lane * 8);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float y = fmaxf((v.v[i] - mu[i]) * sc[i] + bt[i], 0.f);
+      s += y * drop_scale(mask, p, seed, row * 256 + lane * 8 + i) * wv[i];
+    }
+    s = warp_sum(s);
+    if (lane == 0) small[row] = s + b[0];
+  }
+}
+template <typename T>
+int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                  const float* w, const float* b, const uint8_t* mask, float p, uint64_t seed, float* small,
+                  long long M, int C, cudaStream_t st) {
+  if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
+  seghead_fwd_kernel<T><<<(unsigned)min((long long)cdiv(M, 8), (long long)148 * 16), 256, 0, st>>>(x, mean, rstd, gamma, beta, w, b, mask, p, seed, small, M);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// pass 1: per-channel sums {sum dy', sum dy'*xhat} (double), dw[c] = sum dsmall * z, db = sum dsmall
+template <typename T>
+__global__ void __launch_bounds__(256) seghead_bwd_reduce_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
+                                                                 const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                 const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                 const float* __restrict__ w, const uint8_t* __restrict__ mask,
+                                                                 float p, uint64_t seed, double* __restrict__ sums,
+                                                                 float* __restrict__ dw, float* __restrict__ db, long long M) {
+  __shared__ float sm[3][8][256];
+  __shared__ float sdb[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float mu[8], rs[8], gm[8], bt[8], wv[8], s1[8], s2[8], s3[8];
+  float sd = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane * 8 + i;
+    mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
+    s1[i] = s2[i] = s3[i] = 0.f;
+  }
+  for (long long row = (long long)blockIdx.x * 8 + warp; row < M; row += (long long)gridDim.x * 8) {
+    Vec8<T> v;
+    v.load(x + row * 256 + lane * 8);
+    const float ds = dsmall[row];
+    sd += ds;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xh = (v.v[i] - mu[i]) * rs[i];
+      const float y = xh * gm[i] + bt[i];
+      const float k = drop_scale(mask, p, seed, row * 256 + lane * 8 + i);
+      const float z = fmaxf(y, 0.f) * k;
+      const float dy = y > 0.f ? ds * wv[i] * k : 0.f;
+      s1[i] += dy; s2[i] += dy * xh; s3[i] += ds * z;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { sm[0][warp][lane * 8 + i] = s1[i]; sm[1][warp][lane * 8 + i] = s2[i]; sm[2][warp][lane * 8 + i] = s3[i]; }
+  if (lane == 0) sdb[warp] = sd;
+  __syncthreads();
+  const int c = threadIdx.x;
+  double a = 0.0, bq = 0.0; float cw = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { a += sm[0][k][c]; bq += sm[1][k][c]; cw += sm[2][k][c]; }
+  atomicAdd(&sums[c], a); atomicAdd(&sums[256 + c], bq); atomicAdd(&dw[c], cw);
+  if (c == 0) { float t = 0.f; for (int k = 0; k < 8; ++k) t += sdb[k]; atomicAdd(db, t); }
+}
+template <typename T>
+int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
+                         const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
+                         float* dw, float* db, long long M, int C, cudaStream_t st) {
+  if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
+  seghead_bwd_reduce_kernel<T><<<(unsigned)min((long long)cdiv(M, 8), (long long)148 * 4), 256, 0, st>>>(dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, dw, db, M);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T>
+__global__ void __launch_bounds__(256) seghead_bwd_apply_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
+                                                                const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                const float* __restrict__ w, const uint8_t* __restrict__ mask,
+                                                                float p, uint64_t seed, const double* __restrict__ sums,
+                                                                double count, T* __restrict__ dx, float* dgamma, float* dbeta,
+                                                                long long M) {
+  const int lane = threadIdx.x & 31;
+  if (blockIdx.x == 0) { dbeta[threadIdx.x] = (float)sums[threadIdx.x]; dgamma[threadIdx.x] = (float)sums[256 + threadIdx.x]; }
+  const float inv = (float)(1.0 / count);
+  float mu[8], rs[8], gm[8], bt[8], wv[8], m1[8], m2[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = lane * 8 + i;
+    mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
+    m1[i] = (float)sums[c] * inv; m2[i] = (float)sums[256 + c] * inv;
+  }
+  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * 8) {
+    Vec8<T> v;
+    v.load(x + row * 256 + lane * 8);
+    const float ds = dsmall[row];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xh = (v.v[i] - mu[i]) * rs[i];
+      const float y = xh * gm[i] + bt[i];
+      const float dy = y > 0.f ? ds * wv[i] * drop_scale(mask, p, seed, row * 256 + lane * 8 + i) : 0.f;
+      v.v[i] = gm[i] * rs[i] * (dy - m1[i] - xh * m2[i]);
+    }
+    v.store(dx + row * 256 + lane * 8);
+  }
+}
+template <typename T>
+int k_seghead_bwd_apply(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
+                        const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed,
+                        const double* sums, double count, T* dx, float* dgamma, float* dbeta, long long M, int C,
+                        cudaStream_t st) {
+  if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
+  seghead_bwd_apply_kernel<T><<<(unsigned)min((long long)cdiv(M, 8), (long long)148 * 16), 256, 0, st>>>(dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, count, dx, dgamma, dbeta, M);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ depth head tail
+// output_conv[4..5] (Models/DPT_decoder.py:480-481): Conv1x1(32->1) + Sigmoid on the ReLU'd 32-ch map
+template <typename T>
+__global__ void depthhead_fwd_kernel(const T* __restrict__ h, const float* __restrict__ w, const float* __restrict__ b,
+                                     float* __restrict__ out, long long M, int C) {
+  FOR_GRID(row, M) {
+    float s = b[0];
+    for (int c = 0; c < C; c += 8) {
+      Vec8<T> v;
+      v.load(h + row * C + c);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += v.v[i] * w[c + i];
+    }
+    out[row] = 1.f / (1.f + __expf(-s));
+  }
+}
+template <typename T>
+int k_depthhead_fwd(const T* h, const float* w, const float* b, float* out, long long M, int C, cudaStream_t st) {
+  depthhead_fwd_kernel<T><<<GRID1D(M, 256), 0, st>>>(h, w, b, out, M, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+template <typename T>
+__global__ void __launch_bounds__(256) depthhead_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ out,
+                                                            const T* __restrict__ h, const float* __restrict__ w,
+                                                            T* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db,
+                                                            long long M, int C) {
+  __shared__ float sdw[64];
+  __shared__ float sdb;
+  if (threadIdx.x < 64) sdw[threadIdx.x] = 0.f;
+  if (threadIdx.x == 0) sdb = 0.f;
+  __syncthreads();
+  float lw[32], ldb = 0.f;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) lw[i] = 0.f;
+  FOR_GRID(row, M) {
+    const float o = out[row];
+    const float ds = dout[row] * o * (1.f - o);
+    ldb += ds;
+#pragma unroll
+    for (int c = 0; c < 32; c += 8) {
+      Vec8<T> v, d;
+      v.load(h + row * 32 + c);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { lw[c + i] += ds * v.v[i]; d.v[i] = ds * w[c + i]; }
+      d.store(dh + row * 32 + c);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 32; ++i) { const float s = warp_sum(lw[i]); if ((threadIdx.x & 31) == 0) atomicAdd(&sdw[i], s); }
+  ldb = warp_sum(ldb);
+  if ((threadIdx.x & 31) == 0) atomicAdd(&sdb, ldb);
+  __syncthreads();
+  if (threadIdx.x < C) atomicAdd(&dw[threadIdx.x], sdw[threadIdx.x]);
+  if (threadIdx.x == 0) atomicAdd(db, sdb);
+}
+template <typename T>
+int k_depthhead_bwd(const float* dout, const float* out, const T* h, const float* w, T* dh, float* dw, float* db,
+                    long long M, int C, cudaStream_t st) {
+  if (C != 32) { s4g_set_error("depthhead: C must be 32"); return S4G_ERR_SHAPE; }
+  depthhead_bwd_kernel<T><<<148 * 4, 256, 0, st>>>(dout, out, h, w, dh, dw, db, M, C);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ weight packing
+template <typename T> __global__ void pack_linear_kernel(const float* __restrict__ w, T* __restrict__ wp, T* __restrict__ wt, int N, int K) {
+  __shared__ float tile[32][33];
+  const int k = blockIdx.x * 32 + threadIdx.x, n0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int n = n0 + j;
+    float v = 0.f;
+    if (n < N && k < K) { v = w[(long long)n * K + k]; wp[(long long)n * K + k] = from_f<T>(v); }
+    tile[j][threadIdx.x] = v;
+  }
+  __syncthreads();
+  if (!wt) return;
+  const int n = n0 + threadIdx.x;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int kk = blockIdx.x * 32 + j;
+    if (n < N && kk < K) wt[(long long)kk * N + n] = from_f<T>(tile[threadIdx.x][j]);
+  }
+}
+template <typename T> int k_pack_linear(const float* w, T* wp, T* wt, int N, int K, cudaStream_t st) {
+  pack_linear_kernel<T><<<dim3(cdiv(K, 32), cdiv(N, 32)), dim3(32, 8), 0, st>>>(w, wp, wt, N, K);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// conv weight [Co][Ci][R][R] -> fprop wf[Co][tap][Ci]; dgrad wd[Ci][tap'][Co] with tap' = flipped tap
+template <typename T> __global__ void pack_conv_kernel(const float* __restrict__ w, T* __restrict__ wf, T* __restrict__ wd, int Co, int Ci, int R) {
+  const int taps = R * R;
+  const long long n = (long long)Co * Ci * taps;
+  FOR_GRID(t, n) {
+    const int tap = (int)(t % taps);
+    const int ci = (int)((t / taps) % Ci), co = (int)(t / ((long long)taps * Ci));
+    const float v = w[t];
+    wf[((long long)co * taps + tap) * Ci + ci] = from_f<T>(v);
+    if (wd) wd[((long long)ci * taps + (taps - 1 - tap)) * Co + co] = from_f<T>(v);
+  }
+}
+template <typename T> int k_pack_conv(const float* w, T* wf, T* wd, int Co, int Ci, int R, cudaStream_t st) {
+  pack_conv_kernel<T><<<GRID1D((long long)Co * Ci * R * R, 256), 0, st>>>(w, wf, wd, Co, Ci, R);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// ConvTranspose weight [Ci][Co][k][k] -> fprop B operand wf[(kh,kw,co)][ci]; dgrad B operand wd[ci][(kh,kw,co)]
+template <typename T> __global__ void pack_convT_kernel(const float* __restrict__ w, T* __restrict__ wf, T* __restrict__ wd, int Ci, int Co, int k) {
+  const int kk = k * k;
+  const long long n = (long long)Ci * Co * kk;
+  FOR_GRID(t, n) {
+    const int tap = (int)(t % kk);
+    const int co = (int)((t / kk) % Co), ci = (int)(t / ((long long)kk * Co));
+    const float v = w[t];
+    const long long col = (long long)tap * Co + co;
+    wf[col * Ci + ci] = from_f<T>(v);
+    wd[(long long)ci * kk * Co + col] = from_f<T>(v);
+  }
+}
+template <typename T> int k_pack_convT(const float* w, T* wf, T* wd, int Ci, int Co, int k, cudaStream_t st) {
+  pack_convT_kernel<T><<<GRID1D((long long)Ci * Co * k * k, 256), 0, st>>>(w, wf, wd, Ci, Co, k);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+__global__ void unpack_conv_grad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int Co, int Ci, int R) {
+  const int taps = R * R;
+  const long long n = (long long)Co * Ci * taps;
+  FOR_GRID(t, n) {
+    const int tap = (int)(t % taps);
+    const int ci = (int)((t / taps) % Ci), co = (int)(t / ((long long)taps * Ci));
+    dw[t] = dwp[((long long)co * taps + tap) * Ci + ci];
+  }
+}
+int k_unpack_conv_grad(const float* dwp, float* dw, int Co, int Ci, int R, cudaStream_t st) {
+  unpack_conv_grad_kernel<<<GRID1D((long long)Co * Ci * R * R, 256), 0, st>>>(dwp, dw, Co, Ci, R);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+__global__ void unpack_convT_grad_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int Ci, int Co, int k) {
+  const int kk = k * k;
+  const long long n = (long long)Ci * Co * kk;
+  FOR_GRID(t, n) {
+    const int tap = (int)(t % kk);
+    const int co = (int)((t / kk) % Co), ci = (int)(t / ((long long)kk * Co));
+    dw[t] = dwp[((long long)tap * Co + co) * Ci + ci];
+  }
+}
+int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cudaStream_t st) {
+  unpack_convT_grad_kernel<<<GRID1D((long long)Ci * Co * k * k, 256), 0, st>>>(dwp, dw, Ci, Co, k);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ instantiation
+#define INST(T)                                                                                                        \
+  template int k_patchify<T>(const float*, T*, int, cudaStream_t);                                                     \
+  template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
+  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t); \
+  template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t);                                        \
+  template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t);                                       \
+  template int k_tokens_to_nhwc<T>(const float*, T*, int, cudaStream_t);                                               \
+  template int k_tap_grad<T>(const T*, float*, int, int, cudaStream_t);                                                \
+  template int k_cast_f32<T>(const float*, T*, long long, cudaStream_t);                                               \
+  template int k_relu<T>(const T*, T*, long long, cudaStream_t);                                                       \
+  template int k_relu_bwd_add<T>(const T*, const T*, const T*, T*, long long, cudaStream_t);                           \
+  template int k_add<T>(const T*, const T*, T*, long long, cudaStream_t);                                              \
+  template int k_pixel_shuffle<T>(const T*, const float*, T*, int, int, int, int, int, cudaStream_t);                  \
+  template int k_pixel_unshuffle<T>(const T*, T*, int, int, int, int, int, cudaStream_t);                              \
+  template int k_im2col_s2<T>(const T*, T*, int, int, int, int, cudaStream_t);                                         \
+  template int k_col2im_s2<T>(const T*, T*, int, int, int, int, cudaStream_t);                                         \
+  template int k_bilinear2x_fwd<T>(const T*, T*, int, int, int, int, cudaStream_t);                                    \
+  template int k_bilinear2x_bwd<T>(const T*, T*, int, int, int, int, cudaStream_t);                                    \
+  template int k_bn_stats<T>(const T*, double*, long long, int, cudaStream_t);                                         \
+  template int k_bn_apply<T>(const T*, const float*, const float*, const float*, const float*, const T*, T*, int, long long, int, cudaStream_t); \
+  template int k_bn_bwd_reduce<T>(const T*, const T*, const float*, const float*, const float*, const float*, double*, int, long long, int, cudaStream_t); \
+  template int k_bn_bwd_apply<T>(const T*, const T*, const float*, const float*, const float*, const float*, const double*, double, T*, float*, float*, int, long long, int, cudaStream_t); \
+  template int k_seghead_fwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, float*, long long, int, cudaStream_t); \
+  template int k_seghead_bwd_reduce<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, double*, float*, float*, long long, int, cudaStream_t); \
+  template int k_seghead_bwd_apply<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, const double*, double, T*, float*, float*, long long, int, cudaStream_t); \
+  template int k_depthhead_fwd<T>(const T*, const float*, const float*, float*, long long, int, cudaStream_t);         \
+  template int k_depthhead_bwd<T>(const float*, const float*, const T*, const float*, T*, float*, float*, long long, int, cudaStream_t); \
+  template int k_pack_linear<T>(const float*, T*, T*, int, int, cudaStream_t);                                         \
+  template int k_pack_conv<T>(const float*, T*, T*, int, int, int, cudaStream_t);                                      \
+  template int k_pack_convT<T>(const float*, T*, T*, int, int, int, cudaStream_t);
+INST(float)
+INST(bf16)

@@ -1,0 +1,845 @@
+// Static forward/backward schedule of ViT-B/16 (+ DPT decoder | classification head).
+//
+// The schedule is built once per (batch, dense, dtype, backend): every activation gets a fixed offset in one
+// caller-owned workspace, every op becomes a closure that enqueues kernels on the caller's stream, and
+// backward is the reverse list of the closures pushed alongside.  No allocation, no host sync, no autograd
+// graph walk at run time => the whole step is CUDA-graph capturable.
+//
+// Reference semantics followed (paths relative to the reference repo):
+//   encoder   Models/models.py:325-338 (== :427-456, :545-558) + timm 0.6.12 Block/Attention/Mlp
+//   decoder   Models/DPT_decoder.py:501-539, RCU :212-233, fusion :281-301, heads :469-497
+#include <functional>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+namespace {
+
+struct Param {
+  float* p = nullptr;
+  float* g = nullptr;
+  long long n = 0;
+};
+
+struct Act {  // NHWC activation (or [rows, C] matrix with H = W = 1)
+  size_t v = 0, g = 0;
+  int B = 0, H = 0, W = 0, C = 0;
+  long long rows() const { return (long long)B * H * W; }
+  long long numel() const { return rows() * C; }
+};
+
+typedef std::function<int(cudaStream_t)> Op;
+
+}  // namespace
+
+struct S4GModel {
+  S4GModelDesc d;
+  std::map<std::string, Param> params;
+  char* ws = nullptr;
+  size_t ws_bytes = 0, ws_need = 0;
+  bool built = false;
+  std::vector<Op> pack, fwd, bwd_dec, bwd_enc;  // bwd lists are stored in forward order and run reversed
+  std::vector<Act> acts;
+  std::vector<std::pair<int, std::string>> bucket_of;  // (bwd position class, param name)
+  void* grad_arena = nullptr;
+  size_t grad_arena_bytes = 0;
+  s4g_allreduce_fn allreduce = nullptr;
+  void* allreduce_user = nullptr;
+  std::vector<cudaEvent_t> events;
+  std::string bucket_str;
+  int launches = 0;
+  // per-call state read by closures
+  const float* images = nullptr;
+  float* out = nullptr;
+  const float* dout = nullptr;
+  int training = 1;
+  uint64_t seed = 0;
+  const uint8_t* dropout_mask = nullptr;
+  std::vector<std::string> enc_param_order;  // names in backward completion order (for buckets)
+  std::vector<std::string> dec_param_names;
+  std::vector<size_t> enc_block_mark;         // bwd_enc index at which block i's grads are complete
+
+  template <typename U> U* at(size_t off) const { return reinterpret_cast<U*>(ws + off); }
+};
+
+namespace {
+
+template <typename T>
+struct Builder {
+  S4GModel* m;
+  size_t top = 0;
+  const int B;
+  const bool tensor;  // tcgen05 / tensor-core kernels
+  size_t dwp_scratch = 0, dwp_bytes = 0;      // packed weight-gradient staging
+  size_t wg_scratch = 0, wg_bytes = 0;        // split-K partials for the tcgen05 wgrad
+  std::vector<Op>* bwd;                        // current backward list
+
+  explicit Builder(S4GModel* mm) : m(mm), B(mm->d.batch), tensor(mm->d.backend == S4G_BACKEND_TENSOR) {}
+
+  size_t alloc(size_t bytes) {
+    size_t o = (top + 255) & ~(size_t)255;
+    top = o + bytes;
+    return o;
+  }
+  int act(int Bn, int H, int W, int C, bool grad = true) {
+    Act a;
+    a.B = Bn; a.H = H; a.W = W; a.C = C;
+    a.v = alloc(sizeof(T) * a.numel());
+    if (grad) a.g = alloc(sizeof(T) * a.numel());
+    m->acts.push_back(a);
+    return (int)m->acts.size() - 1;
+  }
+  Param* P(const std::string& name) {
+    auto it = m->params.find(name);
+    if (it == m->params.end()) { missing.push_back(name); static Param dummy; return &dummy; }
+    return &it->second;
+  }
+  Param* Popt(const std::string& name) {
+    auto it = m->params.find(name);
+    return it == m->params.end() ? nullptr : &it->second;
+  }
+  std::vector<std::string> missing;
+  T* V(int a) const { return m->template at<T>(m->acts[a].v); }
+  T* G(int a) const { return m->template at<T>(m->acts[a].g); }
+
+  // ---- contraction dispatch -----------------------------------------------------------------------------
+  int fprop(const ConvGeom& g, const T* X, const T* W, const EpiParams& e, cudaStream_t st) const {
+    m->launches++;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (tensor) return umma_conv_fprop(g, X, W, e, st);
+    }
+    return simt_conv_fprop<T>(g, X, W, e, st);
+  }
+  int wgrad(const ConvGeom& g, const T* dY, const T* X, float* dW, cudaStream_t st) const {
+    m->launches++;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (tensor) return umma_conv_wgrad(g, dY, X, dW, m->template at<float>(wg_scratch), wg_bytes, st);
+    }
+    return simt_conv_wgrad<T>(g, dY, X, dW, st);
+  }
+  static EpiParams epi(void* out, int ldo, const float* bias = nullptr, int mode = EPI_NONE, int out_f32 = 0) {
+    EpiParams e{};
+    e.bias = bias; e.out = out; e.ldo = ldo; e.mode = mode; e.out_f32 = out_f32; e.alpha = 1.f;
+    return e;
+  }
+
+  // ---- linear layers (nn.Linear and 1x1 Conv2d share the [N,K] weight layout) ------------------------------
+  struct Lin { Param* w; Param* b; size_t wf, wd; int N, K; };
+  Lin linear(const std::string& name, int N, int K, bool dgrad = true) {
+    Lin l{P(name + ".weight"), Popt(name + ".bias"), 0, 0, N, K};
+    l.wf = alloc(sizeof(T) * (size_t)N * K);
+    l.wd = dgrad ? alloc(sizeof(T) * (size_t)N * K) : 0;
+    S4GModel* mm = m;
+    m->pack.push_back([mm, l, dgrad](cudaStream_t st) {
+      mm->launches++;
+      return k_pack_linear<T>(l.w->p, mm->template at<T>(l.wf), dgrad ? mm->template at<T>(l.wd) : nullptr, l.N, l.K, st);
+    });
+    return l;
+  }
+  // dW, db of a linear layer given dY [M,N], X [M,K]
+  int linear_param_grads(const Lin& l, const T* dY, const T* X, long long M, cudaStream_t st) const {
+    if (l.w->g) S4G_TRY(wgrad(linear_geom(M, l.N, l.K), dY, X, l.w->g, st));
+    if (l.b && l.b->g) {
+      S4G_CUDA(cudaMemsetAsync(l.b->g, 0, sizeof(float) * l.N, st));
+      m->launches++;
+      S4G_TRY(k_colsum<T>(dY, l.b->g, M, l.N, l.N, st));
+    }
+    return 0;
+  }
+
+  // ---- 3x3 convolutions --------------------------------------------------------------------------------------
+  struct Conv { Param* w; Param* b; size_t wf, wd; int Co, Ci; };
+  Conv conv3(const std::string& name, int Co, int Ci) {
+    Conv c{P(name + ".weight"), Popt(name + ".bias"), 0, 0, Co, Ci};
+    c.wf = alloc(sizeof(T) * (size_t)Co * Ci * 9);
+    c.wd = alloc(sizeof(T) * (size_t)Co * Ci * 9);
+    dwp_bytes = std::max(dwp_bytes, sizeof(float) * (size_t)Co * Ci * 9);
+    S4GModel* mm = m;
+    m->pack.push_back([mm, c](cudaStream_t st) {
+      mm->launches++;
+      return k_pack_conv<T>(c.w->p, mm->template at<T>(c.wf), mm->template at<T>(c.wd), c.Co, c.Ci, 3, st);
+    });
+    return c;
+  }
+  // out = conv3x3(in) (+bias) (epilogue mode); pushes forward and backward closures
+  void conv3_layer(const Conv& c, int in, int out, int mode = EPI_NONE, bool in_grad = true) {
+    Builder* self = this;
+    S4GModel* mm = m;
+    const Act ai = m->acts[in];
+    note_wgrad(conv3_geom(ai.B, ai.H, ai.W, c.Ci, c.Co));
+    m->fwd.push_back([=](cudaStream_t st) {
+      const Act& a = mm->acts[in];
+      EpiParams e = epi(self->V(out), c.Co, c.b ? c.b->p : nullptr, mode);
+      return self->fprop(conv3_geom(a.B, a.H, a.W, c.Ci, c.Co), self->V(in), mm->template at<T>(c.wf), e, st);
+    });
+    bwd->push_back([=](cudaStream_t st) {
+      const Act& a = mm->acts[in];
+      const ConvGeom g = conv3_geom(a.B, a.H, a.W, c.Ci, c.Co);
+      if (in_grad) {
+        EpiParams e = epi(self->G(in), c.Ci);
+        S4G_TRY(self->fprop(conv3_geom(a.B, a.H, a.W, c.Co, c.Ci), self->G(out), mm->template at<T>(c.wd), e, st));
+      }
+      if (c.w->g) {
+        float* dwp = mm->template at<float>(self->dwp_scratch);
+        S4G_TRY(self->wgrad(g, self->G(out), self->V(in), dwp, st));
+        mm->launches++;
+        S4G_TRY(k_unpack_conv_grad(dwp, c.w->g, c.Co, c.Ci, 3, st));
+      }
+      if (c.b && c.b->g) {
+        S4G_CUDA(cudaMemsetAsync(c.b->g, 0, sizeof(float) * c.Co, st));
+        mm->launches++;
+        S4G_TRY(k_colsum<T>(self->G(out), c.b->g, a.rows(), c.Co, c.Co, st));
+      }
+      return 0;
+    });
+  }
+  void note_wgrad(const ConvGeom& g) {
+    if (std::is_same<T, bf16>::value && tensor) wg_bytes = std::max(wg_bytes, umma_wgrad_scratch_bytes(g));
+  }
+  // out = in . W^T + b  (1x1 conv / linear on an Act)
+  void lin_layer(const Lin& l, int in, int out, bool in_grad = true) {
+    Builder* self = this;
+    S4GModel* mm = m;
+    note_wgrad(linear_geom(m->acts[in].rows(), l.N, l.K));
+    m->fwd.push_back([=](cudaStream_t st) {
+      EpiParams e = epi(self->V(out), l.N, l.b ? l.b->p : nullptr);
+      return self->fprop(linear_geom(mm->acts[in].rows(), l.N, l.K), self->V(in), mm->template at<T>(l.wf), e, st);
+    });
+    bwd->push_back([=](cudaStream_t st) {
+      const long long M = mm->acts[in].rows();
+      if (in_grad) {
+        EpiParams e = epi(self->G(in), l.K);
+        S4G_TRY(self->fprop(linear_geom(M, l.K, l.N), self->G(out), mm->template at<T>(l.wd), e, st));
+      }
+      return self->linear_param_grads(l, self->G(out), self->V(in), M, st);
+    });
+  }
+
+  // ---- BatchNorm2d (train / eval) ----------------------------------------------------------------------------
+  struct BN { Param *w, *b, *rm, *rv, *nbt; size_t stats, sums, mean, rstd; };
+  BN bn(const std::string& name) {
+    BN n{P(name + ".weight"), P(name + ".bias"), P(name + ".running_mean"), P(name + ".running_var"),
+         P(name + ".num_batches_tracked"), 0, 0, 0, 0};
+    n.stats = alloc(sizeof(double) * 512);
+    n.sums = alloc(sizeof(double) * 512);
+    n.mean = alloc(sizeof(float) * 256);
+    n.rstd = alloc(sizeof(float) * 256);
+    return n;
+  }
+  // statistics of x (forward): fills mean/rstd, updates running stats when training
+  int bn_forward_stats(const BN& n, const T* x, long long M, cudaStream_t st) const {
+    float* mean = m->template at<float>(n.mean);
+    float* rstd = m->template at<float>(n.rstd);
+    if (!m->training) { m->launches++; return k_bn_eval_prepare(n.rm->p, n.rv->p, mean, rstd, 1e-5f, 256, st); }
+    double* stats = m->template at<double>(n.stats);
+    S4G_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 512, st));
+    m->launches += 2;
+    S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st));
+    if (m->d.world_size > 1) {
+      if (!m->allreduce) { s4g_set_error("SyncBatchNorm needs s4g_model_set_allreduce"); return S4G_ERR_STATE; }
+      S4G_TRY(m->allreduce(m->allreduce_user, stats, 512, st));
+    }
+    return k_bn_finalize(stats, (double)M * m->d.world_size, mean, rstd, n.rm->p, n.rv->p,
+                         reinterpret_cast<long long*>(n.nbt->p), 0.1f, 1e-5f, 256, st);
+  }
+  int bn_backward(const BN& n, const T* dy, const T* x, T* dx, int relu, long long M, cudaStream_t st) const {
+    double* sums = m->template at<double>(n.sums);
+    const float* mean = m->template at<float>(n.mean);
+    const float* rstd = m->template at<float>(n.rstd);
+    S4G_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 512, st));
+    m->launches += 2;
+    S4G_TRY(k_bn_bwd_reduce<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, relu, M, 256, st));
+    if (m->d.world_size > 1) S4G_TRY(m->allreduce(m->allreduce_user, sums, 512, st));
+    return k_bn_bwd_apply<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, (double)M * m->d.world_size, dx, n.w->g, n.b->g,
+                             relu, M, 256, st);
+  }
+
+  // ---- ResidualConvUnit_custom (Models/DPT_decoder.py:170-233) ------------------------------------------------
+  // returns the output act; x.g receives skip + ReLU-path gradient
+  int rcu(const std::string& p, int x, bool use_bn) {
+    const Act ax = m->acts[x];
+    Builder* self = this;
+    S4GModel* mm = m;
+    const long long M = ax.rows(), n = ax.numel();
+    const int r = act(ax.B, ax.H, ax.W, 256), c1 = act(ax.B, ax.H, ax.W, 256), r2 = act(ax.B, ax.H, ax.W, 256),
+              c2 = act(ax.B, ax.H, ax.W, 256), out = act(ax.B, ax.H, ax.W, 256);
+    Conv k1 = conv3(p + "conv1", 256, 256), k2 = conv3(p + "conv2", 256, 256);
+    BN b1{}, b2{};
+    if (use_bn) { b1 = bn(p + "bn1"); b2 = bn(p + "bn2"); }
+    // r = relu(x);  backward: x.g = out.g + (x > 0) * r.g
+    m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_relu<T>(self->V(x), self->V(r), n, st); });
+    bwd->push_back([=](cudaStream_t st) {
+      mm->launches++;
+      return k_relu_bwd_add<T>(self->G(r), self->V(x), self->G(out), self->G(x), n, st);
+    });
+    conv3_layer(k1, r, c1);
+    if (use_bn) {
+      m->fwd.push_back([=](cudaStream_t st) {
+        S4G_TRY(self->bn_forward_stats(b1, self->V(c1), M, st));
+        mm->launches++;
+        return k_bn_apply<T>(self->V(c1), mm->template at<float>(b1.mean), mm->template at<float>(b1.rstd), b1.w->p, b1.b->p,
+                             nullptr, self->V(r2), 1, M, 256, st);
+      });
+      bwd->push_back([=](cudaStream_t st) { return self->bn_backward(b1, self->G(r2), self->V(c1), self->G(c1), 1, M, st); });
+    } else {
+      m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_relu<T>(self->V(c1), self->V(r2), n, st); });
+      bwd->push_back([=](cudaStream_t st) {
+        mm->launches++;
+        return k_relu_bwd_add<T>(self->G(r2), self->V(c1), nullptr, self->G(c1), n, st);
+      });
+    }
+    conv3_layer(k2, r2, c2);
+    if (use_bn) {
+      m->fwd.push_back([=](cudaStream_t st) {
+        S4G_TRY(self->bn_forward_stats(b2, self->V(c2), M, st));
+        mm->launches++;
+        return k_bn_apply<T>(self->V(c2), mm->template at<float>(b2.mean), mm->template at<float>(b2.rstd), b2.w->p, b2.b->p,
+                             self->V(x), self->V(out), 0, M, 256, st);
+      });
+      bwd->push_back([=](cudaStream_t st) { return self->bn_backward(b2, self->G(out), self->V(c2), self->G(c2), 0, M, st); });
+    } else {
+      m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_add<T>(self->V(c2), self->V(x), self->V(out), n, st); });
+      // d(c2) == d(out); resolved at run time because fusion() may re-alias out.g after this unit is built
+      bwd->push_back([=](cudaStream_t) { mm->acts[c2].g = mm->acts[out].g; return 0; });
+    }
+    return out;
+  }
+
+  // ---- FeatureFusionBlock_custom (Models/DPT_decoder.py:238-301) ----------------------------------------------
+  int fusion(const std::string& p, int x0, int x1, bool use_bn) {
+    Builder* self = this;
+    S4GModel* mm = m;
+    int s = x0;
+    if (x1 >= 0) {
+      const int res = rcu(p + "resConfUnit1.", x1, use_bn);
+      const Act a = m->acts[x0];
+      s = act(a.B, a.H, a.W, 256);
+      const long long n = a.numel();
+      m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_add<T>(self->V(x0), self->V(res), self->V(s), n, st); });
+      bwd->push_back([](cudaStream_t) { return 0; });
+      m->acts[x0].g = m->acts[s].g;   // d(x0) == d(res) == d(s)
+      m->acts[res].g = m->acts[s].g;
+    }
+    const int t = rcu(p + "resConfUnit2.", s, use_bn);
+    const Act at = m->acts[t];
+    const int u = act(at.B, 2 * at.H, 2 * at.W, 256);
+    m->fwd.push_back([=](cudaStream_t st) {
+      const Act& a = mm->acts[t];
+      mm->launches++;
+      return k_bilinear2x_fwd<T>(self->V(t), self->V(u), a.B, a.H, a.W, 256, st);
+    });
+    bwd->push_back([=](cudaStream_t st) {
+      const Act& a = mm->acts[t];
+      mm->launches++;
+      return k_bilinear2x_bwd<T>(self->G(u), self->G(t), a.B, a.H, a.W, 256, st);
+    });
+    const int out = act(at.B, 2 * at.H, 2 * at.W, 256);
+    lin_layer(linear(p + "out_conv", 256, 256), u, out);
+    return out;
+  }
+
+  // ---- encoder -------------------------------------------------------------------------------------------------
+  struct Block {
+    Param *n1w, *n1b, *n2w, *n2b;
+    Lin qkv, proj, fc1, fc2;
+    size_t h1, mean1, rstd1, qkvb, ao, lse, h2, mean2, rstd2, u, a;
+  };
+  std::vector<size_t> xs;  // residual stream snapshots: xs[2i] = block i input, xs[2i+1] = after attention
+  std::vector<Block> blocks;
+  size_t patches = 0, pe = 0;
+  Lin pe_lin{};
+  size_t dxa = 0, dxb = 0, dxT = 0, dh = 0, du = 0, dao = 0, dqkv = 0;  // backward temporaries
+  int tap_act[4] = {-1, -1, -1, -1};
+
+  int attn_fwd(const T* qkv, T* o, float* lse, cudaStream_t st) const {
+    m->launches++;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (tensor) return attn_fwd_mma(qkv, o, lse, B, 197, 12, st);
+    }
+    return attn_fwd_simt<T>(qkv, o, lse, B, 197, 12, st);
+  }
+  int attn_bwd(const T* qkv, const T* o, const T* dout, const float* lse, T* dqkv_, cudaStream_t st) const {
+    m->launches++;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (tensor) return attn_bwd_mma(qkv, o, dout, lse, dqkv_, B, 197, 12, st);
+    }
+    return attn_bwd_simt<T>(qkv, o, dout, lse, dqkv_, B, 197, 12, st);
+  }
+
+  void build_encoder(bool dense) {
+    Builder* self = this;
+    S4GModel* mm = m;
+    const long long Tk = (long long)B * 197, Pn = (long long)B * 196;
+    const bool train_enc = !m->d.frozen;
+    patches = alloc(sizeof(T) * Pn * 768);
+    pe = alloc(sizeof(float) * Pn * 768);
+    pe_lin = linear("patch_embed.proj", 768, 768, false);
+    note_wgrad(linear_geom(Pn, 768, 768));
+    Param* cls = P("cls_token");
+    Param* pos = P("pos_embed");
+    xs.resize(25);
+    for (auto& x : xs) x = alloc(sizeof(float) * Tk * 768);
+    m->fwd.push_back([=](cudaStream_t st) {
+      mm->launches += 3;
+      S4G_TRY(k_patchify<T>(mm->images, mm->template at<T>(self->patches), self->B, st));
+      EpiParams e = epi(mm->template at<float>(self->pe), 768, self->pe_lin.b->p, EPI_NONE, 1);
+      S4G_TRY(self->fprop(linear_geom(Pn, 768, 768), mm->template at<T>(self->patches), mm->template at<T>(self->pe_lin.wf), e, st));
+      return k_assemble_tokens(mm->template at<float>(self->pe), cls->p, pos->p, mm->template at<float>(self->xs[0]), self->B, st);
+    });
+    for (int i = 0; i < 12; ++i) {
+      const std::string p = "blocks." + std::to_string(i) + ".";
+      Block b;
+      b.n1w = P(p + "norm1.weight"); b.n1b = P(p + "norm1.bias");
+      b.n2w = P(p + "norm2.weight"); b.n2b = P(p + "norm2.bias");
+      b.qkv = linear(p + "attn.qkv", 2304, 768, train_enc);
+      b.proj = linear(p + "attn.proj", 768, 768, train_enc);
+      b.fc1 = linear(p + "mlp.fc1", 3072, 768, train_enc);
+      b.fc2 = linear(p + "mlp.fc2", 768, 3072, train_enc);
+      b.h1 = alloc(sizeof(T) * Tk * 768); b.h2 = alloc(sizeof(T) * Tk * 768);
+      b.mean1 = alloc(sizeof(float) * Tk); b.rstd1 = alloc(sizeof(float) * Tk);
+      b.mean2 = alloc(sizeof(float) * Tk); b.rstd2 = alloc(sizeof(float) * Tk);
+      b.qkvb = alloc(sizeof(T) * Tk * 2304);
+      b.ao = alloc(sizeof(T) * Tk * 768);
+      b.lse = alloc(sizeof(float) * (size_t)B * 12 * 197);
+      b.u = alloc(sizeof(T) * Tk * 3072); b.a = alloc(sizeof(T) * Tk * 3072);
+      note_wgrad(linear_geom(Tk, 2304, 768)); note_wgrad(linear_geom(Tk, 768, 768));
+      note_wgrad(linear_geom(Tk, 3072, 768)); note_wgrad(linear_geom(Tk, 768, 3072));
+      blocks.push_back(b);
+      const size_t xin = xs[2 * i], xmid = xs[2 * i + 1], xout = xs[2 * i + 2];
+      m->fwd.push_back([=](cudaStream_t st) {
+        float* x0 = mm->template at<float>(xin);
+        float* x1 = mm->template at<float>(xmid);
+        float* x2 = mm->template at<float>(xout);
+        T* h1 = mm->template at<T>(b.h1);
+        T* h2 = mm->template at<T>(b.h2);
+        T* qkv = mm->template at<T>(b.qkvb);
+        T* ao = mm->template at<T>(b.ao);
+        mm->launches += 2;
+        S4G_TRY(k_layernorm_fwd<T>(x0, b.n1w->p, b.n1b->p, h1, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), (int)Tk, 768, 1e-6f, st));
+        S4G_TRY(self->fprop(linear_geom(Tk, 2304, 768), h1, mm->template at<T>(b.qkv.wf), epi(qkv, 2304, b.qkv.b->p), st));
+        S4G_TRY(self->attn_fwd(qkv, ao, mm->template at<float>(b.lse), st));
+        EpiParams e1 = epi(x1, 768, b.proj.b->p, EPI_NONE, 1);
+        e1.res = x0; e1.res_f32 = 1; e1.ldr = 768;
+        S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), ao, mm->template at<T>(b.proj.wf), e1, st));
+        S4G_TRY(k_layernorm_fwd<T>(x1, b.n2w->p, b.n2b->p, h2, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), (int)Tk, 768, 1e-6f, st));
+        EpiParams e2 = epi(mm->template at<T>(b.a), 3072, b.fc1.b->p, EPI_GELU);
+        e2.out2 = mm->template at<T>(b.u);
+        S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), h2, mm->template at<T>(b.fc1.wf), e2, st));
+        EpiParams e3 = epi(x2, 768, b.fc2.b->p, EPI_NONE, 1);
+        e3.res = x1; e3.res_f32 = 1; e3.ldr = 768;
+        return self->fprop(linear_geom(Tk, 768, 3072), mm->template at<T>(b.a), mm->template at<T>(b.fc2.wf), e3, st);
+      });
+      if (dense && (i == 2 || i == 5 || i == 8 || i == 11)) {
+        const int k = i / 3;
+        tap_act[k] = act(B, 14, 14, 768, train_enc);
+        const int ta = tap_act[k];
+        m->fwd.push_back([=](cudaStream_t st) {
+          mm->launches++;
+          return k_tokens_to_nhwc<T>(mm->template at<float>(xout), self->V(ta), self->B, st);
+        });
+      }
+    }
+    if (!train_enc) return;
+    // ---------------- encoder backward (stored in forward order; run reversed) ----------------
+    dxa = alloc(sizeof(float) * Tk * 768); dxb = alloc(sizeof(float) * Tk * 768);
+    dxT = alloc(sizeof(T) * Tk * 768); dh = alloc(sizeof(T) * Tk * 768);
+    du = alloc(sizeof(T) * Tk * 3072); dao = alloc(sizeof(T) * Tk * 768); dqkv = alloc(sizeof(T) * Tk * 2304);
+    // patch-embed / token-assembly backward: gradient arrives in dxa (12 blocks => even number of ping-pongs)
+    m->bwd_enc.push_back([=](cudaStream_t st) {
+      float* dx = mm->template at<float>(self->dxa);
+      mm->launches += 2;
+      if (cls->g || pos->g) S4G_TRY(k_assemble_tokens_bwd(dx, nullptr, cls->g, pos->g, self->B, st));
+      T* dpe = mm->template at<T>(self->dxT);
+      S4G_TRY(k_tokens_to_nhwc<T>(dx, dpe, self->B, st));
+      return self->linear_param_grads(self->pe_lin, dpe, mm->template at<T>(self->patches), Pn, st);
+    });
+    for (int i = 0; i < 12; ++i) {
+      const Block b = blocks[i];
+      const size_t xin = xs[2 * i], xmid = xs[2 * i + 1];
+      const int tapk = (dense && (i == 2 || i == 5 || i == 8 || i == 11)) ? i / 3 : -1;
+      const int ta = tapk >= 0 ? tap_act[tapk] : -1;
+      m->bwd_enc.push_back([=](cudaStream_t st) {
+        // incoming gradient of the block output: dxa; result (block input gradient) also ends in dxa
+        float* dxo = mm->template at<float>(self->dxa);
+        float* dxm = mm->template at<float>(self->dxb);
+        T* dxt = mm->template at<T>(self->dxT);
+        T* dhb = mm->template at<T>(self->dh);
+        T* dub = mm->template at<T>(self->du);
+        T* daob = mm->template at<T>(self->dao);
+        T* dqkvb = mm->template at<T>(self->dqkv);
+        if (ta >= 0) { mm->launches++; S4G_TRY(k_tap_grad<T>(self->G(ta), dxo, self->B, i == 11 ? 0 : 1, st)); }
+        const long long n = Tk * 768;
+        mm->launches += 4;
+        // mlp: x2 = x1 + fc2(gelu(fc1(ln2(x1))))
+        S4G_TRY(k_cast_f32<T>(dxo, dxt, n, st));
+        EpiParams e = epi(dub, 3072, nullptr, EPI_DGELU);
+        e.aux = mm->template at<T>(b.u);
+        S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), e, st));
+        S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st));
+        S4G_TRY(self->fprop(linear_geom(Tk, 768, 3072), dub, mm->template at<T>(b.fc1.wd), epi(dhb, 768), st));
+        S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st));
+        S4G_CUDA(cudaMemsetAsync(b.n2w->g, 0, sizeof(float) * 768, st));
+        S4G_CUDA(cudaMemsetAsync(b.n2b->g, 0, sizeof(float) * 768, st));
+        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st));
+        // attention: x1 = x0 + proj(attn(qkv(ln1(x0))))
+        S4G_TRY(k_cast_f32<T>(dxm, dxt, n, st));
+        S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), dxt, mm->template at<T>(b.proj.wd), epi(daob, 768), st));
+        S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st));
+        S4G_TRY(self->attn_bwd(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, st));
+        S4G_TRY(self->fprop(linear_geom(Tk, 768, 2304), dqkvb, mm->template at<T>(b.qkv.wd), epi(dhb, 768), st));
+        S4G_TRY(self->linear_param_grads(b.qkv, dqkvb, mm->template at<T>(b.h1), Tk, st));
+        S4G_CUDA(cudaMemsetAsync(b.n1w->g, 0, sizeof(float) * 768, st));
+        S4G_CUDA(cudaMemsetAsync(b.n1b->g, 0, sizeof(float) * 768, st));
+        return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st);
+      });
+    }
+  }
+
+  // ---- decoder ---------------------------------------------------------------------------------------------------
+  size_t head_small = 0, head_dsmall = 0;
+  void build_decoder() {
+    Builder* self = this;
+    S4GModel* mm = m;
+    bwd = &m->bwd_dec;
+    const bool seg = m->d.dense == S4G_DENSE_SEG;
+    const bool tap_grad = !m->d.frozen;
+    const std::string d = "decoder.";
+    // reassemble (Models/DPT_decoder.py:517-520)
+    int l[4];
+    {  // act_postprocess12: 1x1 768->96, ConvT k4 s4
+      const int a = act(B, 14, 14, 96);
+      lin_layer(linear(d + "act_postprocess12.0", 96, 768), tap_act[0], a, tap_grad);
+      l[0] = convT_layer(d + "act_postprocess12.1", a, 96, 4);
+    }
+    {
+      const int a = act(B, 14, 14, 192);
+      lin_layer(linear(d + "act_postprocess22.0", 192, 768), tap_act[1], a, tap_grad);
+      l[1] = convT_layer(d + "act_postprocess22.1", a, 192, 2);
+    }
+    {
+      l[2] = act(B, 14, 14, 384);
+      lin_layer(linear(d + "act_postprocess32.0", 384, 768), tap_act[2], l[2], tap_grad);
+    }
+    {
+      const int a = act(B, 14, 14, 768);
+      lin_layer(linear(d + "act_postprocess42.0", 768, 768), tap_act[3], a, tap_grad);
+      l[3] = conv_s2_layer(d + "act_postprocess42.1", a);
+    }
+    const int feat[4] = {96, 192, 384, 768};
+    int r[4];
+    for (int k = 0; k < 4; ++k) {
+      const Act a = m->acts[l[k]];
+      r[k] = act(a.B, a.H, a.W, 256);
+      conv3_layer(conv3(d + "layer" + std::to_string(k + 1) + "_rn", 256, feat[k]), l[k], r[k]);
+    }
+    const int p4 = fusion(d + "refinenet4.", r[3], -1, seg);
+    const int p3 = fusion(d + "refinenet3.", p4, r[2], seg);
+    const int p2 = fusion(d + "refinenet2.", p3, r[1], seg);
+    const int p1 = fusion(d + "refinenet1.", p2, r[0], seg);
+    const long long M1 = (long long)B * 112 * 112;
+    head_small = alloc(sizeof(float) * M1);
+    head_dsmall = alloc(sizeof(float) * M1);
+    if (seg) {
+      const int c = act(B, 112, 112, 256);
+      conv3_layer(conv3(d + "output_conv.0", 256, 256), p1, c);
+      BN n = bn(d + "output_conv.1");
+      Param* w4 = P(d + "output_conv.4.weight");
+      Param* b4 = P(d + "output_conv.4.bias");
+      m->fwd.push_back([=](cudaStream_t st) {
+        S4G_TRY(self->bn_forward_stats(n, self->V(c), M1, st));
+        mm->launches += 2;
+        float* small = mm->template at<float>(self->head_small);
+        S4G_TRY(k_seghead_fwd<T>(self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p, b4->p,
+                                 mm->training ? mm->dropout_mask : nullptr, mm->training ? mm->d.dropout_p : 0.f, mm->seed, small, M1, 256, st));
+        return k_bilinear2x_f32_fwd(small, mm->out, self->B, 112, 112, st);
+      });
+      bwd->push_back([=](cudaStream_t st) {
+        float* ds = mm->template at<float>(self->head_dsmall);
+        double* sums = mm->template at<double>(n.sums);
+        mm->launches += 3;
+        S4G_TRY(k_bilinear2x_f32_bwd(mm->dout, ds, self->B, 112, 112, st));
+        S4G_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 512, st));
+        S4G_CUDA(cudaMemsetAsync(w4->g, 0, sizeof(float) * 256, st));
+        S4G_CUDA(cudaMemsetAsync(b4->g, 0, sizeof(float), st));
+        S4G_TRY(k_seghead_bwd_reduce<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
+                                        mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, w4->g, b4->g, M1, 256, st));
+        if (mm->d.world_size > 1) S4G_TRY(mm->allreduce(mm->allreduce_user, sums, 512, st));
+        return k_seghead_bwd_apply<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
+                                      mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, (double)M1 * mm->d.world_size, self->G(c),
+                                      n.w->g, n.b->g, M1, 256, st);
+      });
+    } else {
+      const int c = act(B, 112, 112, 128);
+      conv3_layer(conv3(d + "output_conv.0", 128, 256), p1, c);
+      const int u = act(B, 224, 224, 128);
+      m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_bilinear2x_fwd<T>(self->V(c), self->V(u), self->B, 112, 112, 128, st); });
+      bwd->push_back([=](cudaStream_t st) { mm->launches++; return k_bilinear2x_bwd<T>(self->G(u), self->G(c), self->B, 112, 112, 128, st); });
+      const int h = act(B, 224, 224, 32);
+      conv3_layer(conv3(d + "output_conv.2", 32, 128), u, h, EPI_RELU);
+      Param* w4 = P(d + "output_conv.4.weight");
+      Param* b4 = P(d + "output_conv.4.bias");
+      const long long M2 = (long long)B * 224 * 224;
+      m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_depthhead_fwd<T>(self->V(h), w4->p, b4->p, mm->out, M2, 32, st); });
+      // inserted BEFORE conv(…2)'s backward in run order because bwd runs reversed
+      bwd->push_back([=](cudaStream_t st) {
+        S4G_CUDA(cudaMemsetAsync(w4->g, 0, sizeof(float) * 32, st));
+        S4G_CUDA(cudaMemsetAsync(b4->g, 0, sizeof(float), st));
+        mm->launches += 2;
+        S4G_TRY(k_depthhead_bwd<T>(mm->dout, mm->out, self->V(h), w4->p, self->G(h), w4->g, b4->g, M2, 32, st));
+        return k_relu_bwd_add<T>(self->G(h), self->V(h), nullptr, self->G(h), M2 * 32, st);  // ReLU mask (h = relu(.))
+      });
+    }
+  }
+
+  // ConvTranspose2d(C, C, k, stride k) (Models/DPT_decoder.py:341-350, 365-374)
+  int convT_layer(const std::string& name, int in, int C, int k) {
+    Builder* self = this;
+    S4GModel* mm = m;
+    Param* w = P(name + ".weight");
+    Param* b = P(name + ".bias");
+    const int kk = k * k;
+    const size_t wf = alloc(sizeof(T) * (size_t)kk * C * C), wd = alloc(sizeof(T) * (size_t)kk * C * C);
+    dwp_bytes = std::max(dwp_bytes, sizeof(float) * (size_t)kk * C * C);
+    m->pack.push_back([=](cudaStream_t st) { mm->launches++; return k_pack_convT<T>(w->p, mm->template at<T>(wf), mm->template at<T>(wd), C, C, k, st); });
+    const Act a = m->acts[in];
+    const long long M = a.rows();
+    const size_t ycol = alloc(sizeof(T) * M * kk * C), dycol = alloc(sizeof(T) * M * kk * C);
+    const int out = act(a.B, a.H * k, a.W * k, C);
+    note_wgrad(linear_geom(M, kk * C, C));
+    m->fwd.push_back([=](cudaStream_t st) {
+      S4G_TRY(self->fprop(linear_geom(M, kk * C, C), self->V(in), mm->template at<T>(wf), epi(mm->template at<T>(ycol), kk * C), st));
+      mm->launches++;
+      return k_pixel_shuffle<T>(mm->template at<T>(ycol), b->p, self->V(out), a.B, a.H, a.W, C, k, st);
+    });
+    bwd->push_back([=](cudaStream_t st) {
+      T* dy = mm->template at<T>(dycol);
+      mm->launches += 3;
+      S4G_TRY(k_pixel_unshuffle<T>(self->G(out), dy, a.B, a.H, a.W, C, k, st));
+      S4G_TRY(self->fprop(linear_geom(M, C, kk * C), dy, mm->template at<T>(wd), epi(self->G(in), C), st));
+      float* dwp = mm->template at<float>(self->dwp_scratch);
+      S4G_TRY(self->wgrad(linear_geom(M, kk * C, C), dy, self->V(in), dwp, st));
+      S4G_TRY(k_unpack_convT_grad(dwp, w->g, C, C, k, st));
+      S4G_CUDA(cudaMemsetAsync(b->g, 0, sizeof(float) * C, st));
+      return k_colsum<T>(self->G(out), b->g, M * kk, C, C, st);
+    });
+    return out;
+  }
+
+  // Conv2d(768, 768, 3, stride 2, pad 1) (Models/DPT_decoder.py:403-409): explicit im2col + GEMM
+  int conv_s2_layer(const std::string& name, int in) {
+    Builder* self = this;
+    S4GModel* mm = m;
+    Param* w = P(name + ".weight");
+    Param* b = P(name + ".bias");
+    const Act a = m->acts[in];
+    const int C = a.C, Ho = (a.H + 1) / 2, Wo = (a.W + 1) / 2;
+    const long long M = (long long)a.B * Ho * Wo;
+    const size_t wf = alloc(sizeof(T) * (size_t)C * C * 9), wt = alloc(sizeof(T) * (size_t)C * C * 9);
+    dwp_bytes = std::max(dwp_bytes, sizeof(float) * (size_t)C * C * 9);
+    const size_t col = alloc(sizeof(T) * M * 9 * C), dcol = alloc(sizeof(T) * M * 9 * C);
+    const size_t wstage = alloc(sizeof(float) * (size_t)C * C * 9);
+    m->pack.push_back([=](cudaStream_t st) {
+      // wf[co][tap][ci] ; wt = wf^T ([tap*C+ci][co]) via the fp32 staging copy of the packed layout
+      mm->launches += 3;
+      S4G_TRY(k_pack_conv<float>(w->p, mm->template at<float>(wstage), nullptr, C, C, 3, st));
+      return k_pack_linear<T>(mm->template at<float>(wstage), mm->template at<T>(wf), mm->template at<T>(wt), C, 9 * C, st);
+    });
+    const int out = act(a.B, Ho, Wo, C);
+    note_wgrad(linear_geom(M, C, 9 * C));
+    m->fwd.push_back([=](cudaStream_t st) {
+      mm->launches++;
+      S4G_TRY(k_im2col_s2<T>(self->V(in), mm->template at<T>(col), a.B, a.H, a.W, C, st));
+      return self->fprop(linear_geom(M, C, 9 * C), mm->template at<T>(col), mm->template at<T>(wf), epi(self->V(out), C, b->p), st);
+    });
+    bwd->push_back([=](cudaStream_t st) {
+      T* dc = mm->template at<T>(dcol);
+      mm->launches += 3;
+      S4G_TRY(self->fprop(linear_geom(M, 9 * C, C), self->G(out), mm->template at<T>(wt), epi(dc, 9 * C), st));
+      S4G_TRY(k_col2im_s2<T>(dc, self->G(in), a.B, a.H, a.W, C, st));
+      float* dwp = mm->template at<float>(self->dwp_scratch);
+      S4G_TRY(self->wgrad(linear_geom(M, C, 9 * C), self->G(out), mm->template at<T>(col), dwp, st));
+      S4G_TRY(k_unpack_conv_grad(dwp, w->g, C, C, 3, st));
+      S4G_CUDA(cudaMemsetAsync(b->g, 0, sizeof(float) * C, st));
+      return k_colsum<T>(self->G(out), b->g, M, C, C, st);
+    });
+    return out;
+  }
+
+  // ---- classification branch (Models/models.py:338,348-354) -------------------------------------------------------
+  void build_cls_head() {
+    Builder* self = this;
+    S4GModel* mm = m;
+    bwd = &m->bwd_dec;
+    const long long Tk = (long long)B * 197;
+    Param* nw = P("norm.weight");
+    Param* nb = P("norm.bias");
+    const size_t hn = alloc(sizeof(T) * Tk * 768), mean = alloc(sizeof(float) * Tk), rstd = alloc(sizeof(float) * Tk);
+    const size_t pooled = alloc(sizeof(T) * (size_t)B * 768), dpooled = alloc(sizeof(T) * (size_t)B * 768);
+    const size_t dhn = alloc(sizeof(T) * Tk * 768), logit_t = alloc(sizeof(T) * (size_t)B * std::max(1, m->d.num_classes));
+    const bool has_head = m->d.num_classes > 0;
+    Lin head{};
+    if (has_head) head = linear("lin_head", m->d.num_classes, 768);
+    (void)hn; (void)mean; (void)rstd; (void)pooled; (void)dpooled; (void)dhn; (void)logit_t; (void)head; (void)nw; (void)nb;
+    (void)self; (void)mm;
+    s4g_set_error("classification branch (S4G_DENSE_NONE) is scheduled for the next round");
+    unsupported = true;
+  }
+  bool unsupported = false;
+
+  int finish() {
+    dwp_scratch = alloc(dwp_bytes);
+    wg_scratch = alloc(wg_bytes);
+    m->ws_need = top + 256;
+    if (!missing.empty()) {
+      std::string s = "unbound state_dict entries:";
+      for (size_t i = 0; i < missing.size() && i < 8; ++i) s += " " + missing[i];
+      s4g_set_error(s);
+      return S4G_ERR_NAME;
+    }
+    return unsupported ? S4G_ERR_STATE : 0;
+  }
+};
+
+// Builders are kept alive with the model (closures hold `self`).
+struct BuilderHolder {
+  std::unique_ptr<Builder<float>> f;
+  std::unique_ptr<Builder<bf16>> h;
+};
+std::map<S4GModel*, BuilderHolder> g_builders;
+
+template <typename T>
+int build(S4GModel* m, std::unique_ptr<Builder<T>>& slot) {
+  slot.reset(new Builder<T>(m));
+  Builder<T>& b = *slot;
+  b.bwd = &m->bwd_dec;
+  b.build_encoder(m->d.dense != S4G_DENSE_NONE);
+  if (m->d.dense != S4G_DENSE_NONE) b.build_decoder();
+  else b.build_cls_head();
+  return b.finish();
+}
+
+int ensure_built(S4GModel* m) {
+  if (m->built) return 0;
+  m->pack.clear(); m->fwd.clear(); m->bwd_dec.clear(); m->bwd_enc.clear(); m->acts.clear();
+  int r;
+  if (m->d.dtype == S4G_DTYPE_F32) r = build<float>(m, g_builders[m].f);
+  else r = build<bf16>(m, g_builders[m].h);
+  if (r == 0) m->built = true;
+  return r;
+}
+
+}  // namespace
+
+extern "C" {
+
+int s4g_model_create(const S4GModelDesc* desc, S4GModel** out) {
+  if (!desc || !out || desc->batch <= 0) { s4g_set_error("model_create: bad descriptor"); return S4G_ERR_SHAPE; }
+  if (desc->dtype == S4G_DTYPE_F32 && desc->backend == S4G_BACKEND_TENSOR) {
+    s4g_set_error("model_create: the tensor-core backend is bf16 only (fp32 is the FFMA validation mode)");
+    return S4G_ERR_STATE;
+  }
+  S4GModel* m = new S4GModel();
+  m->d = *desc;
+  if (m->d.world_size < 1) m->d.world_size = 1;
+  *out = m;
+  return 0;
+}
+void s4g_model_destroy(S4GModel* m) {
+  if (!m) return;
+  g_builders.erase(m);
+  delete m;
+}
+int s4g_model_bind(S4GModel* m, const char* name, void* data, void* grad, long long numel) {
+  if (!m || !name || !data) { s4g_set_error("model_bind: null argument"); return S4G_ERR_STATE; }
+  Param& p = m->params[name];  // node address is stable; closures hold Param*
+  p.p = reinterpret_cast<float*>(data);
+  p.g = reinterpret_cast<float*>(grad);
+  p.n = numel;
+  return 0;
+}
+int s4g_model_set_grad_arena(S4GModel* m, void* grads, size_t bytes) {
+  m->grad_arena = grads; m->grad_arena_bytes = bytes;
+  return 0;
+}
+size_t s4g_model_workspace_bytes(S4GModel* m) {
+  if (ensure_built(m) != 0) return 0;
+  return m->ws_need;
+}
+int s4g_model_set_workspace(S4GModel* m, void* workspace, size_t bytes) {
+  S4G_TRY(ensure_built(m));
+  if (bytes < m->ws_need) { s4g_set_error("model_set_workspace: workspace too small"); return S4G_ERR_WORKSPACE; }
+  if (reinterpret_cast<uintptr_t>(workspace) & 255) { s4g_set_error("model_set_workspace: need 256 B alignment"); return S4G_ERR_ALIGN; }
+  m->ws = reinterpret_cast<char*>(workspace);
+  m->ws_bytes = bytes;
+  return 0;
+}
+int s4g_model_set_allreduce(S4GModel* m, s4g_allreduce_fn fn, void* user) {
+  m->allreduce = fn; m->allreduce_user = user;
+  return 0;
+}
+int s4g_model_set_bucket_events(S4GModel* m, void** events, int n) {
+  m->events.clear();
+  for (int i = 0; i < n; ++i) m->events.push_back(reinterpret_cast<cudaEvent_t>(events[i]));
+  return 0;
+}
+static int bucket_of_block(int block, int n_buckets) {
+  // bucket 0 = decoder; encoder blocks 11..0 spread over buckets 1..n-1 in backward order
+  const int ne = n_buckets - 1;
+  if (ne <= 0) return 0;
+  const int rev = 11 - block;  // 0 = first finished
+  return 1 + rev * ne / 12;
+}
+const char* s4g_model_bucket_params(S4GModel* m, int bucket, int n_buckets) {
+  m->bucket_str.clear();
+  for (auto& kv : m->params) {
+    const std::string& name = kv.first;
+    if (!kv.second.g) continue;
+    int bkt;
+    if (name.compare(0, 8, "decoder.") == 0 || name.compare(0, 8, "lin_head") == 0 || name.compare(0, 5, "norm.") == 0) bkt = 0;
+    else if (name.compare(0, 7, "blocks.") == 0) bkt = bucket_of_block(atoi(name.c_str() + 7), n_buckets);
+    else bkt = n_buckets - 1;
+    if (bkt == bucket) { m->bucket_str += name; m->bucket_str += '\n'; }
+  }
+  return m->bucket_str.c_str();
+}
+int s4g_model_last_launches(S4GModel* m) { return m->launches; }
+
+int s4g_model_forward(S4GModel* m, const float* images, float* out, int training, uint64_t seed,
+                      const uint8_t* dropout_mask, void* stream) {
+  S4G_TRY(ensure_built(m));
+  if (!m->ws) { s4g_set_error("model_forward: workspace not set"); return S4G_ERR_STATE; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  m->images = images; m->out = out; m->training = training; m->seed = seed; m->dropout_mask = dropout_mask;
+  m->launches = 0;
+  for (auto& op : m->pack) S4G_TRY(op(st));
+  for (auto& op : m->fwd) S4G_TRY(op(st));
+  return 0;
+}
+
+int s4g_model_backward(S4GModel* m, const float* dout, void* stream) {
+  if (!m->built || !m->ws) { s4g_set_error("model_backward: forward has not run"); return S4G_ERR_STATE; }
+  if (!m->training) { s4g_set_error("model_backward: last forward was not in training mode"); return S4G_ERR_STATE; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  m->dout = dout;
+  m->launches = 0;
+  const int nb = (int)m->events.size();
+  for (size_t i = m->bwd_dec.size(); i-- > 0;) S4G_TRY(m->bwd_dec[i](st));
+  if (nb > 0) S4G_CUDA(cudaEventRecord(m->events[0], st));
+  // bwd_enc[0] = patch-embed, bwd_enc[1 + i] = block i
+  for (size_t i = m->bwd_enc.size(); i-- > 0;) {
+    S4G_TRY(m->bwd_enc[i](st));
+    if (nb > 1 && i >= 1) {
+      const int block = (int)i - 1;
+      const int bkt = bucket_of_block(block, nb);
+      const bool last_of_bucket = block == 0 ? false : bucket_of_block(block - 1, nb) != bkt;
+      if (last_of_bucket && bkt < nb - 1) S4G_CUDA(cudaEventRecord(m->events[bkt], st));
+    }
+  }
+  if (nb > 1) S4G_CUDA(cudaEventRecord(m->events[nb - 1], st));
+  return 0;
+}
+
+}  // extern "C"

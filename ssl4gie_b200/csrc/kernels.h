@@ -1,0 +1,135 @@
+// Internal launcher declarations (host side). Every launcher enqueues on `st`, never synchronises,
+// never allocates, and returns 0 or a negative S4G_ERR_* code.
+#pragma once
+#include "../../include/ssl4gie_b200.h"
+#include "common.cuh"
+
+struct ConvGeom {
+  int Nimg, Hi, Wi, Cin, Ho, Wo, Cout, R, S, stride, pad;
+  int ldx;  // channel stride of X rows (elements), normally Cin
+  int ldy;  // channel stride of dY rows (wgrad), normally Cout
+};
+static inline ConvGeom linear_geom(long long M, int N, int K) {
+  ConvGeom g{(int)M, 1, 1, K, 1, 1, N, 1, 1, 1, 0, K, N};
+  return g;
+}
+static inline ConvGeom conv3_geom(int B, int H, int W, int Cin, int Cout) {
+  ConvGeom g{B, H, W, Cin, H, W, Cout, 3, 3, 1, 1, Cin, Cout};
+  return g;
+}
+
+// ---- validation (SIMT) contractions: simt.cu
+template <typename T> int simt_conv_fprop(const ConvGeom& g, const T* X, const T* W, const EpiParams& e, cudaStream_t st);
+template <typename T> int simt_conv_wgrad(const ConvGeom& g, const T* dY, const T* X, float* dW, cudaStream_t st);
+
+// ---- tcgen05 contractions (bf16 in, fp32 accumulate in TMEM): umma.cu
+int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiParams& e, cudaStream_t st);
+int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW, float* scratch, size_t scratch_bytes,
+                    cudaStream_t st);
+size_t umma_wgrad_scratch_bytes(const ConvGeom& g);
+int umma_init();
+
+// ---- elementwise / normalisation / resampling: elementwise.cu
+template <typename T> int k_patchify(const float* img, T* out, int B, cudaStream_t st);
+int k_assemble_tokens(const float* pe, const float* cls, const float* pos, float* x, int B, cudaStream_t st);
+int k_assemble_tokens_bwd(const float* dx, float* dpe, float* dcls, float* dpos, int B, cudaStream_t st);
+template <typename T>
+int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y, float* mean, float* rstd, int rows,
+                    int C, float eps, cudaStream_t st);
+// dx = (dres ? dres : 0) + LN-backward(dy); dgamma/dbeta accumulate atomically (must be zeroed by caller)
+template <typename T>
+int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                    const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st);
+template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st);
+template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st);  // out zeroed by caller
+template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
+template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st);    // inverse of above
+template <typename T> int k_cast_f32(const float* in, T* out, long long n, cudaStream_t st);
+template <typename T> int k_relu(const T* x, T* y, long long n, cudaStream_t st);
+// dx = (dskip ? dskip : 0) + (x > 0 ? dr : 0)
+template <typename T> int k_relu_bwd_add(const T* dr, const T* x, const T* dskip, T* dx, long long n, cudaStream_t st);
+template <typename T> int k_add(const T* a, const T* b, T* y, long long n, cudaStream_t st);
+template <typename T>
+int k_pixel_shuffle(const T* ycol, const float* bias, T* out, int B, int H, int W, int C, int k, cudaStream_t st);
+template <typename T>
+int k_pixel_unshuffle(const T* dout, T* dycol, int B, int H, int W, int C, int k, cudaStream_t st);
+template <typename T> int k_im2col_s2(const T* x, T* col, int B, int H, int W, int C, cudaStream_t st);    // 3x3 s2 p1
+template <typename T> int k_col2im_s2(const T* dcol, T* dx, int B, int H, int W, int C, cudaStream_t st);
+template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st);
+template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int W, int C, cudaStream_t st);
+
+// BatchNorm2d(train): stats[0..C) = sum, [C..2C) = sumsq as double (zeroed by caller)
+template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st);
+// mean/rstd from (possibly all-reduced) sums over `count` rows; running stats update like torch
+int k_bn_finalize(const double* stats, double count, float* mean, float* rstd, float* running_mean, float* running_var,
+                  long long* num_batches_tracked, float momentum, float eps, int C, cudaStream_t st);
+int k_bn_eval_prepare(const float* running_mean, const float* running_var, float* mean, float* rstd, float eps, int C,
+                      cudaStream_t st);
+// y = bn(x) [relu] [+ skip]
+template <typename T>
+int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta, const T* skip,
+               T* y, int relu, long long M, int C, cudaStream_t st);
+// sums[0..C) = sum(dy'), [C..2C) = sum(dy' * xhat) where dy' = relu ? dy*(bn(x)>0) : dy   (double, zeroed by caller)
+template <typename T>
+int k_bn_bwd_reduce(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma,
+                    const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st);
+template <typename T>
+int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                   const double* sums, double count, T* dx, float* dgamma, float* dbeta, int relu, long long M, int C,
+                   cudaStream_t st);
+
+// seg head tail: BN -> ReLU -> Dropout(p) -> 1x1 (C->1) + b  => small [M] fp32
+template <typename T>
+int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
+                  const float* w, const float* b, const uint8_t* mask, float p, uint64_t seed, float* small,
+                  long long M, int C, cudaStream_t st);
+// pass 1: reductions (BN sums + dw[C] + db) ; pass 2: dx
+template <typename T>
+int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
+                         const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
+                         float* dw, float* db, long long M, int C, cudaStream_t st);
+template <typename T>
+int k_seghead_bwd_apply(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
+                        const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed,
+                        const double* sums, double count, T* dx, float* dgamma, float* dbeta, long long M, int C,
+                        cudaStream_t st);
+// depth head tail: (already ReLU'd) h[M,C] . w + b -> sigmoid => out [M] fp32 ; bwd gives dh and dw/db
+template <typename T>
+int k_depthhead_fwd(const T* h, const float* w, const float* b, float* out, long long M, int C, cudaStream_t st);
+template <typename T>
+int k_depthhead_bwd(const float* dout, const float* out, const T* h, const float* w, T* dh, float* dw, float* db,
+                    long long M, int C, cudaStream_t st);
+// single-channel fp32 bilinear x2 (seg logits)
+int k_bilinear2x_f32_fwd(const float* x, float* y, int B, int H, int W, cudaStream_t st);
+int k_bilinear2x_f32_bwd(const float* dy, float* dx, int B, int H, int W, cudaStream_t st);
+
+// ---- weight packing (fp32 torch layout -> T kernel layout): elementwise.cu
+template <typename T> int k_pack_linear(const float* w, T* wp, T* wt, int N, int K, cudaStream_t st);  // wp[N,K], wt[K,N]
+template <typename T> int k_pack_conv(const float* w, T* wf, T* wd, int Co, int Ci, int R, cudaStream_t st);
+template <typename T> int k_pack_convT(const float* w, T* wf, T* wd, int Ci, int Co, int k, cudaStream_t st);
+int k_unpack_conv_grad(const float* dwp, float* dw, int Co, int Ci, int R, cudaStream_t st);
+int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cudaStream_t st);
+
+// ---- attention: attention.cu   qkv [B*197, 2304] (q|k|v, head-major inside), o [B*197, 768]
+template <typename T> int attn_fwd_simt(const T* qkv, T* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
+template <typename T>
+int attn_bwd_simt(const T* qkv, const T* o, const T* dout, const float* lse, T* dqkv, int B, int Ntok, int H,
+                  cudaStream_t st);
+int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
+int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int Ntok, int H,
+                 cudaStream_t st);
+
+// ---- losses: loss.cu   (sums are fp32 scratch, zeroed inside)
+int k_dice_fwd(const float* logits, const float* targets, float* sums, float* loss, int B, int HW, float smooth,
+               cudaStream_t st);
+int k_dice_bwd(const float* logits, const float* targets, const float* sums, const float* gout, float* dlogits, int B,
+               int HW, float smooth, cudaStream_t st);
+int k_ssi_fwd(const float* pred, const float* targ, float* scratch, float* loss, float* ssi_out, int B, int H, int W,
+              float alpha, int scales, cudaStream_t st);
+int k_ssi_bwd(const float* pred, const float* targ, const float* scratch, const float* gout, float* dpred, int B, int H,
+              int W, float alpha, int scales, cudaStream_t st);
+size_t ssi_scratch_floats(int B);
+
+// ---- optimizer: optim.cu
+int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps, float wd,
+            int step, float grad_scale, cudaStream_t st);

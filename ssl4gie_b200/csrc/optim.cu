@@ -1,0 +1,33 @@
+// Fused AdamW over one flat fp32 parameter arena (reference: torch.optim.AdamW(model.parameters(), lr) at
+// Binary_segmentation/train_segmentation.py:204; defaults betas (0.9, 0.999), eps 1e-8, weight_decay 0.01).
+// HBM-bound: 28 B/param (read p,g,m,v; write p,m,v).
+#include "kernels.h"
+
+__global__ void __launch_bounds__(256) adamw_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m,
+                                                    float4* __restrict__ v, long long n4, float lr, float b1, float b2, float eps,
+                                                    float wd, float bc1, float bc2_sqrt, float gs) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 pv = p[i], gv = g[i], mv = m[i], vv = v[i];
+    float* pp = &pv.x; float* gp = &gv.x; float* mp = &mv.x; float* vp = &vv.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float gr = gp[k] * gs;
+      pp[k] *= 1.f - lr * wd;
+      mp[k] = b1 * mp[k] + (1.f - b1) * gr;
+      vp[k] = b2 * vp[k] + (1.f - b2) * gr * gr;
+      const float denom = sqrtf(vp[k]) / bc2_sqrt + eps;
+      pp[k] -= (lr / bc1) * (mp[k] / denom);
+    }
+    p[i] = pv; m[i] = mv; v[i] = vv;
+  }
+}
+int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps, float wd,
+            int step, float grad_scale, cudaStream_t st) {
+  if (n % 4) { s4g_set_error("adamw: arena length must be a multiple of 4"); return S4G_ERR_SHAPE; }
+  const float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
+  adamw_kernel<<<148 * 8, 256, 0, st>>>(reinterpret_cast<float4*>(p), reinterpret_cast<const float4*>(g),
+                                        reinterpret_cast<float4*>(m), reinterpret_cast<float4*>(v), n / 4, lr, b1, b2, eps, wd,
+                                        bc1, sqrtf(bc2), grad_scale);
+  S4G_KERNEL_CHECK();
+  return 0;
+}

@@ -1,0 +1,98 @@
+"""Drop-in loss modules: same constructors / forward signatures as the reference, fused CUDA kernels underneath."""
+import torch
+import torch.nn as nn
+
+from . import _C
+
+
+class _DiceFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets, smooth):
+        _C.require_cuda(logits, "logits")
+        lg = logits.detach().float().contiguous()
+        tg = targets.detach().float().contiguous()
+        B = lg.shape[0]
+        HW = lg.numel() // B
+        scratch = torch.empty(_C.lib().s4g_dice_scratch_bytes(B), dtype=torch.uint8, device=lg.device)
+        loss = torch.empty((), dtype=torch.float32, device=lg.device)
+        _C.check(_C.lib().s4g_dice_fwd(_C.ptr(lg), _C.ptr(tg), _C.ptr(scratch), _C.ptr(loss), B, HW, smooth, _C.stream_ptr()))
+        ctx.save_for_backward(lg, tg, scratch)
+        ctx.smooth = smooth
+        ctx.shape = logits.shape
+        ctx.dtype = logits.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        lg, tg, scratch = ctx.saved_tensors
+        B = lg.shape[0]
+        g = gout.detach().float().contiguous()
+        d = torch.empty_like(lg)
+        _C.check(_C.lib().s4g_dice_bwd(_C.ptr(lg), _C.ptr(tg), _C.ptr(scratch), _C.ptr(g), _C.ptr(d), B, lg.numel() // B,
+                                       ctx.smooth, _C.stream_ptr()))
+        return d.view(ctx.shape).to(ctx.dtype), None, None
+
+
+class SoftDiceLoss(nn.Module):
+    """reference: Binary_segmentation/Metrics/losses.py:5-24"""
+
+    def __init__(self, smooth=1e-8):
+        super().__init__()
+        self.smooth = smooth
+
+    def forward(self, logits, targets):
+        return _DiceFn.apply(logits, targets, float(self.smooth))
+
+
+class _SSIFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, prediction, target, alpha, scales, holder):
+        _C.require_cuda(prediction, "prediction")
+        p = prediction.detach().float().contiguous()
+        t = target.detach().float().contiguous()
+        B, H, W = p.shape[0], p.shape[-2], p.shape[-1]
+        scratch = torch.empty(_C.lib().s4g_ssi_scratch_bytes(B), dtype=torch.uint8, device=p.device)
+        loss = torch.empty((), dtype=torch.float32, device=p.device)
+        ssi = torch.empty((B, H, W), dtype=torch.float32, device=p.device)
+        _C.check(_C.lib().s4g_ssi_fwd(_C.ptr(p), _C.ptr(t), _C.ptr(scratch), _C.ptr(loss), _C.ptr(ssi), B, H, W, alpha, scales,
+                                      _C.stream_ptr()))
+        holder.append(ssi)
+        ctx.save_for_backward(p, t, scratch)
+        ctx.cfg = (alpha, scales, prediction.shape, prediction.dtype)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        p, t, scratch = ctx.saved_tensors
+        alpha, scales, shape, dtype = ctx.cfg
+        B, H, W = p.shape[0], p.shape[-2], p.shape[-1]
+        g = gout.detach().float().contiguous()
+        d = torch.empty_like(p)
+        _C.check(_C.lib().s4g_ssi_bwd(_C.ptr(p), _C.ptr(t), _C.ptr(scratch), _C.ptr(g), _C.ptr(d), B, H, W, alpha, scales,
+                                      _C.stream_ptr()))
+        return d.view(shape).to(dtype), None, None, None, None
+
+
+class ScaleAndShiftInvariantLoss(nn.Module):
+    """reference: Depth_estimation/Metrics/losses.py:120-151 (batch-based reduction only, as the reference uses)"""
+
+    def __init__(self, alpha=0.5, scales=4, reduction="batch-based"):
+        super().__init__()
+        if reduction != "batch-based":
+            raise NotImplementedError("the reference training scripts only use reduction='batch-based'")
+        if scales > 4:
+            raise NotImplementedError("scales <= 4")
+        self.__alpha = alpha
+        self.__scales = scales
+        self.__prediction_ssi = None
+
+    def forward(self, prediction, target):
+        holder = []
+        loss = _SSIFn.apply(prediction, target, float(self.__alpha), int(self.__scales), holder)
+        self.__prediction_ssi = holder[0]
+        return loss
+
+    def __get_prediction_ssi(self):
+        return self.__prediction_ssi
+
+    prediction_ssi = property(__get_prediction_ssi)
