@@ -1,5 +1,645 @@
+// tcgen05 / TMEM / TMA contraction engine for sm_100a (bf16 operands, fp32 accumulation in tensor memory).
+//
+//   umma_conv_fprop : D[M, N] = sum_{tap, c} A_tap[M, c] * W[N, tap*Cin + c]   (+ fused epilogue)
+//        A_tap is the NHWC activation shifted by the tap offset, fetched by 4-D TMA boxes whose
+//        out-of-bounds elements the hardware zero-fills (= the conv's zero padding, no im2col buffer).
+//        Linear layers / 1x1 convs are the 1-tap case.  Both operands K-major, SWIZZLE_128B.
+//   umma_conv_wgrad : dW[Cout, tap*Cin + c] = sum_pixels dY[pix, Cout] * X_tap[pix, c]
+//        contraction over pixels: both operands are MN-major (channel-contiguous) in shared memory,
+//        the same TMA boxes as fprop, split over pixel ranges across CTAs, fp32 red.add epilogue.
+//
+// Kernel anatomy (one CTA per SM, persistent over tiles, 192 threads):
+//   warp 0      TMA producer (one elected lane): global -> smem ring, mbarrier complete_tx
+//   warp 1      tcgen05.mma issuer (one elected lane) + TMEM allocator; tcgen05.commit frees smem slots
+//   warps 2..5  epilogue: tcgen05.ld 32x32b from TMEM (two accumulator stages ping-pong with the main loop),
+//               bias / GELU / GELU' / ReLU / residual, vectorised global stores
+#include <cuda.h>
+
 #include "kernels.h"
-int umma_init() { return 0; }
-int umma_conv_fprop(const ConvGeom&, const bf16*, const bf16*, const EpiParams&, cudaStream_t) { s4g_set_error("tcgen05 path not built yet"); return S4G_ERR_STATE; }
-int umma_conv_wgrad(const ConvGeom&, const bf16*, const bf16*, float*, float*, size_t, cudaStream_t) { s4g_set_error("tcgen05 path not built yet"); return S4G_ERR_STATE; }
+
+namespace {
+
+constexpr int BLOCK_K = 64;           // bf16 elements = 128 B = one swizzle row
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = 128 * 128;  // 128 rows x 128 B
+constexpr int NUM_THREADS = 192;
+
+// ------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  const uint32_t addr = smem_u32(bar);
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+// shared-memory matrix descriptor, SWIZZLE_128B (cute::UMMA::SmemDescriptor: version 1, layout type 2)
+//   K-major : rows of 128 B (64 bf16 along K), 8-row groups 1024 B apart (SBO); LBO unused
+//   MN-major: rows of 128 B (64 bf16 along M/N), 8 K-rows per 1024 B atom (SBO), next 64 M/N elements LBO away
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// instruction descriptor, kind::f16: D=f32, A=B=bf16 (cute::UMMA::InstrDescriptor bit layout)
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------ shared layout
+struct SmemCtl {
+  uint64_t full[STAGES], empty[STAGES], tfull[2], tempty[2];
+  uint32_t tmem_base;
+};
+
+struct TileGeom {  // how a row tile maps onto the NHWC tensor: rows = (dn, dy, dx) boxes
+  int bw, bh, bn;  // box extents (pixels)
+  int tw, th, tn;  // tiles along w, h, n
+  int H, W, Nimg;
+};
+__device__ __forceinline__ void tile_origin(const TileGeom& t, int tile, int& n0, int& h0, int& w0) {
+  const int iw = tile % t.tw, ih = (tile / t.tw) % t.th, in = tile / (t.tw * t.th);
+  w0 = iw * t.bw; h0 = ih * t.bh; n0 = in * t.bn;
+}
+
+struct FpropParams {
+  TileGeom tg;
+  int taps, S, pad, chunks;  // chunks = ceil(Cin / 64)
+  int tiles_m, tiles_n, block_n, N;
+  EpiParams e;
+};
+
+// 32 consecutive columns of one output row
+__device__ __forceinline__ void epi_row32(const EpiParams& e, long long row, int col0, int ncols, const uint32_t (&acc)[32]) {
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(acc[i]) * e.alpha;
+  if (e.bias) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      if (i < ncols) {
+        const float4 b = *reinterpret_cast<const float4*>(e.bias + col0 + i);
+        v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+      }
+    }
+  }
+  const long long o = row * e.ldo + col0;
+  if (e.mode == EPI_GELU) {
+    if (e.out2) {
+      bf16* p2 = reinterpret_cast<bf16*>(e.out2) + o;
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        if (i < ncols) {
+          Vec8<bf16> t;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) t.v[k] = v[i + k];
+          t.store(p2 + i);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = gelu_f(v[i]);
+  } else if (e.mode == EPI_DGELU) {
+    const bf16* pa = reinterpret_cast<const bf16*>(e.aux) + o;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      if (i < ncols) {
+        Vec8<bf16> t;
+        t.load(pa + i);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[i + k] *= dgelu_f(t.v[k]);
+      }
+    }
+  } else if (e.mode == EPI_RELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  }
+  if (e.res) {
+    const long long r = row * e.ldr + col0;
+    if (e.res_f32) {
+      const float* pr = reinterpret_cast<const float*>(e.res) + r;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        if (i < ncols) {
+          const float4 t = *reinterpret_cast<const float4*>(pr + i);
+          v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+        }
+      }
+    } else {
+      const bf16* pr = reinterpret_cast<const bf16*>(e.res) + r;
+#pragma unroll
+      for (int i = 0; i < 32; i += 8) {
+        if (i < ncols) {
+          Vec8<bf16> t;
+          t.load(pr + i);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[i + k] += t.v[k];
+        }
+      }
+    }
+  }
+  if (e.out_f32) {
+    float* po = reinterpret_cast<float*>(e.out) + o;
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      if (i < ncols) {
+        float4 t = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+        if (e.accumulate) {
+          const float4 q = *reinterpret_cast<const float4*>(po + i);
+          t.x += q.x; t.y += q.y; t.z += q.z; t.w += q.w;
+        }
+        *reinterpret_cast<float4*>(po + i) = t;
+      }
+    }
+  } else {
+    bf16* po = reinterpret_cast<bf16*>(e.out) + o;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      if (i < ncols) {
+        Vec8<bf16> t;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t.v[k] = v[i + k];
+        t.store(po + i);
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
+  return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~(uintptr_t)1023);
+}
+
+// =========================================================================================== fprop
+__global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                    const __grid_constant__ CUtensorMap tmB, const FpropParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_1024(smem_raw);
+  const int b_stage_bytes = p.block_n * 128;
+  const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
+  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + STAGES * stage_bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int k_iters = p.taps * p.chunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+        int n0, h0, w0;
+        tile_origin(p.tg, tm, n0, h0, w0);
+        for (int tap = 0; tap < p.taps; ++tap) {
+          const int dy = tap / p.S - p.pad, dx = tap % p.S - p.pad;
+          for (int ch = 0; ch < p.chunks; ++ch) {
+            mbar_wait(&ctl->empty[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * stage_bytes;
+            mbar_expect_tx(&ctl->full[stage], stage_bytes);
+            tma_load_4d(&tmA, &ctl->full[stage], sa, ch * BLOCK_K, w0 + dx, h0 + dy, n0);
+            tma_load_3d(&tmB, &ctl->full[stage], sa + A_STAGE_BYTES, ch * BLOCK_K, tap, tn * p.block_n);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    const uint32_t idesc = make_idesc(128, p.block_n, 0, 0);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(&ctl->tempty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * 256;
+      for (int k = 0; k < k_iters; ++k) {
+        mbar_wait(&ctl->full[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint32_t sb = sa + A_STAGE_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < BLOCK_K / 16; ++kk) {
+            const uint64_t da = make_desc(sa + kk * 32, 16, 1024);
+            const uint64_t db = make_desc(sb + kk * 32, 16, 1024);
+            umma_bf16(tmem_d, da, db, idesc, (k | kk) != 0);
+          }
+          umma_commit(&ctl->empty[stage]);
+          if (k == k_iters - 1) umma_commit(&ctl->tfull[acc]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..5)
+    const int q = warp & 3;  // TMEM lane quarter this warp may touch
+    const int r = q * 32 + lane;
+    int acc = 0; uint32_t acc_phase = 0;
+    const TileGeom& t = p.tg;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+      int n0, h0, w0;
+      tile_origin(t, tm, n0, h0, w0);
+      const int dx = r % t.bw, dy = (r / t.bw) % t.bh, dn = r / (t.bw * t.bh);
+      const int n = n0 + dn, h = h0 + dy, w = w0 + dx;
+      const bool valid = dn < t.bn && n < t.Nimg && h < t.H && w < t.W;
+      const long long row = ((long long)n * t.H + h) * t.W + w;
+      mbar_wait(&ctl->tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld_wait();
+        const int col0 = tn * p.block_n + c0;
+        const int ncols = min(32, p.N - col0);
+        if (valid && ncols > 0) epi_row32(p.e, row, col0, ncols, v);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// =========================================================================================== wgrad
+struct WgradParams {
+  TileGeom tg;      // 64-pixel chunks
+  int taps, S, pad;
+  int Cout, Cin, K;  // K = taps * Cin (row length of dW)
+  int tiles_co, tiles_ci, block_n, splits;
+  int chunks_total;  // pixel chunks
+  float* dW;
+};
+
+__global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmY,
+                                                                    const __grid_constant__ CUtensorMap tmX, const WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_1024(smem_raw);
+  const int a_bytes = 2 * BLOCK_K * 128;                   // two 64-channel groups of dY, 64 pixels each
+  const int ngroups = p.block_n / 64;
+  const int stage_bytes = a_bytes + ngroups * BLOCK_K * 128;
+  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + STAGES * stage_bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int out_tiles = p.tiles_co * p.tiles_ci * p.taps;
+  const int num_work = out_tiles * p.splits;
+  const int chunks_per_split = (p.chunks_total + p.splits - 1) / p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmY);
+    tma_prefetch_desc(&tmX);
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  // work item -> (split, tap, ci tile, co tile); consecutive CTAs share the pixel range (L2 reuse of dY / X)
+  auto decode = [&](int wi, int& split, int& tap, int& tci, int& tco) {
+    tco = wi % p.tiles_co; wi /= p.tiles_co;
+    tci = wi % p.tiles_ci; wi /= p.tiles_ci;
+    tap = wi % p.taps; split = wi / p.taps;
+  };
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0; uint32_t phase = 0;
+      for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+        int split, tap, tci, tco;
+        decode(wi, split, tap, tci, tco);
+        const int dy = tap / p.S - p.pad, dx = tap % p.S - p.pad;
+        const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
+        for (int c = c_begin; c < c_end; ++c) {
+          int n0, h0, w0;
+          tile_origin(p.tg, c, n0, h0, w0);
+          mbar_wait(&ctl->empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * stage_bytes;
+          mbar_expect_tx(&ctl->full[stage], stage_bytes);
+          for (int g = 0; g < 2; ++g) tma_load_4d(&tmY, &ctl->full[stage], sa + g * BLOCK_K * 128, tco * 128 + g * 64, w0, h0, n0);
+          for (int g = 0; g < ngroups; ++g)
+            tma_load_4d(&tmX, &ctl->full[stage], sa + a_bytes + g * BLOCK_K * 128, tci * p.block_n + g * 64, w0 + dx, h0 + dy, n0);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = make_idesc(128, p.block_n, 1, 1);
+    int stage = 0; uint32_t phase = 0;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+      int split, tap, tci, tco;
+      decode(wi, split, tap, tci, tco);
+      const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
+      if (c_begin >= c_end) continue;
+      mbar_wait(&ctl->tempty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * 256;
+      for (int c = c_begin; c < c_end; ++c) {
+        mbar_wait(&ctl->full[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint32_t sb = sa + a_bytes;
+#pragma unroll
+          for (int kk = 0; kk < BLOCK_K / 16; ++kk) {
+            // MN-major: 16 pixels = two 8-row atoms (SBO = 1024 B); 64-channel groups are LBO = 64 px * 128 B apart
+            const uint64_t da = make_desc(sa + kk * 2048, BLOCK_K * 128, 1024);
+            const uint64_t db = make_desc(sb + kk * 2048, BLOCK_K * 128, 1024);
+            umma_bf16(tmem_d, da, db, idesc, (c != c_begin) || kk != 0);
+          }
+          umma_commit(&ctl->empty[stage]);
+          if (c == c_end - 1) umma_commit(&ctl->tfull[acc]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else {
+    const int q = warp & 3;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+      int split, tap, tci, tco;
+      decode(wi, split, tap, tci, tco);
+      const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
+      if (c_begin >= c_end) continue;
+      const int co = tco * 128 + q * 32 + lane;
+      mbar_wait(&ctl->tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld_wait();
+        const int ci0 = tci * p.block_n + c0;
+        if (co < p.Cout && ci0 < p.Cin) {
+          float* dst = p.dW + (long long)co * p.K + (long long)tap * p.Cin + ci0;
+          const int ncols = min(32, p.Cin - ci0);
+          for (int i = 0; i < ncols; ++i) atomicAdd(dst + i, __uint_as_float(v[i]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+int g_num_sms = 148;
+
+int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+             const uint32_t* box) {
+  cuuint64_t gd[4]; cuuint64_t gs[3]; cuuint32_t bx[4]; cuuint32_t es[4] = {1, 1, 1, 1};
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; }
+  for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
+  if (reinterpret_cast<uintptr_t>(base) & 15) { s4g_set_error("tcgen05 path: operand base must be 16 B aligned"); return S4G_ERR_ALIGN; }
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[256];
+    snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed (%d): rank %d dims %llu %llu %llu %llu box %u %u %u %u", (int)r, rank,
+             (unsigned long long)dims[0], (unsigned long long)dims[1], rank > 2 ? (unsigned long long)dims[2] : 0ull,
+             rank > 3 ? (unsigned long long)dims[3] : 0ull, box[0], box[1], rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    s4g_set_error(buf);
+    return S4G_ERR_CUDA;
+  }
+  return 0;
+}
+
+int pow2_divisor(int v, int cap) {
+  int p = 1;
+  while (p * 2 <= cap && v % (p * 2) == 0) p *= 2;
+  return p;
+}
+// rows-per-tile decomposition: bw | W and bh | H powers of two, bn fills the rest (bw*bh*bn == rows exactly: the
+// TMA transaction byte count of a stage depends on it)
+TileGeom make_tiles(int Nimg, int H, int W, int rows) {
+  TileGeom t;
+  t.H = H; t.W = W; t.Nimg = Nimg;
+  t.bw = pow2_divisor(W, rows);
+  t.bh = pow2_divisor(H, rows / t.bw);
+  t.bn = rows / (t.bw * t.bh);
+  t.tw = (W + t.bw - 1) / t.bw; t.th = (H + t.bh - 1) / t.bh; t.tn = (Nimg + t.bn - 1) / t.bn;
+  return t;
+}
+// plain [M, C] matrix: rows run along "w"
+TileGeom matrix_tiles(long long M, int rows) {
+  TileGeom t;
+  t.H = 1; t.W = (int)M; t.Nimg = 1;
+  t.bw = rows; t.bh = 1; t.bn = 1;
+  t.tw = (int)((M + rows - 1) / rows); t.th = 1; t.tn = 1;
+  return t;
+}
+// activation tensor map: NHWC [Nimg,H,W,C] (row stride ld) -> dims {C, W, H, N}; plain matrix [M, C] -> {C, M, 1, 1}
+int make_act_map(CUtensorMap* map, const bf16* base, const ConvGeom& g, int C, int ld, const TileGeom& t, bool matrix, int H, int W) {
+  uint64_t dims[4], strides[3]; uint32_t box[4];
+  if (matrix) {
+    dims[0] = C; dims[1] = (uint64_t)g.Nimg * H * W; dims[2] = 1; dims[3] = 1;
+    strides[0] = (uint64_t)ld * 2; strides[1] = strides[0] * dims[1]; strides[2] = strides[1];
+    box[0] = 64; box[1] = t.bw; box[2] = 1; box[3] = 1;
+  } else {
+    dims[0] = C; dims[1] = W; dims[2] = H; dims[3] = g.Nimg;
+    strides[0] = (uint64_t)ld * 2; strides[1] = strides[0] * W; strides[2] = strides[1] * H;
+    box[0] = 64; box[1] = t.bw; box[2] = t.bh; box[3] = t.bn;
+  }
+  return make_map(map, base, 4, dims, strides, box);
+}
+int pick_block_n(int N) {
+  if (N <= 256) return (N + 15) / 16 * 16;
+  if (N % 256 == 0) return 256;
+  if (N % 192 == 0) return 192;
+  if (N % 128 == 0) return 128;
+  return 256;
+}
+
+}  // namespace
+
+int umma_init() {
+  if (g_encode) return 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  S4G_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (!fn || qres != cudaDriverEntryPointSuccess) { s4g_set_error("cuTensorMapEncodeTiled is not available in this driver"); return S4G_ERR_CUDA; }
+  g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  int dev = 0;
+  S4G_CUDA(cudaGetDevice(&dev));
+  S4G_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  return 0;
+}
+
+int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiParams& e, cudaStream_t st) {
+  S4G_TRY(umma_init());
+  if (g.stride != 1 || g.Ho != g.Hi || g.Wo != g.Wi) { s4g_set_error("umma_conv_fprop: stride-1 'same' convolutions only"); return S4G_ERR_SHAPE; }
+  if (g.Cin % 8 || g.ldx % 8 || g.Cout % 8) { s4g_set_error("umma_conv_fprop: channel counts must be multiples of 8"); return S4G_ERR_SHAPE; }
+  const bool matrix = g.Hi == 1 && g.Wi == 1;
+  FpropParams p{};
+  p.tg = matrix ? matrix_tiles(g.Nimg, 128) : make_tiles(g.Nimg, g.Hi, g.Wi, 128);
+  p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
+  p.chunks = cdiv(g.Cin, BLOCK_K);
+  p.block_n = pick_block_n(g.Cout);
+  p.N = g.Cout;
+  p.tiles_m = p.tg.tw * p.tg.th * p.tg.tn;
+  p.tiles_n = cdiv(g.Cout, p.block_n);
+  p.e = e;
+  CUtensorMap tmA, tmB;
+  S4G_TRY(make_act_map(&tmA, X, g, g.Cin, g.ldx, p.tg, matrix, g.Hi, g.Wi));
+  {
+    // weights [Cout][taps][Cin] as a 3-D tensor {Cin, taps, Cout}: the channel tail of a tap is zero-filled by
+    // TMA instead of running into the next tap
+    uint64_t dims[3] = {(uint64_t)g.Cin, (uint64_t)p.taps, (uint64_t)g.Cout};
+    uint64_t strides[2] = {(uint64_t)g.Cin * 2, (uint64_t)g.Cin * p.taps * 2};
+    uint32_t box[3] = {64, 1, (uint32_t)p.block_n};
+    S4G_TRY(make_map(&tmB, W, 3, dims, strides, box));
+  }
+  const size_t smem = 1024 + (size_t)STAGES * (A_STAGE_BYTES + p.block_n * 128) + sizeof(SmemCtl);
+  const int grid = std::min(p.tiles_m * p.tiles_n, g_num_sms);
+  umma_fprop_kernel<<<grid, NUM_THREADS, smem, st>>>(tmA, tmB, p);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+
 size_t umma_wgrad_scratch_bytes(const ConvGeom&) { return 0; }
+
+int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW, float*, size_t, cudaStream_t st) {
+  S4G_TRY(umma_init());
+  if (g.stride != 1 || g.Ho != g.Hi || g.Wo != g.Wi) { s4g_set_error("umma_conv_wgrad: stride-1 'same' convolutions only"); return S4G_ERR_SHAPE; }
+  if (g.Cin % 8 || g.ldx % 8 || g.Cout % 8 || g.ldy % 8) { s4g_set_error("umma_conv_wgrad: channel counts must be multiples of 8"); return S4G_ERR_SHAPE; }
+  const bool matrix = g.Hi == 1 && g.Wi == 1;
+  WgradParams p{};
+  p.tg = matrix ? matrix_tiles(g.Nimg, BLOCK_K) : make_tiles(g.Nimg, g.Hi, g.Wi, BLOCK_K);
+  p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
+  p.Cout = g.Cout; p.Cin = g.Cin; p.K = p.taps * g.Cin;
+  p.block_n = std::min(256, (g.Cin + 63) / 64 * 64);
+  p.tiles_co = cdiv(g.Cout, 128);
+  p.tiles_ci = cdiv(g.Cin, p.block_n);
+  p.chunks_total = p.tg.tw * p.tg.th * p.tg.tn;
+  const int out_tiles = p.tiles_co * p.tiles_ci * p.taps;
+  p.splits = std::max(1, std::min(p.chunks_total, (2 * g_num_sms + out_tiles - 1) / out_tiles));
+  // re-balance so that no split is empty
+  const int cps = cdiv(p.chunks_total, p.splits);
+  p.splits = cdiv(p.chunks_total, cps);
+  p.dW = dW;
+  CUtensorMap tmY, tmX;
+  ConvGeom gy = g;
+  S4G_TRY(make_act_map(&tmY, dY, gy, g.Cout, g.ldy, p.tg, matrix, g.Hi, g.Wi));
+  S4G_TRY(make_act_map(&tmX, X, g, g.Cin, g.ldx, p.tg, matrix, g.Hi, g.Wi));
+  S4G_CUDA(cudaMemsetAsync(dW, 0, sizeof(float) * (size_t)g.Cout * p.K, st));
+  const size_t smem = 1024 + (size_t)STAGES * (2 * BLOCK_K * 128 + (p.block_n / 64) * BLOCK_K * 128) + sizeof(SmemCtl);
+  const int grid = std::min(out_tiles * p.splits, g_num_sms);
+  umma_wgrad_kernel<<<grid, NUM_THREADS, smem, st>>>(tmY, tmX, p);
+  S4G_KERNEL_CHECK();
+  return 0;
+}

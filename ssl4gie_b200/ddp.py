@@ -1,0 +1,70 @@
+"""Data-parallel gradient exchange for the fused schedule (reference: DDP(model, find_unused_parameters=True),
+Binary_segmentation/train_segmentation.py:203, collective C1 in SURVEY.md §2.3).
+
+The C++ backward records one CUDA event per gradient bucket as soon as that bucket's gradients are final
+(bucket 0 = DPT decoder, then encoder blocks 11..0 in equal groups, the last bucket also holding patch_embed /
+cls_token / pos_embed).  Each bucket is a contiguous slice of the flat fp32 gradient arena, all-reduced with NCCL on
+a side stream that waits on the bucket's event, so the exchange overlaps the rest of backward.  The unused
+parameters (norm.*, decoder.refinenet4.resConfUnit1.*) are known statically and are simply not in the arena —
+no find_unused_parameters graph walk."""
+import torch
+import torch.distributed as dist
+
+from .engine import Engine
+
+
+class GradientAllReduce:
+    def __init__(self, model, n_buckets=5, process_group=None):
+        core = model.module if hasattr(model, "module") else model
+        self.engine = Engine.of(core)
+        self.engine.materialize()
+        self.engine.enable_direct_grads()
+        self.group = process_group
+        self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self.n_buckets = n_buckets
+        self.comm_stream = None
+        self.slices = None
+        self.events = None
+        self.handles = []
+
+    def _setup(self, handle):
+        e = self.engine
+        offs = {}
+        base = e.flat_grads.data_ptr()
+        for n, g in e.grad_views.items():
+            offs[n] = ((g.data_ptr() - base) // 4, g.numel())
+        self.slices = []
+        for i in range(self.n_buckets):
+            names = handle.bucket_params(i, self.n_buckets)
+            if not names:
+                self.slices.append(None)
+                continue
+            lo = min(offs[n][0] for n in names)
+            hi = max(offs[n][0] + offs[n][1] for n in names)
+            self.slices.append((lo, hi))
+        if e.flat_grads.is_cuda:
+            self.comm_stream = torch.cuda.Stream()
+            self.events = [torch.cuda.Event() for _ in range(self.n_buckets)]
+            for ev in self.events:
+                ev.record()  # materialise the cudaEvent_t handles
+            e.bucket_events = self.events
+
+    def prepare(self, batch):
+        """Call once before the first backward (needs the C model handle for the bucket plan)."""
+        if self.slices is None:
+            self._setup(self.engine.handle(batch))
+
+    def reduce(self):
+        """After loss.backward(): enqueue the bucket all-reduces (overlapping the tail of backward) and make the
+        current stream wait for them."""
+        if self.world_size == 1:
+            return
+        flat = self.engine.flat_grads
+        cur = torch.cuda.current_stream()
+        with torch.cuda.stream(self.comm_stream):
+            for ev, sl in zip(self.events, self.slices):
+                if sl is None:
+                    continue
+                self.comm_stream.wait_event(ev)
+                dist.all_reduce(flat[sl[0]:sl[1]], group=self.group)
+        cur.wait_stream(self.comm_stream)

@@ -78,10 +78,13 @@ def test_fp32_step_matches_golden(dense, golden_dir):
         assert g is not None, n
         gn = g.double().norm().item()
         rn = float(fix["grad_norm"][i])
-        e = abs(gn - rn) / (rn + 1e-30)
+        # gradients that are analytically ~0 (the last bias under the shift-invariant depth loss) are rounding noise
+        # on both sides: measure against a floor tied to the typical gradient scale
+        floor = 1e-3 * float(np.median(fix["grad_norm"]))
+        e = abs(gn - rn) / max(rn, floor)
         k = min(8, g.numel())
         head = torch.from_numpy(fix["grad_head"][i][:k])
-        e2 = (g.flatten()[:k].cpu() - head).abs().max().item() / (g.abs().max().item() + 1e-30)
+        e2 = (g.flatten()[:k].cpu() - head).abs().max().item() / max(g.abs().max().item(), floor)
         if max(e, e2) > worst[1]:
             worst = (n, max(e, e2))
     # per-tensor gradients of the CPU-fp32 fixture are themselves only ~1e-3 accurate for the cancellation-heavy
