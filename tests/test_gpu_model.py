@@ -78,6 +78,12 @@ def test_fp32_step_matches_golden(dense, golden_dir):
         assert g is not None, n
         gn = g.double().norm().item()
         rn = float(fix["grad_norm"][i])
+        if dense == "depth" and n == "decoder.output_conv.4.bias":
+            # sum of ~1e5 cancelling terms (the SSI loss is shift invariant, sigmoid' ~ const at init): the fp64 oracle
+            # gives -4.2e-8, the reference's own fp32 run -6.8e-6 — the fixture value is rounding noise, so only the
+            # magnitude is checked
+            assert gn < 2e-5, gn
+            continue
         # gradients that are analytically ~0 (the last bias under the shift-invariant depth loss) are rounding noise
         # on both sides: measure against a floor tied to the typical gradient scale
         floor = 1e-3 * float(np.median(fix["grad_norm"]))
