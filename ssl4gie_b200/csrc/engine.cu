@@ -113,13 +113,18 @@ struct Builder {
     }
     return simt_conv_fprop<T>(g, X, W, e, st);
   }
-  int wgrad(const ConvGeom& g, const T* dY, const T* X, float* dW, cudaStream_t st) const {
+  // torch_layout (tcgen05 path only): write torch's [Cout][Cin][R][S] instead of the packed [Cout][tap][Cin]
+  int wgrad(const ConvGeom& g, const T* dY, const T* X, float* dW, cudaStream_t st, int torch_layout = 0) const {
     m->launches++;
     if constexpr (std::is_same<T, bf16>::value) {
-      if (tensor) return umma_conv_wgrad(g, dY, X, dW, m->template at<float>(wg_scratch), wg_bytes, st);
+      if (tensor) {
+        m->launches++;  // split-K reduce
+        return umma_conv_wgrad(g, dY, X, dW, m->template at<float>(wg_scratch), wg_bytes, st, torch_layout);
+      }
     }
     return simt_conv_wgrad<T>(g, dY, X, dW, st);
   }
+  bool umma_path() const { return std::is_same<T, bf16>::value && tensor; }
   static EpiParams epi(void* out, int ldo, const float* bias = nullptr, int mode = EPI_NONE, int out_f32 = 0) {
     EpiParams e{};
     e.bias = bias; e.out = out; e.ldo = ldo; e.mode = mode; e.out_f32 = out_f32; e.alpha = 1.f;
@@ -183,10 +188,14 @@ struct Builder {
         S4G_TRY(self->fprop(conv3_geom(a.B, a.H, a.W, c.Co, c.Ci), self->G(out), mm->template at<T>(c.wd), e, st));
       }
       if (c.w->g) {
-        float* dwp = mm->template at<float>(self->dwp_scratch);
-        S4G_TRY(self->wgrad(g, self->G(out), self->V(in), dwp, st));
-        mm->launches++;
-        S4G_TRY(k_unpack_conv_grad(dwp, c.w->g, c.Co, c.Ci, 3, st));
+        if (self->umma_path()) {
+          S4G_TRY(self->wgrad(g, self->G(out), self->V(in), c.w->g, st, 1));
+        } else {
+          float* dwp = mm->template at<float>(self->dwp_scratch);
+          S4G_TRY(self->wgrad(g, self->G(out), self->V(in), dwp, st));
+          mm->launches++;
+          S4G_TRY(k_unpack_conv_grad(dwp, c.w->g, c.Co, c.Ci, 3, st));
+        }
       }
       if (c.b && c.b->g) {
         S4G_CUDA(cudaMemsetAsync(c.b->g, 0, sizeof(float) * c.Co, st));

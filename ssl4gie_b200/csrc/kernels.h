@@ -24,8 +24,9 @@ template <typename T> int simt_conv_wgrad(const ConvGeom& g, const T* dY, const 
 
 // ---- tcgen05 contractions (bf16 in, fp32 accumulate in TMEM): umma.cu
 int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiParams& e, cudaStream_t st);
+// dW layout: packed [Cout][tap][Cin] (torch_layout = 0) or torch's [Cout][Cin][R][S] (torch_layout = 1)
 int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW, float* scratch, size_t scratch_bytes,
-                    cudaStream_t st);
+                    cudaStream_t st, int torch_layout = 0);
 size_t umma_wgrad_scratch_bytes(const ConvGeom& g);
 int umma_init();
 

@@ -366,7 +366,8 @@ struct WgradParams {
   int Cout, Cin, K;  // K = taps * Cin (row length of dW)
   int tiles_co, tiles_ci, block_n, splits;
   int chunks_total;  // pixel chunks
-  float* dW;
+  int chunks_per_split;
+  float* part;       // split-K partials: [split][tap][tci][tco][block_n columns (ci)][128 rows (co)] fp32
 };
 
 __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmY,
@@ -380,7 +381,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int out_tiles = p.tiles_co * p.tiles_ci * p.taps;
   const int num_work = out_tiles * p.splits;
-  const int chunks_per_split = (p.chunks_total + p.splits - 1) / p.splits;
+  const int chunks_per_split = p.chunks_per_split;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmY);
@@ -464,7 +465,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
       decode(wi, split, tap, tci, tco);
       const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
       if (c_begin >= c_end) continue;
-      const int co = tco * 128 + q * 32 + lane;
+      // partial tile, column-major (co contiguous): each store instruction of a warp writes 128 contiguous bytes
+      float* part = p.part + (size_t)wi * 128 * p.block_n + q * 32 + lane;
       mbar_wait(&ctl->tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
@@ -472,11 +474,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
-        const int ci0 = tci * p.block_n + c0;
-        if (co < p.Cout && ci0 < p.Cin) {
-          float* dst = p.dW + (long long)co * p.K + (long long)tap * p.Cin + ci0;
-          const int ncols = min(32, p.Cin - ci0);
-          for (int i = 0; i < ncols; ++i) atomicAdd(dst + i, __uint_as_float(v[i]));
+        if (tci * p.block_n + c0 < p.Cin) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) part[(size_t)(c0 + i) * 128] = __uint_as_float(v[i]);
         }
       }
       tc_fence_before();
@@ -488,6 +488,41 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// Deterministic split-K reduction + layout change: dW[co*so + ci*si + tap*st] = sum_split part[split][tap][tci][tco][ci][co]
+struct WgradReduceParams {
+  const float* part;
+  float* dW;
+  int Cout, Cin, taps, tiles_co, tiles_ci, block_n, splits;
+  long long so, si, st;
+};
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReduceParams p) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
+  const int co0 = blockIdx.x * 32, ci0 = blockIdx.y * 32, tap = blockIdx.z;
+  const int tco = co0 >> 7, tci = ci0 / p.block_n;
+  const size_t tile_elems = (size_t)128 * p.block_n;
+  const size_t split_stride = (size_t)p.taps * p.tiles_ci * p.tiles_co * tile_elems;
+  const float* base = p.part + (((size_t)tap * p.tiles_ci + tci) * p.tiles_co + tco) * tile_elems + (co0 & 127) + tx;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int cil = ty + j * 8;                       // ci within this 32-block
+    const int col = ci0 - tci * p.block_n + cil;      // column inside the tile
+    float acc = 0.f;
+    if (ci0 + cil < p.Cin) {
+      const float* src = base + (size_t)col * 128;
+      for (int s = 0; s < p.splits; ++s) acc += src[(size_t)s * split_stride];
+    }
+    tile[cil][tx] = acc;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int col = ty + j * 8;                       // co within the 32-block
+    const int co = co0 + col, ci = ci0 + tx;
+    if (co < p.Cout && ci < p.Cin) p.dW[co * p.so + ci * p.si + tap * p.st] = tile[tx][col];
+  }
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -611,35 +646,80 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
   return 0;
 }
 
-size_t umma_wgrad_scratch_bytes(const ConvGeom&) { return 0; }
+namespace {
+struct WgradPlan {
+  TileGeom tg;
+  int block_n, tiles_co, tiles_ci, out_tiles, chunks_total, splits, cps;
+  size_t scratch_bytes;
+};
+// Split-K plan: enough (output tile x pixel range) work items to fill the SMs in whole waves, few enough that the
+// fp32 partials (written once, read once by the reduce kernel) stay cheap.
+WgradPlan plan_wgrad(const ConvGeom& g) {
+  WgradPlan w;
+  const bool matrix = g.Hi == 1 && g.Wi == 1;
+  w.tg = matrix ? matrix_tiles(g.Nimg, BLOCK_K) : make_tiles(g.Nimg, g.Hi, g.Wi, BLOCK_K);
+  const int taps = g.R * g.S;
+  w.block_n = std::min(256, (g.Cin + 63) / 64 * 64);
+  w.tiles_co = cdiv(g.Cout, 128);
+  w.tiles_ci = cdiv(g.Cin, w.block_n);
+  w.out_tiles = w.tiles_co * w.tiles_ci * taps;
+  w.chunks_total = w.tg.tw * w.tg.th * w.tg.tn;
+  const double t_chunk = 0.0014 * w.block_n;                       // us per 64-pixel chunk (4 MMAs of 128 x block_n x 16)
+  const double tile_bytes = 128.0 * w.block_n * 4;
+  double best = 1e30;
+  w.splits = 1; w.cps = w.chunks_total;
+  for (int s = 1; s <= std::min(w.chunks_total, 256); ++s) {
+    const int cps = cdiv(w.chunks_total, s);
+    const int se = cdiv(w.chunks_total, cps);
+    if (se != s) continue;
+    const long long items = (long long)w.out_tiles * se;
+    const long long rounds = (items + g_num_sms - 1) / g_num_sms;
+    const double t = rounds * (cps * t_chunk + 2.0) + items * tile_bytes * 2 / 3.0e6;
+    if (t < best) { best = t; w.splits = se; w.cps = cps; }
+  }
+  w.scratch_bytes = (size_t)w.out_tiles * w.splits * 128 * w.block_n * sizeof(float);
+  return w;
+}
+}  // namespace
 
-int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW, float*, size_t, cudaStream_t st) {
+size_t umma_wgrad_scratch_bytes(const ConvGeom& g) {
+  if (umma_init() != 0) return 0;
+  return plan_wgrad(g).scratch_bytes;
+}
+
+int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW, float* scratch, size_t scratch_bytes,
+                    cudaStream_t st, int torch_layout) {
   S4G_TRY(umma_init());
   if (g.stride != 1 || g.Ho != g.Hi || g.Wo != g.Wi) { s4g_set_error("umma_conv_wgrad: stride-1 'same' convolutions only"); return S4G_ERR_SHAPE; }
   if (g.Cin % 8 || g.ldx % 8 || g.Cout % 8 || g.ldy % 8) { s4g_set_error("umma_conv_wgrad: channel counts must be multiples of 8"); return S4G_ERR_SHAPE; }
   const bool matrix = g.Hi == 1 && g.Wi == 1;
+  const WgradPlan w = plan_wgrad(g);
+  if (!scratch || scratch_bytes < w.scratch_bytes) { s4g_set_error("umma_conv_wgrad: split-K scratch too small (see s4g_wgrad_scratch_bytes)"); return S4G_ERR_WORKSPACE; }
   WgradParams p{};
-  p.tg = matrix ? matrix_tiles(g.Nimg, BLOCK_K) : make_tiles(g.Nimg, g.Hi, g.Wi, BLOCK_K);
+  p.tg = w.tg;
   p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
   p.Cout = g.Cout; p.Cin = g.Cin; p.K = p.taps * g.Cin;
-  p.block_n = std::min(256, (g.Cin + 63) / 64 * 64);
-  p.tiles_co = cdiv(g.Cout, 128);
-  p.tiles_ci = cdiv(g.Cin, p.block_n);
-  p.chunks_total = p.tg.tw * p.tg.th * p.tg.tn;
-  const int out_tiles = p.tiles_co * p.tiles_ci * p.taps;
-  p.splits = std::max(1, std::min(p.chunks_total, (2 * g_num_sms + out_tiles - 1) / out_tiles));
-  // re-balance so that no split is empty
-  const int cps = cdiv(p.chunks_total, p.splits);
-  p.splits = cdiv(p.chunks_total, cps);
-  p.dW = dW;
+  p.block_n = w.block_n;
+  p.tiles_co = w.tiles_co;
+  p.tiles_ci = w.tiles_ci;
+  p.chunks_total = w.chunks_total;
+  p.splits = w.splits;
+  p.chunks_per_split = w.cps;
+  p.part = scratch;
   CUtensorMap tmY, tmX;
-  ConvGeom gy = g;
-  S4G_TRY(make_act_map(&tmY, dY, gy, g.Cout, g.ldy, p.tg, matrix, g.Hi, g.Wi));
+  S4G_TRY(make_act_map(&tmY, dY, g, g.Cout, g.ldy, p.tg, matrix, g.Hi, g.Wi));
   S4G_TRY(make_act_map(&tmX, X, g, g.Cin, g.ldx, p.tg, matrix, g.Hi, g.Wi));
-  S4G_CUDA(cudaMemsetAsync(dW, 0, sizeof(float) * (size_t)g.Cout * p.K, st));
   const size_t smem = 1024 + (size_t)STAGES * (2 * BLOCK_K * 128 + (p.block_n / 64) * BLOCK_K * 128) + sizeof(SmemCtl);
-  const int grid = std::min(out_tiles * p.splits, g_num_sms);
+  const int grid = std::min(w.out_tiles * p.splits, g_num_sms);
   umma_wgrad_kernel<<<grid, NUM_THREADS, smem, st>>>(tmY, tmX, p);
+  S4G_KERNEL_CHECK();
+  WgradReduceParams r{};
+  r.part = scratch; r.dW = dW;
+  r.Cout = g.Cout; r.Cin = g.Cin; r.taps = p.taps; r.tiles_co = p.tiles_co; r.tiles_ci = p.tiles_ci; r.block_n = p.block_n;
+  r.splits = p.splits;
+  if (torch_layout) { r.so = (long long)g.Cin * p.taps; r.si = p.taps; r.st = 1; }   // [Cout][Cin][R][S]
+  else { r.so = p.K; r.si = 1; r.st = g.Cin; }                                        // packed [Cout][tap][Cin]
+  wgrad_reduce_kernel<<<dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps), dim3(32, 8), 0, st>>>(r);
   S4G_KERNEL_CHECK();
   return 0;
 }

@@ -78,11 +78,12 @@ def test_fp32_step_matches_golden(dense, golden_dir):
         assert g is not None, n
         gn = g.double().norm().item()
         rn = float(fix["grad_norm"][i])
-        if dense == "depth" and n == "decoder.output_conv.4.bias":
-            # sum of ~1e5 cancelling terms (the SSI loss is shift invariant, sigmoid' ~ const at init): the fp64 oracle
-            # gives -4.2e-8, the reference's own fp32 run -6.8e-6 — the fixture value is rounding noise, so only the
-            # magnitude is checked
-            assert gn < 2e-5, gn
+        if dense == "depth" and n.startswith("decoder.output_conv.4."):
+            # sums of ~1e5 cancelling terms (the SSI loss is shift invariant and sigmoid' ~ const at init): for the bias
+            # the fp64 oracle gives -4.2e-8 where the reference's own fp32 run gives -6.8e-6, and its fp32 weight
+            # gradient is 70% off the fp64 one — these two fixture entries are rounding noise, so only the magnitude
+            # is checked here (the tight check is against the fp64 oracle in the next test)
+            assert gn < 5 * max(rn, 1e-5), (n, gn, rn)
             continue
         # gradients that are analytically ~0 (the last bias under the shift-invariant depth loss) are rounding noise
         # on both sides: measure against a floor tied to the typical gradient scale
