@@ -19,7 +19,8 @@ if which in ("all", "wgrad"):
     for (M, N, K) in [(64, 128, 64), (128, 128, 64), (394, 2304, 768), (12608, 768, 768), (6272, 1536, 96), (500, 32, 128)]:
         dY = torch.randn(M, N, generator=g).cuda().bfloat16(); X = torch.randn(M, K, generator=g).cuda().bfloat16()
         dW = torch.empty(N, K, device="cuda")
-        C.check(C.lib().s4g_linear_wgrad(C.ptr(dY), C.ptr(X), C.ptr(dW), M, N, K, C.BF16, C.TENSOR, None, 0, C.stream_ptr()))
+        nb = C.lib().s4g_wgrad_scratch_bytes(M, 1, 1, K, N, 1); sc = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        C.check(C.lib().s4g_linear_wgrad(C.ptr(dY), C.ptr(X), C.ptr(dW), M, N, K, C.BF16, C.TENSOR, C.ptr(sc), nb, C.stream_ptr()))
         torch.cuda.synchronize()
         ref = dY.float().t() @ X.float()
         print("linear_wgrad", M, N, K, "rel", rel(dW, ref), flush=True)
@@ -37,6 +38,7 @@ if which in ("all", "conv"):
         dw_ref = torch.nn.grad.conv2d_weight(x, w.shape, dy, padding=1)
         dyn = dy.permute(0, 2, 3, 1).contiguous().bfloat16()
         dwp = torch.empty(Cout, 3, 3, Cin, device="cuda")
-        C.check(C.lib().s4g_conv3x3_wgrad(C.ptr(dyn), C.ptr(xn), C.ptr(dwp), B, H, H, Cin, Cout, C.BF16, C.TENSOR, None, 0, C.stream_ptr()))
+        nb = C.lib().s4g_wgrad_scratch_bytes(B, H, H, Cin, Cout, 9); sc = torch.empty(nb, dtype=torch.uint8, device="cuda")
+        C.check(C.lib().s4g_conv3x3_wgrad(C.ptr(dyn), C.ptr(xn), C.ptr(dwp), B, H, H, Cin, Cout, C.BF16, C.TENSOR, C.ptr(sc), nb, C.stream_ptr()))
         torch.cuda.synchronize()
         print("conv_wgrad", B, H, Cin, Cout, "rel", rel(dwp.permute(0, 3, 1, 2), dw_ref), flush=True)

@@ -65,6 +65,15 @@ __device__ __forceinline__ void tma_load_3d(const CUtensorMap* m, uint64_t* bar,
       ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
@@ -145,8 +154,12 @@ struct FpropParams {
   TileGeom tg;
   int taps, S, pad, chunks;  // chunks = ceil(Cin / 64)
   int tiles_m, tiles_n, block_n, N;
+  int tma_epi;       // 1: bf16 outputs staged in swizzled smem and written with TMA stores
+  long long M;       // rows of the output matrix (for the aux read guard)
   EpiParams e;
 };
+
+constexpr int EPI_STAGE_BYTES = 128 * 128;  // one 128-row x 64-column bf16 slab, SWIZZLE_128B
 
 // 32 consecutive columns of one output row
 __device__ __forceinline__ void epi_row32(const EpiParams& e, long long row, int col0, int ncols, const uint32_t (&acc)[32]) {
@@ -250,12 +263,15 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
 
 // =========================================================================================== fprop
 __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                                    const __grid_constant__ CUtensorMap tmB, const FpropParams p) {
+                                                                    const __grid_constant__ CUtensorMap tmB,
+                                                                    const __grid_constant__ CUtensorMap tmO,
+                                                                    const __grid_constant__ CUtensorMap tmO2, const FpropParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
   const int b_stage_bytes = p.block_n * 128;
   const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
-  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + STAGES * stage_bytes);
+  uint8_t* epi_smem = smem + STAGES * stage_bytes;  // 2 x EPI_STAGE_BYTES (1024 B aligned: stage sizes are multiples of 2 KB)
+  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(epi_smem + 2 * EPI_STAGE_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int k_iters = p.taps * p.chunks;
@@ -263,6 +279,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (p.tma_epi) { tma_prefetch_desc(&tmO); if (p.e.out2) tma_prefetch_desc(&tmO2); }
     for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4); }
     fence_barrier_init();
@@ -328,6 +345,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
     const int q = warp & 3;  // TMEM lane quarter this warp may touch
     const int r = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
+    uint32_t epi_count = 0;
     const TileGeom& t = p.tg;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
@@ -340,19 +358,105 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
       mbar_wait(&ctl->tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
-      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c0, v);
-        tmem_ld_wait();
-        const int col0 = tn * p.block_n + c0;
-        const int ncols = min(32, p.N - col0);
-        if (valid && ncols > 0) epi_row32(p.e, row, col0, ncols, v);
+      if (p.tma_epi) {
+        // bf16 outputs: each warp stages its own 32 rows x 64 columns in a private 128B-swizzled smem slab and writes
+        // it with its own TMA store (which clips the M / N tails) -- no cross-warp synchronisation in the epilogue
+        const int npass = p.e.out2 ? 2 : 1;
+        const int nslabs = (p.block_n + 63) >> 6;
+        const int rl = lane;  // row inside this warp's slab
+        for (int sl = 0; sl < nslabs; ++sl) {
+          for (int pass = 0; pass < npass; ++pass) {
+            uint8_t* buf = epi_smem + (q * 2 + (epi_count & 1)) * (EPI_STAGE_BYTES / 4);
+            if (lane == 0) tma_store_wait_read<1>();  // the store that last read this buffer is done with it
+            __syncwarp();
+            const bool pre = p.e.out2 && pass == 0;  // pre-activation copy
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              uint32_t v[32];
+              tmem_ld32(taddr + sl * 64 + half * 32, v);
+              tmem_ld_wait();
+              if (sl == nslabs - 1 && pass == npass - 1 && half == 1) {
+                // accumulator fully read: hand the TMEM stage back to the MMA warp before the stores
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+              }
+              const int col0 = tn * p.block_n + sl * 64 + half * 32;
+              const int ncols = p.N - col0;
+              float f[32];
+#pragma unroll
+              for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * p.e.alpha;
+              if (p.e.bias) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                  if (i < ncols) {
+                    const float4 bb = *reinterpret_cast<const float4*>(p.e.bias + col0 + i);
+                    f[i] += bb.x; f[i + 1] += bb.y; f[i + 2] += bb.z; f[i + 3] += bb.w;
+                  }
+                }
+              }
+              if (!pre) {
+                if (p.e.mode == EPI_GELU) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) f[i] = gelu_f(f[i]);
+                } else if (p.e.mode == EPI_RELU) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+                } else if (p.e.mode == EPI_DGELU) {
+                  if (valid) {
+                    const bf16* pa = reinterpret_cast<const bf16*>(p.e.aux) + row * p.e.ldo + col0;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 8) {
+                      if (i < ncols) {
+                        Vec8<bf16> t8;
+                        t8.load(pa + i);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) f[i + k] *= dgelu_f(t8.v[k]);
+                      }
+                    }
+                  }
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint4 pk;
+                __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) h2[k] = __floats2bfloat162_rn(f[j * 8 + 2 * k], f[j * 8 + 2 * k + 1]);
+                const int chunk = half * 4 + j;
+                *reinterpret_cast<uint4*>(buf + rl * 128 + ((chunk ^ (rl & 7)) << 4)) = pk;
+              }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              const int cc = tn * p.block_n + sl * 64;
+              if (cc < p.N) {
+                // origin of this warp's 32-row sub-box inside the tile
+                const int r0 = q * 32;
+                tma_store_4d(pre ? &tmO2 : &tmO, buf, cc, w0 + r0 % t.bw, h0 + (r0 / t.bw) % t.bh, n0 + r0 / (t.bw * t.bh));
+                tma_store_commit();
+              }
+            }
+            ++epi_count;
+          }
+        }
+      } else {
+        for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c0, v);
+          tmem_ld_wait();
+          const int col0 = tn * p.block_n + c0;
+          const int ncols = min(32, p.N - col0);
+          if (valid && ncols > 0) epi_row32(p.e, row, col0, ncols, v);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (p.tma_epi && lane == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -577,16 +681,25 @@ TileGeom matrix_tiles(long long M, int rows) {
   return t;
 }
 // activation tensor map: NHWC [Nimg,H,W,C] (row stride ld) -> dims {C, W, H, N}; plain matrix [M, C] -> {C, M, 1, 1}
-int make_act_map(CUtensorMap* map, const bf16* base, const ConvGeom& g, int C, int ld, const TileGeom& t, bool matrix, int H, int W) {
+// rows_div = 4: the box covers a quarter (32 consecutive rows) of the tile -- the per-warp epilogue store box
+int make_act_map(CUtensorMap* map, const bf16* base, const ConvGeom& g, int C, int ld, const TileGeom& t, bool matrix, int H, int W,
+                 int rows_div = 1) {
   uint64_t dims[4], strides[3]; uint32_t box[4];
+  int bw = t.bw, bh = t.bh, bn = t.bn;
+  if (rows_div > 1) {
+    const int rows = bw * bh * bn / rows_div;
+    bw = std::min(bw, rows);
+    bh = std::min(bh, rows / bw);
+    bn = rows / (bw * bh);
+  }
   if (matrix) {
     dims[0] = C; dims[1] = (uint64_t)g.Nimg * H * W; dims[2] = 1; dims[3] = 1;
     strides[0] = (uint64_t)ld * 2; strides[1] = strides[0] * dims[1]; strides[2] = strides[1];
-    box[0] = 64; box[1] = t.bw; box[2] = 1; box[3] = 1;
+    box[0] = 64; box[1] = bw; box[2] = 1; box[3] = 1;
   } else {
     dims[0] = C; dims[1] = W; dims[2] = H; dims[3] = g.Nimg;
     strides[0] = (uint64_t)ld * 2; strides[1] = strides[0] * W; strides[2] = strides[1] * H;
-    box[0] = 64; box[1] = t.bw; box[2] = t.bh; box[3] = t.bn;
+    box[0] = 64; box[1] = bw; box[2] = bh; box[3] = bn;
   }
   return make_map(map, base, 4, dims, strides, box);
 }
@@ -639,9 +752,17 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     uint32_t box[3] = {64, 1, (uint32_t)p.block_n};
     S4G_TRY(make_map(&tmB, W, 3, dims, strides, box));
   }
-  const size_t smem = 1024 + (size_t)STAGES * (A_STAGE_BYTES + p.block_n * 128) + sizeof(SmemCtl);
+  p.M = (long long)g.Nimg * g.Hi * g.Wi;
+  p.tma_epi = !(e.out_f32 || e.res || e.accumulate) && e.ldo % 8 == 0 && (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 &&
+              (!e.out2 || (reinterpret_cast<uintptr_t>(e.out2) & 15) == 0);
+  CUtensorMap tmO = tmA, tmO2 = tmA;
+  if (p.tma_epi) {
+    S4G_TRY(make_act_map(&tmO, reinterpret_cast<const bf16*>(e.out), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
+    if (e.out2) S4G_TRY(make_act_map(&tmO2, reinterpret_cast<const bf16*>(e.out2), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
+  }
+  const size_t smem = 1024 + (size_t)STAGES * (A_STAGE_BYTES + p.block_n * 128) + 2 * EPI_STAGE_BYTES + sizeof(SmemCtl);
   const int grid = std::min(p.tiles_m * p.tiles_n, g_num_sms);
-  umma_fprop_kernel<<<grid, NUM_THREADS, smem, st>>>(tmA, tmB, p);
+  umma_fprop_kernel<<<grid, NUM_THREADS, smem, st>>>(tmA, tmB, tmO, tmO2, p);
   S4G_KERNEL_CHECK();
   return 0;
 }
