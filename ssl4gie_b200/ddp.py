@@ -13,6 +13,31 @@ import torch.distributed as dist
 from .engine import Engine
 
 
+def bucket_slices(names_by_bucket, offsets):
+    """Contiguous [lo, hi) float ranges of the flat gradient arena covered by each bucket.
+    names_by_bucket: list of parameter-name lists; offsets: name -> (offset, numel) in floats."""
+    slices = []
+    for names in names_by_bucket:
+        if not names:
+            slices.append(None)
+            continue
+        lo = min(offsets[n][0] for n in names)
+        hi = max(offsets[n][0] + offsets[n][1] for n in names)
+        slices.append((lo, hi))
+    return slices
+
+
+def allreduce_buckets(flat, slices, group=None, events=None, comm_stream=None):
+    """Sum-all-reduce every bucket slice of `flat` (in place).  On CUDA each bucket waits for its event on the
+    communication stream; on CPU (gloo, used by the tests) the calls are issued in order."""
+    for i, sl in enumerate(slices):
+        if sl is None:
+            continue
+        if events is not None and comm_stream is not None:
+            comm_stream.wait_event(events[i])
+        dist.all_reduce(flat[sl[0]:sl[1]], group=group)
+
+
 class GradientAllReduce:
     def __init__(self, model, n_buckets=5, process_group=None):
         core = model.module if hasattr(model, "module") else model
@@ -33,15 +58,7 @@ class GradientAllReduce:
         base = e.flat_grads.data_ptr()
         for n, g in e.grad_views.items():
             offs[n] = ((g.data_ptr() - base) // 4, g.numel())
-        self.slices = []
-        for i in range(self.n_buckets):
-            names = handle.bucket_params(i, self.n_buckets)
-            if not names:
-                self.slices.append(None)
-                continue
-            lo = min(offs[n][0] for n in names)
-            hi = max(offs[n][0] + offs[n][1] for n in names)
-            self.slices.append((lo, hi))
+        self.slices = bucket_slices([handle.bucket_params(i, self.n_buckets) for i in range(self.n_buckets)], offs)
         if e.flat_grads.is_cuda:
             self.comm_stream = torch.cuda.Stream()
             self.events = [torch.cuda.Event() for _ in range(self.n_buckets)]
@@ -62,9 +79,5 @@ class GradientAllReduce:
         flat = self.engine.flat_grads
         cur = torch.cuda.current_stream()
         with torch.cuda.stream(self.comm_stream):
-            for ev, sl in zip(self.events, self.slices):
-                if sl is None:
-                    continue
-                self.comm_stream.wait_event(ev)
-                dist.all_reduce(flat[sl[0]:sl[1]], group=self.group)
+            allreduce_buckets(flat, self.slices, self.group, self.events, self.comm_stream)
         cur.wait_stream(self.comm_stream)

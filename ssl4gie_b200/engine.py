@@ -19,6 +19,23 @@ def _unused_in_dense(name):
     return name.startswith("norm.") or name.startswith("decoder.refinenet4.resConfUnit1.")
 
 
+def arena_layout(model):
+    """Pure host logic (no CUDA): placement of every parameter in the flat fp32 arena.  Parameters that receive a
+    gradient come first (their offsets are also the offsets in the flat gradient arena), every slot is padded to
+    256 B.  Returns (offsets: name -> (offset, numel) in floats, n_active, total)."""
+    named = list(model.named_parameters())
+    e = Engine.__new__(Engine)
+    active = [(n, p) for n, p in named if Engine.produces_grad(e, n, p, model)]
+    inactive = [(n, p) for n, p in named if not Engine.produces_grad(e, n, p, model)]
+    offsets, off, n_active = {}, 0, 0
+    for i, (n, p) in enumerate(active + inactive):
+        offsets[n] = (off, p.numel())
+        off += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
+        if i == len(active) - 1:
+            n_active = off
+    return offsets, n_active, off
+
+
 class Engine:
     _registry = weakref.WeakKeyDictionary()
 
@@ -78,28 +95,20 @@ class Engine:
         for _, p in named:
             if p.dtype != torch.float32:
                 raise RuntimeError("ssl4gie_b200 keeps fp32 master parameters; do not .half()/.bfloat16() the model")
-        active = [(n, p) for n, p in named if self.produces_grad(n, p, model)]
-        inactive = [(n, p) for n, p in named if not self.produces_grad(n, p, model)]
-
-        def padded(p):
-            return (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
-
-        n_active = sum(padded(p) for _, p in active)
-        total = n_active + sum(padded(p) for _, p in inactive)
+        offsets, n_active, total = arena_layout(model)
         flat = torch.zeros(total, dtype=torch.float32, device=dev)
         grads = torch.zeros(n_active, dtype=torch.float32, device=dev)
-        off = 0
         self.views, self.grad_views = {}, {}
-        for n, p in active + inactive:
+        for n, p in named:
+            off = offsets[n][0]
             v = flat[off:off + p.numel()].view_as(p)
             v.copy_(p.data)
             p.data = v
             self.views[n] = v
             if off < n_active:
                 self.grad_views[n] = grads[off:off + p.numel()].view_as(p)
-            off += padded(p)
         self.flat_params, self.flat_grads, self.n_active = flat, grads, n_active
-        self.active_names = [n for n, _ in active]
+        self.active_names = [n for n, _ in named if offsets[n][0] < n_active]
         for h in self.handles.values():
             h.destroy()
         self.handles = {}
