@@ -2,6 +2,8 @@
 // adds, pixel (un)shuffle for k==s transposed convs, stride-2 im2col, bilinear x2 (align_corners=True),
 // BatchNorm (train) statistics / apply / backward, the two head tails, weight packing.
 // All NHWC kernels move 8 channels per thread (16 B bf16 / 32 B fp32), coalesced along C.
+#include <algorithm>
+
 #include "kernels.h"
 
 #define GRID1D(n, bs) dim3((unsigned)min((long long)cdiv((n), (bs)), (long long)148 * 32)), dim3(bs)
@@ -71,6 +73,22 @@ int k_assemble_tokens_bwd(const float* dx, float* dpe, float* dcls, float* dpos,
   return 0;
 }
 
+// 4 consecutive elements of T <-> float4
+__device__ __forceinline__ float4 load4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 load4(const bf16* p) {
+  const uint2 r = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void store4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void store4(bf16* p, float4 v) {
+  uint2 r;
+  *reinterpret_cast<__nv_bfloat162*>(&r.x) = __floats2bfloat162_rn(v.x, v.y);
+  *reinterpret_cast<__nv_bfloat162*>(&r.y) = __floats2bfloat162_rn(v.z, v.w);
+  *reinterpret_cast<uint2*>(p) = r;
+}
+
 // ------------------------------------------------------------------------------------------ LayerNorm
 // one warp per token row, fp32 statistics (two-pass in registers), T output
 template <typename T, int C>
@@ -99,11 +117,8 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const float* __restr
   for (int i = 0; i < V; ++i) {
     const int c4 = lane + 32 * i;
     const float4 g = reinterpret_cast<const float4*>(gamma)[c4], b = reinterpret_cast<const float4*>(beta)[c4];
-    T* o = y + (long long)row * C + c4 * 4;
-    o[0] = from_f<T>((v[i].x - mu) * rs * g.x + b.x);
-    o[1] = from_f<T>((v[i].y - mu) * rs * g.y + b.y);
-    o[2] = from_f<T>((v[i].z - mu) * rs * g.z + b.z);
-    o[3] = from_f<T>((v[i].w - mu) * rs * g.w + b.w);
+    store4(y + (long long)row * C + c4 * 4, make_float4((v[i].x - mu) * rs * g.x + b.x, (v[i].y - mu) * rs * g.y + b.y,
+                                                        (v[i].z - mu) * rs * g.z + b.z, (v[i].w - mu) * rs * g.w + b.w));
   }
 }
 template <typename T>
@@ -124,7 +139,7 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
                                                             const float* __restrict__ dres, float* __restrict__ dx,
                                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                            int rows, int rows_per_block) {
+                                                            int rows, int rows_per_block, T* __restrict__ dx_cast) {
   constexpr int V = C / 128;
   __shared__ float sg[C], sb[C];
   for (int i = threadIdx.x; i < C; i += 256) { sg[i] = 0.f; sb[i] = 0.f; }
@@ -146,7 +161,8 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
       const int c4 = lane + 32 * i;
       const float4 xv = xr[c4];
       const float4 gm = reinterpret_cast<const float4*>(gamma)[c4];
-      const float d0 = to_f(dyr[c4 * 4]), d1 = to_f(dyr[c4 * 4 + 1]), d2 = to_f(dyr[c4 * 4 + 2]), d3 = to_f(dyr[c4 * 4 + 3]);
+      const float4 dq = load4(dyr + c4 * 4);
+      const float d0 = dq.x, d1 = dq.y, d2 = dq.z, d3 = dq.w;
       xh[i] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
       g[i] = make_float4(d0 * gm.x, d1 * gm.y, d2 * gm.z, d3 * gm.w);
       s1 += g[i].x + g[i].y + g[i].z + g[i].w;
@@ -166,6 +182,7 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
         o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
       }
       reinterpret_cast<float4*>(dx + (long long)row * C)[c4] = o;
+      if (dx_cast) store4(dx_cast + (long long)row * C + c4 * 4, o);
     }
   }
 #pragma unroll
@@ -179,12 +196,12 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
 }
 template <typename T>
 int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
-                    const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st) {
+                    const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st, T* dx_cast) {
   const int rpb = max(8, cdiv(rows, 148 * 4));
   if (C == 768)
-    layernorm_bwd_kernel<T, 768><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb);
+    layernorm_bwd_kernel<T, 768><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast);
   else if (C == 512)
-    layernorm_bwd_kernel<T, 512><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb);
+    layernorm_bwd_kernel<T, 512><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast);
   else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
   S4G_KERNEL_CHECK();
   return 0;
@@ -206,25 +223,51 @@ template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long
   return 0;
 }
 
-// column sums of a [M, N] matrix (bias gradients); out must be zeroed; 32 cols x 8 row-lanes per block
-template <typename T> __global__ void colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, long long M, int N, int ld, int rows_per_block) {
-  __shared__ float red[8][33];
-  const int col = blockIdx.x * 32 + (threadIdx.x & 31), rl = threadIdx.x >> 5;
+// column sums of a [M, N] matrix (bias gradients); out must be zeroed.  Block = 32 column groups (8 columns, one
+// 16 B load each) x 8 row lanes, rows walked with a 4-deep unroll; one atomic per column per block.
+template <typename T> __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, long long M, int N, int ld, long long rows_per_block) {
+  __shared__ float red[8][256 + 8];
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + cg * 8;
   const long long r0 = (long long)blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
-  float s = 0.f;
-  if (col < N)
-    for (long long r = r0 + rl; r < r1; r += 8) s += to_f(dy[r * ld + col]);
-  red[rl][threadIdx.x & 31] = s;
-  __syncthreads();
-  if (rl == 0 && col < N) {
+  float s[8];
 #pragma unroll
-    for (int i = 1; i < 8; ++i) s += red[i][threadIdx.x];
-    atomicAdd(&out[col], s);
+  for (int i = 0; i < 8; ++i) s[i] = 0.f;
+  if (col < N) {
+    for (long long rb = r0 + rl; rb < r1; rb += 32) {
+      Vec8<T> v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long r = rb + u * 8;
+        if (r < r1) v[u].load(dy + r * ld + col);
+        else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[u].v[i] = 0.f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] += v[u].v[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[rl][cg * 8 + i] = s[i];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    atomicAdd(&out[c], t);
   }
 }
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st) {
-  const int rpb = (int)max((long long)64, (M + 147) / 148);
-  dim3 grid(cdiv(N, 32), cdiv(M, rpb));
+  if (N % 8 || ld % 8) { s4g_set_error("colsum: N and ld must be multiples of 8"); return S4G_ERR_SHAPE; }
+  const int gx = cdiv(N, 256);
+  const long long want = std::max<long long>(1, (148 * 4) / gx);
+  const long long rpb = std::max<long long>(64, (M + want - 1) / want);
+  dim3 grid(gx, cdiv(M, rpb));
   colsum_kernel<T><<<grid, 256, 0, st>>>(dy, out, M, N, ld, rpb);
   S4G_KERNEL_CHECK();
   return 0;
@@ -250,7 +293,7 @@ template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaSt
   S4G_KERNEL_CHECK();
   return 0;
 }
-template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap, float* __restrict__ dx, int B, int accumulate) {
+template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap, float* __restrict__ dx, int B, int accumulate, T* __restrict__ cast_out) {
   const long long n = (long long)B * 197 * 96;
   FOR_GRID(t, n) {
     const int g = (int)(t % 96);
@@ -268,14 +311,20 @@ template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap
       v.load(dtap + ((long long)b * 196 + tok - 1) * 768 + g * 8);
 #pragma unroll
       for (int k = 0; k < 8; ++k) o.v[k] += v.v[k];
-    } else if (accumulate) {
+    } else if (accumulate && !cast_out) {
       continue;
     }
     o.store(d);
+    if (cast_out) {
+      Vec8<T> c;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) c.v[k] = o.v[k];
+      c.store(cast_out + row * 768 + g * 8);
+    }
   }
 }
-template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st) {
-  tap_grad_kernel<T><<<GRID1D((long long)B * 197 * 96, 256), 0, st>>>(dtap, dx, B, accumulate);
+template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out) {
+  tap_grad_kernel<T><<<GRID1D((long long)B * 197 * 96, 256), 0, st>>>(dtap, dx, B, accumulate, cast_out);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -585,22 +634,33 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const T* __restrict__ a,
     s1[i] = 0.f; s2[i] = 0.f;
     if (BWD) { mu[i] = mean[g * 8 + i]; rs[i] = rstd[g * 8 + i]; gm[i] = gamma[g * 8 + i]; bt[i] = beta[g * 8 + i]; }
   }
-  for (long long r = r0 + rl; r < r1; r += lanes) {
-    Vec8<T> v;
-    v.load(a + r * C + g * 8);
-    if (BWD) {
-      Vec8<T> xv;
-      xv.load(x + r * C + g * 8);
+  for (long long rb = r0 + rl; rb < r1; rb += 4 * lanes) {
+    Vec8<T> v[4], xv[4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float xh = (xv.v[i] - mu[i]) * rs[i];
-        float d = v.v[i];
-        if (relu && xh * gm[i] + bt[i] <= 0.f) d = 0.f;
-        s1[i] += d; s2[i] += d * xh;
+    for (int u = 0; u < 4; ++u) {
+      const long long r = rb + (long long)u * lanes;
+      if (r < r1) {
+        v[u].load(a + r * C + g * 8);
+        if (BWD) xv[u].load(x + r * C + g * 8);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { v[u].v[i] = 0.f; xv[u].v[i] = 0.f; }
       }
-    } else {
+    }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { s1[i] += v.v[i]; s2[i] += v.v[i] * v.v[i]; }
+    for (int u = 0; u < 4; ++u) {
+      if (BWD) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float xh = (xv[u].v[i] - mu[i]) * rs[i];
+          float d = v[u].v[i];
+          if (relu && xh * gm[i] + bt[i] <= 0.f) d = 0.f;
+          s1[i] += d; s2[i] += d * xh;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s1[i] += v[u].v[i]; s2[i] += v[u].v[i] * v[u].v[i]; }
+      }
     }
   }
   float* p1 = sm + (size_t)rl * C + g * 8;
@@ -663,64 +723,113 @@ int k_bn_eval_prepare(const float* rm, const float* rv, float* mean, float* rstd
   S4G_KERNEL_CHECK();
   return 0;
 }
+// Block = 256 threads = (C/8) channel groups x (2048/C) row lanes; a thread keeps its 8 channels' constants in
+// registers and walks rows with a 4-deep unroll (4 x 16 B loads in flight per operand).
 template <typename T>
-__global__ void bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
-                                const float* __restrict__ gamma, const float* __restrict__ beta, const T* __restrict__ skip,
-                                T* __restrict__ y, int relu, long long n8, int C) {
-  const int c8 = C / 8;
-  FOR_GRID(t, n8) {
-    const int g = (int)(t % c8);
-    Vec8<T> v, s;
-    v.load(x + t * 8);
-    if (skip) s.load(skip + t * 8);
+__global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ mean,
+                                                       const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                       const float* __restrict__ beta, const T* __restrict__ skip,
+                                                       T* __restrict__ y, int relu, long long M, int C) {
+  const int c8 = C / 8, lanes = 256 / c8;
+  const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
+  float sc[8], sh[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = g * 8 + i;
-      float o = (v.v[i] - mean[c]) * rstd[c] * gamma[c] + beta[c];
-      if (relu) o = fmaxf(o, 0.f);
-      if (skip) o += s.v[i];
-      v.v[i] = o;
-    }
-    v.store(y + t * 8);
+  for (int i = 0; i < 8; ++i) {
+    const int c = g * 8 + i;
+    sc[i] = rstd[c] * gamma[c];
+    sh[i] = beta[c] - mean[c] * sc[i];
   }
+  const long long stride = (long long)gridDim.x * lanes;
+  for (long long rb = (long long)blockIdx.x * lanes + rl; rb < M; rb += 4 * stride) {
+    Vec8<T> v[4], sk[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long r = rb + u * stride;
+      if (r < M) {
+        v[u].load(x + r * C + g * 8);
+        if (skip) sk[u].load(skip + r * C + g * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long r = rb + u * stride;
+      if (r < M) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float o = fmaf(v[u].v[i], sc[i], sh[i]);
+          if (relu) o = fmaxf(o, 0.f);
+          if (skip) o += sk[u].v[i];
+          v[u].v[i] = o;
+        }
+        v[u].store(y + r * C + g * 8);
+      }
+    }
+  }
+}
+static inline unsigned bn_grid(long long M, int C) {
+  const int lanes = 256 / (C / 8);
+  return (unsigned)std::min<long long>(cdiv(M, (long long)lanes * 4), 148 * 8);
 }
 template <typename T>
 int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta, const T* skip,
                T* y, int relu, long long M, int C, cudaStream_t st) {
-  bn_apply_kernel<T><<<GRID1D(M * C / 8, 256), 0, st>>>(x, mean, rstd, gamma, beta, skip, y, relu, M * C / 8, C);
+  if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
+  bn_apply_kernel<T><<<bn_grid(M, C), 256, 0, st>>>(x, mean, rstd, gamma, beta, skip, y, relu, M, C);
   S4G_KERNEL_CHECK();
   return 0;
 }
 // dx = gamma*rstd*(dy' - sum1/count - xhat*sum2/count); block 0 also writes dgamma = sum2, dbeta = sum1
 template <typename T>
-__global__ void bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean,
-                                    const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                    const float* __restrict__ beta, const double* __restrict__ sums, double count,
-                                    T* __restrict__ dx, float* dgamma, float* dbeta, int relu, long long n8, int C) {
-  const int c8 = C / 8;
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                           const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           const double* __restrict__ sums, double count,
+                                                           T* __restrict__ dx, float* dgamma, float* dbeta, int relu,
+                                                           long long M, int C) {
+  const int c8 = C / 8, lanes = 256 / c8;
+  const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
   if (blockIdx.x == 0 && dgamma)
     for (int c = threadIdx.x; c < C; c += blockDim.x) { dbeta[c] = (float)sums[c]; dgamma[c] = (float)sums[C + c]; }
   const float inv = (float)(1.0 / count);
-  FOR_GRID(t, n8) {
-    const int g = (int)(t % c8);
-    Vec8<T> d, xv;
-    d.load(dy + t * 8); xv.load(x + t * 8);
+  float mu[8], rs[8], gm[8], bt[8], k1[8], k2[8], k3[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = g * 8 + i;
-      const float xh = (xv.v[i] - mean[c]) * rstd[c];
-      float dd = d.v[i];
-      if (relu && xh * gamma[c] + beta[c] <= 0.f) dd = 0.f;
-      d.v[i] = gamma[c] * rstd[c] * (dd - (float)sums[c] * inv - xh * (float)sums[C + c] * inv);
+  for (int i = 0; i < 8; ++i) {
+    const int c = g * 8 + i;
+    mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c];
+    k1[i] = gm[i] * rs[i];
+    k2[i] = k1[i] * (float)sums[c] * inv;
+    k3[i] = k1[i] * (float)sums[C + c] * inv;
+  }
+  const long long stride = (long long)gridDim.x * lanes;
+  for (long long rb = (long long)blockIdx.x * lanes + rl; rb < M; rb += 4 * stride) {
+    Vec8<T> d[4], xv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long r = rb + u * stride;
+      if (r < M) { d[u].load(dy + r * C + g * 8); xv[u].load(x + r * C + g * 8); }
     }
-    d.store(dx + t * 8);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long r = rb + u * stride;
+      if (r < M) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float xh = (xv[u].v[i] - mu[i]) * rs[i];
+          float dd = d[u].v[i];
+          if (relu && xh * gm[i] + bt[i] <= 0.f) dd = 0.f;
+          d[u].v[i] = k1[i] * dd - k2[i] - xh * k3[i];
+        }
+        d[u].store(dx + r * C + g * 8);
+      }
+    }
   }
 }
 template <typename T>
 int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
                    const double* sums, double count, T* dx, float* dgamma, float* dbeta, int relu, long long M, int C,
                    cudaStream_t st) {
-  bn_bwd_apply_kernel<T><<<GRID1D(M * C / 8, 256), 0, st>>>(dy, x, mean, rstd, gamma, beta, sums, count, dx, dgamma, dbeta, relu, M * C / 8, C);
+  if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
+  bn_bwd_apply_kernel<T><<<bn_grid(M, C), 256, 0, st>>>(dy, x, mean, rstd, gamma, beta, sums, count, dx, dgamma, dbeta, relu, M, C);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -728,10 +837,34 @@ int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd
 // ------------------------------------------------------------------------------------------ seg head tail
 // output_conv[1..4] (Models/DPT_decoder.py:492-495): BN -> ReLU -> Dropout(0.1) -> Conv1x1(256->1).
 // One warp per pixel row (C = 256 = 32 lanes x 8 channels).
-__device__ __forceinline__ float drop_scale(const uint8_t* mask, float p, uint64_t seed, long long idx) {
-  if (mask) return mask[idx] ? 1.f / (1.f - p) : 0.f;
-  if (p <= 0.f) return 1.f;
-  return dropout_keep(seed, (uint64_t)idx, p) ? 1.f / (1.f - p) : 0.f;
+// keep-scale (0 or 1/(1-p)) of 8 consecutive elements starting at idx (idx % 8 == 0): from the explicit byte mask
+// (parity tests) or from two 64-bit counter hashes -> eight 16-bit uniform values (recomputed in backward, never stored)
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return x;
+}
+__device__ __forceinline__ void drop_scale8(const uint8_t* mask, float p, uint64_t seed, long long idx, float (&k)[8]) {
+  const float s = 1.f / (1.f - p);
+  if (mask) {
+    const uint2 m = *reinterpret_cast<const uint2*>(mask + idx);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      k[i] = ((m.x >> (8 * i)) & 0xff) ? s : 0.f;
+      k[4 + i] = ((m.y >> (8 * i)) & 0xff) ? s : 0.f;
+    }
+  } else if (p <= 0.f) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) k[i] = 1.f;
+  } else {
+    const uint32_t thr = (uint32_t)(p * 65536.f);
+    const uint64_t h0 = mix64(seed * 0x9E3779B97F4A7C15ULL + (uint64_t)idx);
+    const uint64_t h1 = mix64(h0 ^ 0xD6E8FEB86659FD93ULL);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      k[i] = ((uint32_t)(h0 >> (16 * i)) & 0xffffu) >= thr ? s : 0.f;
+      k[4 + i] = ((uint32_t)(h1 >> (16 * i)) & 0xffffu) >= thr ? s : 0.f;
+    }
+  }
 }
 template <typename T>
 __global__ void __launch_bounds__(256) seghead_fwd_kernel(const T* __restrict__ x, const float* __restrict__ mean,
@@ -740,23 +873,32 @@ __global__ void __launch_bounds__(256) seghead_fwd_kernel(const T* __restrict__ 
                                                           const float* __restrict__ b, const uint8_t* __restrict__ mask,
                                                           float p, uint64_t seed, float* __restrict__ small, long long M) {
   const int lane = threadIdx.x & 31;
-  float mu[8], sc[8], bt[8], wv[8];
+  float sc[8], sh[8], wv[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = lane * 8 + i;
-    mu[i] = mean[c]; sc[i] = rstd[c] * gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
+    sc[i] = rstd[c] * gamma[c]; sh[i] = beta[c] - mean[c] * sc[i]; wv[i] = w[c];
   }
-  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * 8) {
-    Vec8<T> v;
-    v.load(x + row * 256 + lane * 8);
-    float s = 0.f;
+  const float b0 = b[0];
+  const long long stride = (long long)gridDim.x * 8;
+  for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 4 * stride) {
+    Vec8<T> v[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float y = fmaxf((v.v[i] - mu[i]) * sc[i] + bt[i], 0.f);
-      s += y * drop_scale(mask, p, seed, row * 256 + lane * 8 + i) * wv[i];
+    for (int u = 0; u < 4; ++u)
+      if (rb + u * stride < M) v[u].load(x + (rb + u * stride) * 256 + lane * 8);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long row = rb + u * stride;
+      if (row < M) {
+        float k[8];
+        drop_scale8(mask, p, seed, row * 256 + lane * 8, k);
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += fmaxf(fmaf(v[u].v[i], sc[i], sh[i]), 0.f) * k[i] * wv[i];
+        s = warp_sum(s);
+        if (lane == 0) small[row] = s + b0;
+      }
     }
-    s = warp_sum(s);
-    if (lane == 0) small[row] = s + b[0];
   }
 }
 template <typename T>
@@ -787,19 +929,32 @@ __global__ void __launch_bounds__(256) seghead_bwd_reduce_kernel(const float* __
     mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
     s1[i] = s2[i] = s3[i] = 0.f;
   }
-  for (long long row = (long long)blockIdx.x * 8 + warp; row < M; row += (long long)gridDim.x * 8) {
-    Vec8<T> v;
-    v.load(x + row * 256 + lane * 8);
-    const float ds = dsmall[row];
-    sd += ds;
+  const long long stride = (long long)gridDim.x * 8;
+  for (long long rb = (long long)blockIdx.x * 8 + warp; rb < M; rb += 4 * stride) {
+    Vec8<T> v[4];
+    float dsv[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float xh = (v.v[i] - mu[i]) * rs[i];
-      const float y = xh * gm[i] + bt[i];
-      const float k = drop_scale(mask, p, seed, row * 256 + lane * 8 + i);
-      const float z = fmaxf(y, 0.f) * k;
-      const float dy = y > 0.f ? ds * wv[i] * k : 0.f;
-      s1[i] += dy; s2[i] += dy * xh; s3[i] += ds * z;
+    for (int u = 0; u < 4; ++u) {
+      const long long row = rb + u * stride;
+      if (row < M) { v[u].load(x + row * 256 + lane * 8); dsv[u] = dsmall[row]; }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long row = rb + u * stride;
+      if (row < M) {
+        const float ds = dsv[u];
+        sd += ds;
+        float k[8];
+        drop_scale8(mask, p, seed, row * 256 + lane * 8, k);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float xh = (v[u].v[i] - mu[i]) * rs[i];
+          const float y = xh * gm[i] + bt[i];
+          const float z = fmaxf(y, 0.f) * k[i];
+          const float dy = y > 0.f ? ds * wv[i] * k[i] : 0.f;
+          s1[i] += dy; s2[i] += dy * xh; s3[i] += ds * z;
+        }
+      }
     }
   }
 #pragma unroll
@@ -840,18 +995,31 @@ __global__ void __launch_bounds__(256) seghead_bwd_apply_kernel(const float* __r
     mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
     m1[i] = (float)sums[c] * inv; m2[i] = (float)sums[256 + c] * inv;
   }
-  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < M; row += (long long)gridDim.x * 8) {
-    Vec8<T> v;
-    v.load(x + row * 256 + lane * 8);
-    const float ds = dsmall[row];
+  const long long stride = (long long)gridDim.x * 8;
+  for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 4 * stride) {
+    Vec8<T> v[4];
+    float dsv[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float xh = (v.v[i] - mu[i]) * rs[i];
-      const float y = xh * gm[i] + bt[i];
-      const float dy = y > 0.f ? ds * wv[i] * drop_scale(mask, p, seed, row * 256 + lane * 8 + i) : 0.f;
-      v.v[i] = gm[i] * rs[i] * (dy - m1[i] - xh * m2[i]);
+    for (int u = 0; u < 4; ++u) {
+      const long long row = rb + u * stride;
+      if (row < M) { v[u].load(x + row * 256 + lane * 8); dsv[u] = dsmall[row]; }
     }
-    v.store(dx + row * 256 + lane * 8);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long row = rb + u * stride;
+      if (row < M) {
+        float k[8];
+        drop_scale8(mask, p, seed, row * 256 + lane * 8, k);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float xh = (v[u].v[i] - mu[i]) * rs[i];
+          const float y = xh * gm[i] + bt[i];
+          const float dy = y > 0.f ? dsv[u] * wv[i] * k[i] : 0.f;
+          v[u].v[i] = gm[i] * rs[i] * (dy - m1[i] - xh * m2[i]);
+        }
+        v[u].store(dx + row * 256 + lane * 8);
+      }
+    }
   }
 }
 template <typename T>
@@ -1021,11 +1189,11 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
 #define INST(T)                                                                                                        \
   template int k_patchify<T>(const float*, T*, int, cudaStream_t);                                                     \
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
-  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t); \
+  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*); \
   template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t);                                        \
   template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t);                                       \
   template int k_tokens_to_nhwc<T>(const float*, T*, int, cudaStream_t);                                               \
-  template int k_tap_grad<T>(const T*, float*, int, int, cudaStream_t);                                                \
+  template int k_tap_grad<T>(const T*, float*, int, int, cudaStream_t, T*);                                                \
   template int k_cast_f32<T>(const float*, T*, long long, cudaStream_t);                                               \
   template int k_relu<T>(const T*, T*, long long, cudaStream_t);                                                       \
   template int k_relu_bwd_add<T>(const T*, const T*, const T*, T*, long long, cudaStream_t);                           \

@@ -479,11 +479,12 @@ struct Builder {
         T* dub = mm->template at<T>(self->du);
         T* daob = mm->template at<T>(self->dao);
         T* dqkvb = mm->template at<T>(self->dqkv);
-        if (ta >= 0) { mm->launches++; S4G_TRY(k_tap_grad<T>(self->G(ta), dxo, self->B, i == 11 ? 0 : 1, st)); }
-        const long long n = Tk * 768;
-        mm->launches += 4;
+        // dxt = bf16 copy of the incoming gradient: written by the tap-gradient kernel, or by the previous block's
+        // LayerNorm backward (dx_cast)
+        if (ta >= 0) { mm->launches++; S4G_TRY(k_tap_grad<T>(self->G(ta), dxo, self->B, i == 11 ? 0 : 1, st, dxt)); }
+        else if (i == 11) { mm->launches++; S4G_TRY(k_cast_f32<T>(dxo, dxt, Tk * 768, st)); }
+        mm->launches += 2;
         // mlp: x2 = x1 + fc2(gelu(fc1(ln2(x1))))
-        S4G_TRY(k_cast_f32<T>(dxo, dxt, n, st));
         EpiParams e = epi(dub, 3072, nullptr, EPI_DGELU);
         e.aux = mm->template at<T>(b.u);
         S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), e, st));
@@ -492,9 +493,8 @@ struct Builder {
         S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st));
         S4G_CUDA(cudaMemsetAsync(b.n2w->g, 0, sizeof(float) * 768, st));
         S4G_CUDA(cudaMemsetAsync(b.n2b->g, 0, sizeof(float) * 768, st));
-        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st));
+        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st, dxt));
         // attention: x1 = x0 + proj(attn(qkv(ln1(x0))))
-        S4G_TRY(k_cast_f32<T>(dxm, dxt, n, st));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), dxt, mm->template at<T>(b.proj.wd), epi(daob, 768), st));
         S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st));
         S4G_TRY(self->attn_bwd(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, st));
@@ -502,7 +502,7 @@ struct Builder {
         S4G_TRY(self->linear_param_grads(b.qkv, dqkvb, mm->template at<T>(b.h1), Tk, st));
         S4G_CUDA(cudaMemsetAsync(b.n1w->g, 0, sizeof(float) * 768, st));
         S4G_CUDA(cudaMemsetAsync(b.n1b->g, 0, sizeof(float) * 768, st));
-        return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st);
+        return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st, i > 0 ? dxt : nullptr);
       });
     }
   }
