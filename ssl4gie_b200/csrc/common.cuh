@@ -89,6 +89,20 @@ __device__ __forceinline__ float dgelu_f(float x) {
   return cdf + x * pdf;
 }
 
+// fast GELU pieces for the bf16 tensor-core epilogues: erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7, far below bf16
+// resolution); cdf = Phi(x), pdf = phi(x) share one exponential
+__device__ __forceinline__ void gelu_parts_fast(float x, float& cdf, float& pdf) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  const float e = __expf(-z * z);
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float erfa = fmaf(-poly, e, 1.0f);
+  cdf = 0.5f * (1.0f + copysignf(erfa, x));
+  pdf = 0.39894228040143267794f * e;
+}
+__device__ __forceinline__ float gelu_fast(float x) { float c, p; gelu_parts_fast(x, c, p); return x * c; }
+__device__ __forceinline__ float dgelu_fast(float x) { float c, p; gelu_parts_fast(x, c, p); return fmaf(x, p, c); }
+
 // counter-based RNG for dropout (recomputed in backward, never stored)
 __device__ __forceinline__ uint32_t hash_u32(uint64_t x) {
   x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;

@@ -208,17 +208,47 @@ int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float
 }
 
 // ------------------------------------------------------------------------------------------ small elementwise
-template <typename T> __global__ void dgelu_mul_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out, long long n8) {
-  FOR_GRID(i, n8) {
-    Vec8<T> a, b;
-    a.load(dy + i * 8); b.load(u + i * 8);
+// out = dy * gelu'(u)   (bf16: A&S erf, error far below bf16 resolution; fp32: erff)
+template <typename T> __global__ void __launch_bounds__(256) dgelu_mul_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out, long long n8) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
+    Vec8<T> a[2], b[2];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a.v[k] *= dgelu_f(b.v[k]);
-    a.store(out + i * 8);
+    for (int q = 0; q < 2; ++q)
+      if (i0 + q * stride < n8) { a[q].load(dy + (i0 + q * stride) * 8); b[q].load(u + (i0 + q * stride) * 8); }
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      if (i0 + q * stride < n8) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[q].v[k] *= sizeof(T) == 2 ? dgelu_fast(b[q].v[k]) : dgelu_f(b[q].v[k]);
+        a[q].store(out + (i0 + q * stride) * 8);
+      }
   }
 }
 template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st) {
-  dgelu_mul_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(dy, u, out, n / 8);
+  dgelu_mul_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(dy, u, out, n / 8);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// a = gelu(u)
+template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T* __restrict__ u, T* __restrict__ out, long long n8) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
+    Vec8<T> b[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      if (i0 + q * stride < n8) b[q].load(u + (i0 + q * stride) * 8);
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+      if (i0 + q * stride < n8) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) b[q].v[k] = sizeof(T) == 2 ? gelu_fast(b[q].v[k]) : gelu_f(b[q].v[k]);
+        b[q].store(out + (i0 + q * stride) * 8);
+      }
+  }
+}
+template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st) {
+  gelu_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(u, out, n / 8);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1191,6 +1221,7 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
   template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*); \
   template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t);                                        \
+  template int k_gelu<T>(const T*, T*, long long, cudaStream_t);                                                       \
   template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t);                                       \
   template int k_tokens_to_nhwc<T>(const float*, T*, int, cudaStream_t);                                               \
   template int k_tap_grad<T>(const T*, float*, int, int, cudaStream_t, T*);                                                \

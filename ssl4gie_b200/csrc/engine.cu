@@ -434,9 +434,17 @@ struct Builder {
         e1.res = x0; e1.res_f32 = 1; e1.ldr = 768;
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), ao, mm->template at<T>(b.proj.wf), e1, st));
         S4G_TRY(k_layernorm_fwd<T>(x1, b.n2w->p, b.n2b->p, h2, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), (int)Tk, 768, 1e-6f, st));
-        EpiParams e2 = epi(mm->template at<T>(b.a), 3072, b.fc1.b->p, EPI_GELU);
-        e2.out2 = mm->template at<T>(b.u);
-        S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), h2, mm->template at<T>(b.fc1.wf), e2, st));
+        if (self->umma_path()) {
+          // K = 768 is too short to hide the GELU arithmetic behind the MMAs of a tile: u from the GEMM, a = gelu(u)
+          // as its own HBM-bound pass
+          S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), h2, mm->template at<T>(b.fc1.wf), epi(mm->template at<T>(b.u), 3072, b.fc1.b->p), st));
+          mm->launches++;
+          S4G_TRY(k_gelu<T>(mm->template at<T>(b.u), mm->template at<T>(b.a), Tk * 3072, st));
+        } else {
+          EpiParams e2 = epi(mm->template at<T>(b.a), 3072, b.fc1.b->p, EPI_GELU);
+          e2.out2 = mm->template at<T>(b.u);
+          S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), h2, mm->template at<T>(b.fc1.wf), e2, st));
+        }
         EpiParams e3 = epi(x2, 768, b.fc2.b->p, EPI_NONE, 1);
         e3.res = x1; e3.res_f32 = 1; e3.ldr = 768;
         return self->fprop(linear_geom(Tk, 768, 3072), mm->template at<T>(b.a), mm->template at<T>(b.fc2.wf), e3, st);
@@ -485,9 +493,15 @@ struct Builder {
         else if (i == 11) { mm->launches++; S4G_TRY(k_cast_f32<T>(dxo, dxt, Tk * 768, st)); }
         mm->launches += 2;
         // mlp: x2 = x1 + fc2(gelu(fc1(ln2(x1))))
-        EpiParams e = epi(dub, 3072, nullptr, EPI_DGELU);
-        e.aux = mm->template at<T>(b.u);
-        S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), e, st));
+        if (self->umma_path()) {
+          S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), epi(dub, 3072), st));
+          mm->launches++;
+          S4G_TRY(k_dgelu_mul<T>(dub, mm->template at<T>(b.u), dub, Tk * 3072, st));
+        } else {
+          EpiParams e = epi(dub, 3072, nullptr, EPI_DGELU);
+          e.aux = mm->template at<T>(b.u);
+          S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), e, st));
+        }
         S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 3072), dub, mm->template at<T>(b.fc1.wd), epi(dhb, 768), st));
         S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st));

@@ -22,7 +22,9 @@ namespace {
 constexpr int BLOCK_K = 64;           // bf16 elements = 128 B = one swizzle row
 constexpr int STAGES = 4;
 constexpr int A_STAGE_BYTES = 128 * 128;  // 128 rows x 128 B
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 192;          // wgrad kernel: producer, MMA issuer, 4 epilogue warps
+constexpr int EPI_WARPS = 8;              // fprop kernel: two epilogue warps per TMEM lane quarter (column slabs alternate)
+constexpr int FPROP_THREADS = 64 + 32 * EPI_WARPS;
 
 // ------------------------------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -159,7 +161,7 @@ struct FpropParams {
   EpiParams e;
 };
 
-constexpr int EPI_STAGE_BYTES = 128 * 128;  // one 128-row x 64-column bf16 slab, SWIZZLE_128B
+constexpr int EPI_WARP_BYTES = 32 * 128;  // per-warp staging: 32 rows x 64 bf16 columns, SWIZZLE_128B
 
 // 32 consecutive columns of one output row
 __device__ __forceinline__ void epi_row32(const EpiParams& e, long long row, int col0, int ncols, const uint32_t (&acc)[32]) {
@@ -262,7 +264,7 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
 }
 
 // =========================================================================================== fprop
-__global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                     const __grid_constant__ CUtensorMap tmB,
                                                                     const __grid_constant__ CUtensorMap tmO,
                                                                     const __grid_constant__ CUtensorMap tmO2, const FpropParams p) {
@@ -270,8 +272,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
   uint8_t* smem = align_1024(smem_raw);
   const int b_stage_bytes = p.block_n * 128;
   const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
-  uint8_t* epi_smem = smem + STAGES * stage_bytes;  // 2 x EPI_STAGE_BYTES (1024 B aligned: stage sizes are multiples of 2 KB)
-  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(epi_smem + 2 * EPI_STAGE_BYTES);
+  uint8_t* epi_smem = smem + STAGES * stage_bytes;  // EPI_WARPS x EPI_WARP_BYTES (1024 B aligned: stage sizes are multiples of 2 KB)
+  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(epi_smem + EPI_WARPS * EPI_WARP_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int k_iters = p.taps * p.chunks;
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
     tma_prefetch_desc(&tmB);
     if (p.tma_epi) { tma_prefetch_desc(&tmO); if (p.e.out2) tma_prefetch_desc(&tmO2); }
     for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
@@ -345,7 +347,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
     const int q = warp & 3;  // TMEM lane quarter this warp may touch
     const int r = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
-    uint32_t epi_count = 0;
     const TileGeom& t = p.tg;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
@@ -358,30 +359,32 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
       mbar_wait(&ctl->tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
+      const int half = (warp - 2) >> 2;  // which alternate column slabs this warp owns
+      bool released = false;
       if (p.tma_epi) {
-        // bf16 outputs: each warp stages its own 32 rows x 64 columns in a private 128B-swizzled smem slab and writes
-        // it with its own TMA store (which clips the M / N tails) -- no cross-warp synchronisation in the epilogue
+        // bf16 outputs: each warp stages 32 rows x 64 columns in its private 128B-swizzled smem slab and writes it with
+        // its own TMA store (which clips the M / N tails) -- no cross-warp synchronisation in the epilogue
         const int npass = p.e.out2 ? 2 : 1;
         const int nslabs = (p.block_n + 63) >> 6;
-        const int rl = lane;  // row inside this warp's slab
-        for (int sl = 0; sl < nslabs; ++sl) {
+        uint8_t* buf = epi_smem + (warp - 2) * EPI_WARP_BYTES;
+        for (int sl = half; sl < nslabs; sl += 2) {
           for (int pass = 0; pass < npass; ++pass) {
-            uint8_t* buf = epi_smem + (q * 2 + (epi_count & 1)) * (EPI_STAGE_BYTES / 4);
-            if (lane == 0) tma_store_wait_read<1>();  // the store that last read this buffer is done with it
+            if (lane == 0) tma_store_wait_read<0>();  // the previous store is done reading the staging slab
             __syncwarp();
             const bool pre = p.e.out2 && pass == 0;  // pre-activation copy
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
+            for (int hf = 0; hf < 2; ++hf) {
               uint32_t v[32];
-              tmem_ld32(taddr + sl * 64 + half * 32, v);
+              tmem_ld32(taddr + sl * 64 + hf * 32, v);
               tmem_ld_wait();
-              if (sl == nslabs - 1 && pass == npass - 1 && half == 1) {
-                // accumulator fully read: hand the TMEM stage back to the MMA warp before the stores
+              if (sl + 2 >= nslabs && pass == npass - 1 && hf == 1) {
+                // accumulator fully read by this warp: hand the TMEM stage back to the MMA warp before the stores
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+                released = true;
               }
-              const int col0 = tn * p.block_n + sl * 64 + half * 32;
+              const int col0 = tn * p.block_n + sl * 64 + hf * 32;
               const int ncols = p.N - col0;
               float f[32];
 #pragma unroll
@@ -398,7 +401,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
               if (!pre) {
                 if (p.e.mode == EPI_GELU) {
 #pragma unroll
-                  for (int i = 0; i < 32; ++i) f[i] = gelu_f(f[i]);
+                  for (int i = 0; i < 32; ++i) f[i] = gelu_fast(f[i]);
                 } else if (p.e.mode == EPI_RELU) {
 #pragma unroll
                   for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
@@ -411,7 +414,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
                         Vec8<bf16> t8;
                         t8.load(pa + i);
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) f[i + k] *= dgelu_f(t8.v[k]);
+                        for (int k = 0; k < 8; ++k) f[i + k] *= dgelu_fast(t8.v[k]);
                       }
                     }
                   }
@@ -423,8 +426,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
                 __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) h2[k] = __floats2bfloat162_rn(f[j * 8 + 2 * k], f[j * 8 + 2 * k + 1]);
-                const int chunk = half * 4 + j;
-                *reinterpret_cast<uint4*>(buf + rl * 128 + ((chunk ^ (rl & 7)) << 4)) = pk;
+                const int chunk = hf * 4 + j;
+                *reinterpret_cast<uint4*>(buf + lane * 128 + ((chunk ^ (lane & 7)) << 4)) = pk;
               }
             }
             fence_proxy_async();
@@ -432,16 +435,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
             if (lane == 0) {
               const int cc = tn * p.block_n + sl * 64;
               if (cc < p.N) {
-                // origin of this warp's 32-row sub-box inside the tile
-                const int r0 = q * 32;
+                const int r0 = q * 32;  // origin of this warp's 32-row sub-box inside the tile
                 tma_store_4d(pre ? &tmO2 : &tmO, buf, cc, w0 + r0 % t.bw, h0 + (r0 / t.bw) % t.bh, n0 + r0 / (t.bw * t.bh));
                 tma_store_commit();
               }
             }
-            ++epi_count;
           }
         }
-      } else {
+      } else if (half == 0) {
         for (int c0 = 0; c0 < p.block_n; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(taddr + c0, v);
@@ -450,6 +451,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_fprop_kernel(const __grid
           const int ncols = min(32, p.N - col0);
           if (valid && ncols > 0) epi_row32(p.e, row, col0, ncols, v);
         }
+      }
+      if (!released) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
@@ -760,9 +763,9 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     S4G_TRY(make_act_map(&tmO, reinterpret_cast<const bf16*>(e.out), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
     if (e.out2) S4G_TRY(make_act_map(&tmO2, reinterpret_cast<const bf16*>(e.out2), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
   }
-  const size_t smem = 1024 + (size_t)STAGES * (A_STAGE_BYTES + p.block_n * 128) + 2 * EPI_STAGE_BYTES + sizeof(SmemCtl);
+  const size_t smem = 1024 + (size_t)STAGES * (A_STAGE_BYTES + p.block_n * 128) + EPI_WARPS * EPI_WARP_BYTES + sizeof(SmemCtl);
   const int grid = std::min(p.tiles_m * p.tiles_n, g_num_sms);
-  umma_fprop_kernel<<<grid, NUM_THREADS, smem, st>>>(tmA, tmB, tmO, tmO2, p);
+  umma_fprop_kernel<<<grid, FPROP_THREADS, smem, st>>>(tmA, tmB, tmO, tmO2, p);
   S4G_KERNEL_CHECK();
   return 0;
 }
