@@ -131,77 +131,85 @@ int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y,
   return 0;
 }
 
-// each block owns ROWS_PER_BLOCK rows; warps stride over them; dgamma/dbeta partials reduced in smem, one atomic
-// per column per block
+// LayerNorm backward.  Block = C/4 threads, thread t owns columns 4t..4t+3 for every row of the block's row range, so
+// gamma and the three column accumulators (dgamma, dbeta, and the column sum of the produced dx = bias gradient of the
+// Linear that precedes this residual branch) live in registers.  Rows go 4 at a time: all loads first, then the two
+// per-row reductions (warp shuffle + a small smem exchange), then dx.  One atomic per column per block at the end.
 template <typename T, int C>
-__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
-                                                            const float* __restrict__ gamma,
-                                                            const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                            const float* __restrict__ dres, float* __restrict__ dx,
-                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                            int rows, int rows_per_block, T* __restrict__ dx_cast) {
-  constexpr int V = C / 128;
-  __shared__ float sg[C], sb[C];
-  for (int i = threadIdx.x; i < C; i += 256) { sg[i] = 0.f; sb[i] = 0.f; }
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(C / 4) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
+                                                              const float* __restrict__ gamma,
+                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                              const float* __restrict__ dres, float* __restrict__ dx,
+                                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                              int rows, int rows_per_block, T* __restrict__ dx_cast,
+                                                              float* __restrict__ dxsum) {
+  constexpr int R = 4, NW = C / 128;
+  __shared__ float red[2][NW][2 * R];
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(rows, r0 + rows_per_block);
-  float4 ag[V], ab[V];
+  const float4 gm = reinterpret_cast<const float4*>(gamma)[t];
+  float4 ag = make_float4(0, 0, 0, 0), ab = ag, ac = ag;
+  int buf = 0;
+  for (int rb = r0; rb < r1; rb += R, buf ^= 1) {
+    float4 xv[R], dv[R], rv[R];
+    float mu[R], rs[R];
 #pragma unroll
-  for (int i = 0; i < V; ++i) { ag[i] = make_float4(0, 0, 0, 0); ab[i] = make_float4(0, 0, 0, 0); }
-  for (int row = r0 + warp; row < r1; row += 8) {
-    const float mu = mean[row], rs = rstd[row];
-    const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * C);
-    const T* dyr = dy + (long long)row * C;
-    float4 xh[V], g[V];
-    float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-    for (int i = 0; i < V; ++i) {
-      const int c4 = lane + 32 * i;
-      const float4 xv = xr[c4];
-      const float4 gm = reinterpret_cast<const float4*>(gamma)[c4];
-      const float4 dq = load4(dyr + c4 * 4);
-      const float d0 = dq.x, d1 = dq.y, d2 = dq.z, d3 = dq.w;
-      xh[i] = make_float4((xv.x - mu) * rs, (xv.y - mu) * rs, (xv.z - mu) * rs, (xv.w - mu) * rs);
-      g[i] = make_float4(d0 * gm.x, d1 * gm.y, d2 * gm.z, d3 * gm.w);
-      s1 += g[i].x + g[i].y + g[i].z + g[i].w;
-      s2 += g[i].x * xh[i].x + g[i].y * xh[i].y + g[i].z * xh[i].z + g[i].w * xh[i].w;
-      ag[i].x += d0 * xh[i].x; ag[i].y += d1 * xh[i].y; ag[i].z += d2 * xh[i].z; ag[i].w += d3 * xh[i].w;
-      ab[i].x += d0; ab[i].y += d1; ab[i].z += d2; ab[i].w += d3;
+    for (int u = 0; u < R; ++u) {
+      const int row = min(rb + u, r1 - 1);
+      xv[u] = reinterpret_cast<const float4*>(x + (long long)row * C)[t];
+      dv[u] = load4(dy + (long long)row * C + t * 4);
+      rv[u] = dres ? reinterpret_cast<const float4*>(dres + (long long)row * C)[t] : make_float4(0, 0, 0, 0);
+      mu[u] = mean[row]; rs[u] = rstd[row];
     }
-    s1 = warp_sum(s1) * (1.0f / C);
-    s2 = warp_sum(s2) * (1.0f / C);
+    float4 xh[R], g[R];
+    float part[2 * R];
 #pragma unroll
-    for (int i = 0; i < V; ++i) {
-      const int c4 = lane + 32 * i;
-      float4 o = make_float4(rs * (g[i].x - s1 - xh[i].x * s2), rs * (g[i].y - s1 - xh[i].y * s2),
-                             rs * (g[i].z - s1 - xh[i].z * s2), rs * (g[i].w - s1 - xh[i].w * s2));
-      if (dres) {
-        const float4 r = reinterpret_cast<const float4*>(dres + (long long)row * C)[c4];
-        o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+    for (int u = 0; u < R; ++u) {
+      xh[u] = make_float4((xv[u].x - mu[u]) * rs[u], (xv[u].y - mu[u]) * rs[u], (xv[u].z - mu[u]) * rs[u], (xv[u].w - mu[u]) * rs[u]);
+      g[u] = make_float4(dv[u].x * gm.x, dv[u].y * gm.y, dv[u].z * gm.z, dv[u].w * gm.w);
+      part[u] = g[u].x + g[u].y + g[u].z + g[u].w;
+      part[R + u] = g[u].x * xh[u].x + g[u].y * xh[u].y + g[u].z * xh[u].z + g[u].w * xh[u].w;
+    }
+#pragma unroll
+    for (int k = 0; k < 2 * R; ++k) part[k] = warp_sum(part[k]);
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < 2 * R; ++k) red[buf][warp][k] = part[k];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < R; ++u) {
+      if (rb + u < r1) {
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) { s1 += red[buf][w][u]; s2 += red[buf][w][R + u]; }
+        s1 *= (1.0f / C); s2 *= (1.0f / C);
+        float4 o = make_float4(rs[u] * (g[u].x - s1 - xh[u].x * s2) + rv[u].x, rs[u] * (g[u].y - s1 - xh[u].y * s2) + rv[u].y,
+                               rs[u] * (g[u].z - s1 - xh[u].z * s2) + rv[u].z, rs[u] * (g[u].w - s1 - xh[u].w * s2) + rv[u].w);
+        const long long row = rb + u;
+        reinterpret_cast<float4*>(dx + row * C)[t] = o;
+        if (dx_cast) store4(dx_cast + row * C + t * 4, o);
+        ag.x += dv[u].x * xh[u].x; ag.y += dv[u].y * xh[u].y; ag.z += dv[u].z * xh[u].z; ag.w += dv[u].w * xh[u].w;
+        ab.x += dv[u].x; ab.y += dv[u].y; ab.z += dv[u].z; ab.w += dv[u].w;
+        ac.x += o.x; ac.y += o.y; ac.z += o.z; ac.w += o.w;
       }
-      reinterpret_cast<float4*>(dx + (long long)row * C)[c4] = o;
-      if (dx_cast) store4(dx_cast + (long long)row * C + c4 * 4, o);
     }
   }
-#pragma unroll
-  for (int i = 0; i < V; ++i) {
-    const int c = (lane + 32 * i) * 4;
-    atomicAdd(&sg[c], ag[i].x); atomicAdd(&sg[c + 1], ag[i].y); atomicAdd(&sg[c + 2], ag[i].z); atomicAdd(&sg[c + 3], ag[i].w);
-    atomicAdd(&sb[c], ab[i].x); atomicAdd(&sb[c + 1], ab[i].y); atomicAdd(&sb[c + 2], ab[i].z); atomicAdd(&sb[c + 3], ab[i].w);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += 256) { atomicAdd(&dgamma[i], sg[i]); atomicAdd(&dbeta[i], sb[i]); }
+  const int c = t * 4;
+  atomicAdd(&dgamma[c], ag.x); atomicAdd(&dgamma[c + 1], ag.y); atomicAdd(&dgamma[c + 2], ag.z); atomicAdd(&dgamma[c + 3], ag.w);
+  atomicAdd(&dbeta[c], ab.x); atomicAdd(&dbeta[c + 1], ab.y); atomicAdd(&dbeta[c + 2], ab.z); atomicAdd(&dbeta[c + 3], ab.w);
+  if (dxsum) { atomicAdd(&dxsum[c], ac.x); atomicAdd(&dxsum[c + 1], ac.y); atomicAdd(&dxsum[c + 2], ac.z); atomicAdd(&dxsum[c + 3], ac.w); }
 }
 template <typename T>
 int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
-                    const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st, T* dx_cast) {
-  const int rpb = max(8, cdiv(rows, 148 * 4));
+                    const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st, T* dx_cast,
+                    float* dxsum) {
+  const int rpb = max(8, cdiv(rows, 148 * 3));
   if (C == 768)
-    layernorm_bwd_kernel<T, 768><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast);
+    layernorm_bwd_kernel<T, 768><<<cdiv(rows, rpb), 192, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast, dxsum);
   else if (C == 512)
-    layernorm_bwd_kernel<T, 512><<<cdiv(rows, rpb), 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast);
+    layernorm_bwd_kernel<T, 512><<<cdiv(rows, rpb), 128, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast, dxsum);
   else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
   S4G_KERNEL_CHECK();
   return 0;
@@ -1219,7 +1227,7 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
 #define INST(T)                                                                                                        \
   template int k_patchify<T>(const float*, T*, int, cudaStream_t);                                                     \
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
-  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*); \
+  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*, float*); \
   template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t);                                        \
   template int k_gelu<T>(const T*, T*, long long, cudaStream_t);                                                       \
   template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t);                                       \

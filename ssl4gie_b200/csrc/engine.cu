@@ -145,9 +145,9 @@ struct Builder {
     return l;
   }
   // dW, db of a linear layer given dY [M,N], X [M,K]
-  int linear_param_grads(const Lin& l, const T* dY, const T* X, long long M, cudaStream_t st) const {
+  int linear_param_grads(const Lin& l, const T* dY, const T* X, long long M, cudaStream_t st, bool bias_done = false) const {
     if (l.w->g) S4G_TRY(wgrad(linear_geom(M, l.N, l.K), dY, X, l.w->g, st));
-    if (l.b && l.b->g) {
+    if (l.b && l.b->g && !bias_done) {
       S4G_CUDA(cudaMemsetAsync(l.b->g, 0, sizeof(float) * l.N, st));
       m->launches++;
       S4G_TRY(k_colsum<T>(dY, l.b->g, M, l.N, l.N, st));
@@ -478,6 +478,12 @@ struct Builder {
       const size_t xin = xs[2 * i], xmid = xs[2 * i + 1];
       const int tapk = (dense && (i == 2 || i == 5 || i == 8 || i == 11)) ? i / 3 : -1;
       const int ta = tapk >= 0 ? tap_act[tapk] : -1;
+      // bias gradients of proj / fc2 are column sums of the fp32 residual gradients the LayerNorm backward kernels
+      // produce: LN2-bwd of this block yields proj's, LN1-bwd of this block yields fc2's of block i-1 (unless a tap
+      // gradient is added in between)
+      const bool fc2_bias_fused = i < 11 && ta < 0;
+      const bool prev_fc2_fused = i > 0 && !(dense && (i - 1 == 2 || i - 1 == 5 || i - 1 == 8));
+      float* prev_fc2_bias_g = i > 0 ? blocks[i - 1].fc2.b->g : nullptr;
       m->bwd_enc.push_back([=](cudaStream_t st) {
         // incoming gradient of the block output: dxa; result (block input gradient) also ends in dxa
         float* dxo = mm->template at<float>(self->dxa);
@@ -502,21 +508,24 @@ struct Builder {
           e.aux = mm->template at<T>(b.u);
           S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), e, st));
         }
-        S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st));
+        S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st, fc2_bias_fused));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 3072), dub, mm->template at<T>(b.fc1.wd), epi(dhb, 768), st));
         S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st));
         S4G_CUDA(cudaMemsetAsync(b.n2w->g, 0, sizeof(float) * 768, st));
         S4G_CUDA(cudaMemsetAsync(b.n2b->g, 0, sizeof(float) * 768, st));
-        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st, dxt));
+        S4G_CUDA(cudaMemsetAsync(b.proj.b->g, 0, sizeof(float) * 768, st));
+        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st, dxt, b.proj.b->g));
         // attention: x1 = x0 + proj(attn(qkv(ln1(x0))))
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), dxt, mm->template at<T>(b.proj.wd), epi(daob, 768), st));
-        S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st));
+        S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st, true));
         S4G_TRY(self->attn_bwd(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, st));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 2304), dqkvb, mm->template at<T>(b.qkv.wd), epi(dhb, 768), st));
         S4G_TRY(self->linear_param_grads(b.qkv, dqkvb, mm->template at<T>(b.h1), Tk, st));
         S4G_CUDA(cudaMemsetAsync(b.n1w->g, 0, sizeof(float) * 768, st));
         S4G_CUDA(cudaMemsetAsync(b.n1b->g, 0, sizeof(float) * 768, st));
-        return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st, i > 0 ? dxt : nullptr);
+        if (prev_fc2_fused) S4G_CUDA(cudaMemsetAsync(prev_fc2_bias_g, 0, sizeof(float) * 768, st));
+        return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st, i > 0 ? dxt : nullptr,
+                                  prev_fc2_fused ? prev_fc2_bias_g : nullptr);
       });
     }
   }

@@ -41,7 +41,8 @@ int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y,
 template <typename T>
 int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                     const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st,
-                    T* dx_cast = nullptr);  // dx_cast: optional T copy of dx (the next GEMM's operand)
+                    T* dx_cast = nullptr, float* dxsum = nullptr);
+// dx_cast: optional T copy of dx (the next GEMM's operand); dxsum: optional [C] += column sums of dx (must be zeroed)
 template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st);
 template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st);
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st);  // out zeroed by caller
