@@ -136,7 +136,7 @@ int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y,
 // Linear that precedes this residual branch) live in registers.  Rows go 4 at a time: all loads first, then the two
 // per-row reductions (warp shuffle + a small smem exchange), then dx.  One atomic per column per block at the end.
 template <typename T, int C>
-__global__ void __launch_bounds__(C / 4) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
+__global__ void __launch_bounds__(C / 4, 3) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
                                                               const float* __restrict__ gamma,
                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
                                                               const float* __restrict__ dres, float* __restrict__ dx,
@@ -530,30 +530,27 @@ __device__ __forceinline__ void bil_src(int o, int in_size, float scale, int& i0
   l1 = s - i0;
   l0 = 1.f - l1;
 }
-template <typename T> __global__ void bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
+// grid.y = image row of the output (b * Ho + oh), grid.x * 256 threads cover (ow, channel group): 32-bit index math only
+template <typename T> __global__ void __launch_bounds__(256) bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
-  const long long n = (long long)B * Ho * Wo * c8;
-  FOR_GRID(t, n) {
-    const int g = (int)(t % c8);
-    long long r = t / c8;
-    const int ow = (int)(r % Wo); r /= Wo;
-    const int oh = (int)(r % Ho);
-    const int b = (int)(r / Ho);
-    int h0, h1, w0, w1; float lh0, lh1, lw0, lw1;
-    bil_src(oh, H, sh, h0, h1, lh0, lh1);
-    bil_src(ow, W, sw, w0, w1, lw0, lw1);
-    const T* base = x + (long long)b * H * W * C + g * 8;
-    Vec8<T> a, bq, c, d, o;
-    a.load(base + ((long long)h0 * W + w0) * C); bq.load(base + ((long long)h0 * W + w1) * C);
-    c.load(base + ((long long)h1 * W + w0) * C); d.load(base + ((long long)h1 * W + w1) * C);
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  if (idx >= Wo * c8) return;
+  const int g = idx % c8, ow = idx / c8;
+  const int oh = blockIdx.y % Ho, b = blockIdx.y / Ho;
+  int h0, h1, w0, w1; float lh0, lh1, lw0, lw1;
+  bil_src(oh, H, sh, h0, h1, lh0, lh1);
+  bil_src(ow, W, sw, w0, w1, lw0, lw1);
+  const T* base = x + (size_t)b * H * W * C + g * 8;
+  Vec8<T> a, bq, c, d, o;
+  a.load(base + (size_t)(h0 * W + w0) * C); bq.load(base + (size_t)(h0 * W + w1) * C);
+  c.load(base + (size_t)(h1 * W + w0) * C); d.load(base + (size_t)(h1 * W + w1) * C);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o.v[i] = lh0 * (lw0 * a.v[i] + lw1 * bq.v[i]) + lh1 * (lw0 * c.v[i] + lw1 * d.v[i]);
-    o.store(y + t * 8);
-  }
+  for (int i = 0; i < 8; ++i) o.v[i] = lh0 * (lw0 * a.v[i] + lw1 * bq.v[i]) + lh1 * (lw0 * c.v[i] + lw1 * d.v[i]);
+  o.store(y + ((size_t)blockIdx.y * Wo + ow) * C + g * 8);
 }
 template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st) {
-  bilinear2x_fwd_kernel<T><<<GRID1D((long long)B * 4 * H * W * (C / 8), 256), 0, st>>>(x, y, B, H, W, C);
+  bilinear2x_fwd_kernel<T><<<dim3(cdiv(2 * W * (C / 8), 256), B * 2 * H), 256, 0, st>>>(x, y, B, H, W, C);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -568,44 +565,50 @@ __device__ __forceinline__ void bil_range(int i, int in_size, int& lo, int& hi) 
   lo = max(0, 2 * i - 3);
   hi = min(2 * in_size - 1, 2 * i + 3);
 }
-template <typename T> __global__ void bilinear2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
-  const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
-  const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
-  const long long n = (long long)B * H * W * c8;
-  FOR_GRID(t, n) {
-    const int g = (int)(t % c8);
-    long long r = t / c8;
-    const int w = (int)(r % W); r /= W;
-    const int h = (int)(r % H);
-    const int b = (int)(r / H);
-    int hlo, hhi, wlo, whi;
-    bil_range(h, H, hlo, hhi);
-    bil_range(w, W, wlo, whi);
-    float acc[8];
+// the 7 candidate outputs 2i-3 .. 2i+3 of input i with their weights (0 for non-contributing / out of range)
+__device__ __forceinline__ void bil_taps(int i, int in_size, float scale, float (&wt)[7]) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-    const T* base = dy + (long long)b * Ho * Wo * C + g * 8;
-    for (int oh = hlo; oh <= hhi; ++oh) {
-      const float wh = bil_w(oh, h, H, sh);
-      if (wh == 0.f) continue;
-      for (int ow = wlo; ow <= whi; ++ow) {
-        const float ww = bil_w(ow, w, W, sw);
-        if (ww == 0.f) continue;
-        Vec8<T> v;
-        v.load(base + ((long long)oh * Wo + ow) * C);
-        const float f = wh * ww;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] += f * v.v[i];
-      }
-    }
-    Vec8<T> o;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
-    o.store(dx + t * 8);
+  for (int k = 0; k < 7; ++k) {
+    const int o = 2 * i - 3 + k;
+    wt[k] = (o >= 0 && o < 2 * in_size) ? bil_w(o, i, in_size, scale) : 0.f;
   }
 }
+// grid.y = input row (b * H + h); the separable weights are computed once per thread
+template <typename T> __global__ void __launch_bounds__(256) bilinear2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
+  const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
+  const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  if (idx >= W * c8) return;
+  const int g = idx % c8, w = idx / c8;
+  const int h = blockIdx.y % H, b = blockIdx.y / H;
+  float wh[7], ww[7];
+  bil_taps(h, H, sh, wh);
+  bil_taps(w, W, sw, ww);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  const T* base = dy + (size_t)b * Ho * Wo * C + g * 8;
+#pragma unroll
+  for (int kh = 0; kh < 7; ++kh) {
+    if (wh[kh] == 0.f) continue;
+    const T* rowp = base + (size_t)((2 * h - 3 + kh) * Wo + 2 * w - 3) * C;
+#pragma unroll
+    for (int kw = 0; kw < 7; ++kw) {
+      if (ww[kw] == 0.f) continue;
+      Vec8<T> v;
+      v.load(rowp + (size_t)kw * C);
+      const float f = wh[kh] * ww[kw];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] += f * v.v[i];
+    }
+  }
+  Vec8<T> o;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
+  o.store(dx + ((size_t)blockIdx.y * W + w) * C + g * 8);
+}
 template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int W, int C, cudaStream_t st) {
-  bilinear2x_bwd_kernel<T><<<GRID1D((long long)B * H * W * (C / 8), 256), 0, st>>>(dy, dx, B, H, W, C);
+  bilinear2x_bwd_kernel<T><<<dim3(cdiv(W * (C / 8), 256), B * H), 256, 0, st>>>(dy, dx, B, H, W, C);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -713,6 +716,62 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const T* __restrict__ a,
     atomicAdd(&sums[which * C + ch], s);
   }
 }
+// backward sums {sum dy', sum dy' * xhat}: a thread accumulates sum dy' and sum dy' * x for its 8 channels (only the
+// ReLU-mask constants live in registers, loads stay in their raw 16 B form, 4 in flight per operand);
+// xhat = (x - mean) * rstd is applied once per block in double.
+template <typename T>
+__global__ void __launch_bounds__(256, 2) bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                               const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                               double* __restrict__ sums, int relu, long long M, int C,
+                                                               long long rows_per_block) {
+  extern __shared__ float sm[];  // [2][lanes][C]
+  const int c8 = C / 8, lanes = 256 / c8;
+  const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
+  const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float s1[8], s2[8], sc[8], sh[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    s1[i] = 0.f; s2[i] = 0.f;
+    const int c = g * 8 + i;
+    sc[i] = relu ? rstd[c] * gamma[c] : 0.f;
+    sh[i] = relu ? beta[c] - mean[c] * sc[i] : 1.f;   // relu == 0: the mask test below is always false
+  }
+  const T* pd = dy + g * 8;
+  const T* px = x + g * 8;
+  for (long long rb = r0 + rl; rb < r1; rb += 4 * lanes) {
+    Raw8<T> d[4], xv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long r = min(rb + (long long)u * lanes, r1 - 1);   // clamped; masked out below
+      d[u].load(pd + r * C);
+      xv[u].load(px + r * C);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (rb + (long long)u * lanes < r1) {
+        float a[8], b[8];
+        d[u].get(a); xv[u].get(b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float dd = fmaf(b[i], sc[i], sh[i]) <= 0.f ? 0.f : a[i];
+          s1[i] += dd; s2[i] = fmaf(dd, b[i], s2[i]);
+        }
+      }
+    }
+  }
+  float* p1 = sm + (size_t)rl * C + g * 8;
+  float* p2 = sm + (size_t)(lanes + rl) * C + g * 8;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { p1[i] = s1[i]; p2[i] = s2[i]; }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 256) {
+    double a = 0.0, b = 0.0;
+    for (int l = 0; l < lanes; ++l) { a += (double)sm[(size_t)l * C + c]; b += (double)sm[(size_t)(lanes + l) * C + c]; }
+    atomicAdd(&sums[c], a);
+    atomicAdd(&sums[C + c], (b - (double)mean[c] * a) * (double)rstd[c]);
+  }
+}
 static inline long long bn_rows_per_block(long long M) { return max((long long)32, (M + 148 * 4 - 1) / (148 * 4)); }
 template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
@@ -726,7 +785,7 @@ int k_bn_bwd_reduce(const T* dy, const T* x, const float* mean, const float* rst
                     const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
   const long long rpb = bn_rows_per_block(M);
-  bn_reduce_kernel<T, true><<<cdiv(M, rpb), 256, 2 * 2048 * sizeof(float), st>>>(dy, x, mean, rstd, gamma, beta, sums, relu, M, C, rpb);
+  bn_bwd_reduce_kernel<T><<<cdiv(M, rpb), 256, 2 * 2048 * sizeof(float), st>>>(dy, x, mean, rstd, gamma, beta, sums, relu, M, C, rpb);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -816,48 +875,57 @@ int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* ga
   S4G_KERNEL_CHECK();
   return 0;
 }
-// dx = gamma*rstd*(dy' - sum1/count - xhat*sum2/count); block 0 also writes dgamma = sum2, dbeta = sum1
+// dx = gamma*rstd*(dy' - sum1/count - xhat*sum2/count) = sc*dy' - (c0 + x*c1) with per-channel sc = gamma*rstd,
+// c1 = sc*rstd*sum2/count, c0 = sc*sum1/count - mean*c1; block 0 also writes dgamma = sum2, dbeta = sum1.
+// The ReLU mask uses the same fmaf(x, sc, sh) as the forward bn_apply_kernel.
 template <typename T>
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
-                                                           const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                           const double* __restrict__ sums, double count,
-                                                           T* __restrict__ dx, float* dgamma, float* dbeta, int relu,
-                                                           long long M, int C) {
+__global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                              const double* __restrict__ sums, double count,
+                                                              T* __restrict__ dx, float* dgamma, float* dbeta, int relu,
+                                                              long long M, int C) {
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
   if (blockIdx.x == 0 && dgamma)
     for (int c = threadIdx.x; c < C; c += blockDim.x) { dbeta[c] = (float)sums[c]; dgamma[c] = (float)sums[C + c]; }
   const float inv = (float)(1.0 / count);
-  float mu[8], rs[8], gm[8], bt[8], k1[8], k2[8], k3[8];
+  float sc[8], sh[8], c0[8], c1[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = g * 8 + i;
-    mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c];
-    k1[i] = gm[i] * rs[i];
-    k2[i] = k1[i] * (float)sums[c] * inv;
-    k3[i] = k1[i] * (float)sums[C + c] * inv;
+    const float mu = mean[c], rs = rstd[c];
+    sc[i] = gamma[c] * rs;
+    sh[i] = relu ? beta[c] - mu * sc[i] : 1.f;
+    c1[i] = sc[i] * (float)sums[C + c] * inv * rs;
+    c0[i] = sc[i] * (float)sums[c] * inv - mu * c1[i];
   }
+  const float msk = relu ? 1.f : 0.f;   // relu == 0: fmaf(x, 0, 1) > 0 keeps every element
   const long long stride = (long long)gridDim.x * lanes;
+  const T* pd = dy + g * 8;
+  const T* px = x + g * 8;
+  T* po = dx + g * 8;
   for (long long rb = (long long)blockIdx.x * lanes + rl; rb < M; rb += 4 * stride) {
-    Vec8<T> d[4], xv[4];
+    Raw8<T> d[4], xv[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const long long r = rb + u * stride;
-      if (r < M) { d[u].load(dy + r * C + g * 8); xv[u].load(x + r * C + g * 8); }
+      const long long r = min(rb + u * stride, M - 1);
+      d[u].load(pd + r * C);
+      xv[u].load(px + r * C);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long r = rb + u * stride;
       if (r < M) {
+        float a[8], b[8];
+        d[u].get(a); xv[u].get(b);
+        Vec8<T> o;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const float xh = (xv[u].v[i] - mu[i]) * rs[i];
-          float dd = d[u].v[i];
-          if (relu && xh * gm[i] + bt[i] <= 0.f) dd = 0.f;
-          d[u].v[i] = k1[i] * dd - k2[i] - xh * k3[i];
+          const float dd = fmaf(b[i], sc[i] * msk, sh[i]) <= 0.f ? 0.f : a[i];
+          o.v[i] = fmaf(sc[i], dd, -fmaf(b[i], c1[i], c0[i]));
         }
-        d[u].store(dx + r * C + g * 8);
+        o.store(po + r * C);
       }
     }
   }
@@ -905,11 +973,11 @@ __device__ __forceinline__ void drop_scale8(const uint8_t* mask, float p, uint64
   }
 }
 template <typename T>
-__global__ void __launch_bounds__(256) seghead_fwd_kernel(const T* __restrict__ x, const float* __restrict__ mean,
-                                                          const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                                          const float* __restrict__ beta, const float* __restrict__ w,
-                                                          const float* __restrict__ b, const uint8_t* __restrict__ mask,
-                                                          float p, uint64_t seed, float* __restrict__ small, long long M) {
+__global__ void __launch_bounds__(256, 2) seghead_fwd_kernel(const T* __restrict__ x, const float* __restrict__ mean,
+                                                             const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, const float* __restrict__ w,
+                                                             const float* __restrict__ b, const uint8_t* __restrict__ mask,
+                                                             float p, uint64_t seed, float* __restrict__ small, long long M) {
   const int lane = threadIdx.x & 31;
   float sc[8], sh[8], wv[8];
 #pragma unroll
@@ -919,20 +987,21 @@ __global__ void __launch_bounds__(256) seghead_fwd_kernel(const T* __restrict__ 
   }
   const float b0 = b[0];
   const long long stride = (long long)gridDim.x * 8;
-  for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 4 * stride) {
-    Vec8<T> v[4];
+  const T* px = x + lane * 8;
+  for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 8 * stride) {
+    Raw8<T> v[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (rb + u * stride < M) v[u].load(x + (rb + u * stride) * 256 + lane * 8);
+    for (int u = 0; u < 8; ++u) v[u].load(px + min(rb + u * stride, M - 1) * 256);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 8; ++u) {
       const long long row = rb + u * stride;
       if (row < M) {
-        float k[8];
+        float k[8], f[8];
+        v[u].get(f);
         drop_scale8(mask, p, seed, row * 256 + lane * 8, k);
         float s = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s += fmaxf(fmaf(v[u].v[i], sc[i], sh[i]), 0.f) * k[i] * wv[i];
+        for (int i = 0; i < 8; ++i) s += fmaxf(fmaf(f[i], sc[i], sh[i]), 0.f) * k[i] * wv[i];
         s = warp_sum(s);
         if (lane == 0) small[row] = s + b0;
       }
@@ -948,33 +1017,36 @@ int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float*
   S4G_KERNEL_CHECK();
   return 0;
 }
-// pass 1: per-channel sums {sum dy', sum dy'*xhat} (double), dw[c] = sum dsmall * z, db = sum dsmall
+// pass 1: per-channel sums {sum dy', sum dy'*xhat} (double), dw[c] = sum dsmall * z, db = sum dsmall.
+// A thread accumulates sum dy' and sum dy'*x; xhat = (x - mean) * rstd is applied once per block in double.
 template <typename T>
-__global__ void __launch_bounds__(256) seghead_bwd_reduce_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
-                                                                 const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                                 const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                 const float* __restrict__ w, const uint8_t* __restrict__ mask,
-                                                                 float p, uint64_t seed, double* __restrict__ sums,
-                                                                 float* __restrict__ dw, float* __restrict__ db, long long M) {
+__global__ void __launch_bounds__(256, 2) seghead_bwd_reduce_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
+                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                    const float* __restrict__ w, const uint8_t* __restrict__ mask,
+                                                                    float p, uint64_t seed, double* __restrict__ sums,
+                                                                    float* __restrict__ dw, float* __restrict__ db, long long M) {
   __shared__ float sm[3][8][256];
   __shared__ float sdb[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float mu[8], rs[8], gm[8], bt[8], wv[8], s1[8], s2[8], s3[8];
+  float sc[8], sh[8], wv[8], s1[8], s2[8], s3[8];
   float sd = 0.f;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = lane * 8 + i;
-    mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
+    sc[i] = rstd[c] * gamma[c]; sh[i] = beta[c] - mean[c] * sc[i]; wv[i] = w[c];
     s1[i] = s2[i] = s3[i] = 0.f;
   }
   const long long stride = (long long)gridDim.x * 8;
+  const T* px = x + lane * 8;
   for (long long rb = (long long)blockIdx.x * 8 + warp; rb < M; rb += 4 * stride) {
-    Vec8<T> v[4];
+    Raw8<T> v[4];
     float dsv[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const long long row = rb + u * stride;
-      if (row < M) { v[u].load(x + row * 256 + lane * 8); dsv[u] = dsmall[row]; }
+      const long long row = min(rb + u * stride, M - 1);
+      v[u].load(px + row * 256);
+      dsv[u] = dsmall[row];
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -982,15 +1054,15 @@ __global__ void __launch_bounds__(256) seghead_bwd_reduce_kernel(const float* __
       if (row < M) {
         const float ds = dsv[u];
         sd += ds;
-        float k[8];
+        float k[8], f[8];
+        v[u].get(f);
         drop_scale8(mask, p, seed, row * 256 + lane * 8, k);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const float xh = (v[u].v[i] - mu[i]) * rs[i];
-          const float y = xh * gm[i] + bt[i];
-          const float z = fmaxf(y, 0.f) * k[i];
-          const float dy = y > 0.f ? ds * wv[i] * k[i] : 0.f;
-          s1[i] += dy; s2[i] += dy * xh; s3[i] += ds * z;
+          const float y = fmaf(f[i], sc[i], sh[i]);
+          const float dk = ds * k[i];
+          const float dy = y > 0.f ? dk * wv[i] : 0.f;
+          s1[i] += dy; s2[i] = fmaf(dy, f[i], s2[i]); s3[i] = fmaf(dk, fmaxf(y, 0.f), s3[i]);
         }
       }
     }
@@ -1003,7 +1075,9 @@ __global__ void __launch_bounds__(256) seghead_bwd_reduce_kernel(const float* __
   double a = 0.0, bq = 0.0; float cw = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) { a += sm[0][k][c]; bq += sm[1][k][c]; cw += sm[2][k][c]; }
-  atomicAdd(&sums[c], a); atomicAdd(&sums[256 + c], bq); atomicAdd(&dw[c], cw);
+  atomicAdd(&sums[c], a);
+  atomicAdd(&sums[256 + c], (bq - (double)mean[c] * a) * (double)rstd[c]);
+  atomicAdd(&dw[c], cw);
   if (c == 0) { float t = 0.f; for (int k = 0; k < 8; ++k) t += sdb[k]; atomicAdd(db, t); }
 }
 template <typename T>
@@ -1016,46 +1090,53 @@ int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, con
   return 0;
 }
 template <typename T>
-__global__ void __launch_bounds__(256) seghead_bwd_apply_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
-                                                                const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                const float* __restrict__ w, const uint8_t* __restrict__ mask,
-                                                                float p, uint64_t seed, const double* __restrict__ sums,
-                                                                double count, T* __restrict__ dx, float* dgamma, float* dbeta,
-                                                                long long M) {
+__global__ void __launch_bounds__(256, 2) seghead_bwd_apply_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
+                                                                   const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                   const float* __restrict__ w, const uint8_t* __restrict__ mask,
+                                                                   float p, uint64_t seed, const double* __restrict__ sums,
+                                                                   double count, T* __restrict__ dx, float* dgamma, float* dbeta,
+                                                                   long long M) {
   const int lane = threadIdx.x & 31;
   if (blockIdx.x == 0) { dbeta[threadIdx.x] = (float)sums[threadIdx.x]; dgamma[threadIdx.x] = (float)sums[256 + threadIdx.x]; }
   const float inv = (float)(1.0 / count);
-  float mu[8], rs[8], gm[8], bt[8], wv[8], m1[8], m2[8];
+  // dx = sc*dy - (c0 + x*c1), see bn_bwd_apply_kernel; scw = sc * w folds the 1x1 conv weight into the dy term
+  float sc[8], sh[8], scw[8], c0[8], c1[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = lane * 8 + i;
-    mu[i] = mean[c]; rs[i] = rstd[c]; gm[i] = gamma[c]; bt[i] = beta[c]; wv[i] = w[c];
-    m1[i] = (float)sums[c] * inv; m2[i] = (float)sums[256 + c] * inv;
+    const float mu = mean[c], rs = rstd[c];
+    sc[i] = gamma[c] * rs; sh[i] = beta[c] - mu * sc[i]; scw[i] = sc[i] * w[c];
+    c1[i] = sc[i] * (float)sums[256 + c] * inv * rs;
+    c0[i] = sc[i] * (float)sums[c] * inv - mu * c1[i];
   }
   const long long stride = (long long)gridDim.x * 8;
+  const T* px = x + lane * 8;
+  T* po = dx + lane * 8;
   for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 4 * stride) {
-    Vec8<T> v[4];
+    Raw8<T> v[4];
     float dsv[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const long long row = rb + u * stride;
-      if (row < M) { v[u].load(x + row * 256 + lane * 8); dsv[u] = dsmall[row]; }
+      const long long row = min(rb + u * stride, M - 1);
+      v[u].load(px + row * 256);
+      dsv[u] = dsmall[row];
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long row = rb + u * stride;
       if (row < M) {
-        float k[8];
+        float k[8], f[8];
+        v[u].get(f);
         drop_scale8(mask, p, seed, row * 256 + lane * 8, k);
+        Vec8<T> o;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const float xh = (v[u].v[i] - mu[i]) * rs[i];
-          const float y = xh * gm[i] + bt[i];
-          const float dy = y > 0.f ? dsv[u] * wv[i] * k[i] : 0.f;
-          v[u].v[i] = gm[i] * rs[i] * (dy - m1[i] - xh * m2[i]);
+          const float y = fmaf(f[i], sc[i], sh[i]);
+          const float dyw = y > 0.f ? dsv[u] * k[i] : 0.f;
+          o.v[i] = fmaf(scw[i], dyw, -fmaf(f[i], c1[i], c0[i]));
         }
-        v[u].store(dx + row * 256 + lane * 8);
+        o.store(po + row * 256);
       }
     }
   }

@@ -333,20 +333,23 @@ struct Builder {
       m->acts[res].g = m->acts[s].g;
     }
     const int t = rcu(p + "resConfUnit2.", s, use_bn);
+    // The reference upsamples and then applies the 1x1 out_conv (Models/DPT_decoder.py:295-299).  Both are linear and
+    // the bilinear weights of every output pixel sum to 1, so conv1x1(up(x)) + b == up(conv1x1(x) + b): the 1x1 conv
+    // runs on the 4x smaller map (fprop, dgrad and wgrad) and the full-resolution intermediate is never materialised.
     const Act at = m->acts[t];
-    const int u = act(at.B, 2 * at.H, 2 * at.W, 256);
+    const int v = act(at.B, at.H, at.W, 256);
+    lin_layer(linear(p + "out_conv", 256, 256), t, v);
+    const int out = act(at.B, 2 * at.H, 2 * at.W, 256);
     m->fwd.push_back([=](cudaStream_t st) {
-      const Act& a = mm->acts[t];
+      const Act& a = mm->acts[v];
       mm->launches++;
-      return k_bilinear2x_fwd<T>(self->V(t), self->V(u), a.B, a.H, a.W, 256, st);
+      return k_bilinear2x_fwd<T>(self->V(v), self->V(out), a.B, a.H, a.W, 256, st);
     });
     bwd->push_back([=](cudaStream_t st) {
-      const Act& a = mm->acts[t];
+      const Act& a = mm->acts[v];
       mm->launches++;
-      return k_bilinear2x_bwd<T>(self->G(u), self->G(t), a.B, a.H, a.W, 256, st);
+      return k_bilinear2x_bwd<T>(self->G(out), self->G(v), a.B, a.H, a.W, 256, st);
     });
-    const int out = act(at.B, 2 * at.H, 2 * at.W, 256);
-    lin_layer(linear(p + "out_conv", 256, 256), u, out);
     return out;
   }
 

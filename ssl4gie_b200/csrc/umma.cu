@@ -632,6 +632,45 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReducePara
   }
 }
 
+// Linear-layer form of the reduction (taps == 1, dW row-major [Cout][Cin]): one block per 128 (co) x 32 (ci) panel of an
+// output tile, 16 independent 128 B-coalesced loads per thread and split, transposed through a conflict-free smem
+// panel so that every warp store is a full 128 B row segment of dW.
+__global__ void __launch_bounds__(256) wgrad_reduce_linear_kernel(const WgradReduceParams p) {
+  __shared__ float tile[32][129];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int subs = p.block_n >> 5;
+  const int t = blockIdx.x / subs, sub = blockIdx.x % subs;
+  const int tco = t % p.tiles_co, tci = t / p.tiles_co;
+  const size_t tile_elems = (size_t)128 * p.block_n;
+  const size_t split_stride = (size_t)p.tiles_ci * p.tiles_co * tile_elems;
+  const float* base = p.part + ((size_t)tci * p.tiles_co + tco) * tile_elems + (size_t)sub * 32 * 128;
+  float acc[16];
+#pragma unroll
+  for (int it = 0; it < 16; ++it) acc[it] = 0.f;
+  for (int s = 0; s < p.splits; ++s) {
+    const float* src = base + (size_t)s * split_stride;
+#pragma unroll
+    for (int it = 0; it < 16; ++it) {
+      const int item = it * 8 + warp;            // 128 items = 32 columns x 4 groups of 32 rows
+      acc[it] += src[(item >> 2) * 128 + (item & 3) * 32 + lane];
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < 16; ++it) {
+    const int item = it * 8 + warp;
+    tile[item >> 2][(item & 3) * 32 + lane] = acc[it];
+  }
+  __syncthreads();
+  const int ci = tci * p.block_n + sub * 32 + lane;
+  if (ci >= p.Cin) return;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int col = warp * 16 + k;
+    const int co = tco * 128 + col;
+    if (co < p.Cout) p.dW[(long long)co * p.so + ci] = tile[lane][col];
+  }
+}
+
 // ------------------------------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -706,12 +745,22 @@ int make_act_map(CUtensorMap* map, const bf16* base, const ConvGeom& g, int C, i
   }
   return make_map(map, base, 4, dims, strides, box);
 }
-int pick_block_n(int N) {
+// Output-tile width.  tcgen05 time per tile is proportional to block_n (128 x N x 16 costs N/2 cycles), so the cost of
+// a persistent launch is waves * (block_n + per-tile overhead): pick the 64-multiple that minimises it.  (M = 12608
+// token rows are 99 row tiles: 99 x 3 tiles of 256 columns is 2.007 waves over 148 SMs, 99 x 4 of 192 is 2.68.)
+int pick_block_n(int N, int tiles_m) {
   if (N <= 256) return (N + 15) / 16 * 16;
-  if (N % 256 == 0) return 256;
-  if (N % 192 == 0) return 192;
-  if (N % 128 == 0) return 128;
-  return 256;
+  static const int forced = getenv("S4G_FPROP_BN") ? atoi(getenv("S4G_FPROP_BN")) : 0;
+  if (forced) return forced;
+  int best = 256;
+  long long best_cost = -1;
+  for (int bn = 256; bn >= 128; bn -= 64) {
+    const long long tiles = (long long)tiles_m * cdiv(N, bn);
+    const long long waves = (tiles + g_num_sms - 1) / g_num_sms;
+    const long long cost = waves * (bn + 24);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
 }
 
 }  // namespace
@@ -740,9 +789,9 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
   p.tg = matrix ? matrix_tiles(g.Nimg, 128) : make_tiles(g.Nimg, g.Hi, g.Wi, 128);
   p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
   p.chunks = cdiv(g.Cin, BLOCK_K);
-  p.block_n = pick_block_n(g.Cout);
-  p.N = g.Cout;
   p.tiles_m = p.tg.tw * p.tg.th * p.tg.tn;
+  p.block_n = pick_block_n(g.Cout, p.tiles_m);
+  p.N = g.Cout;
   p.tiles_n = cdiv(g.Cout, p.block_n);
   p.e = e;
   CUtensorMap tmA, tmB;
@@ -843,7 +892,10 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   r.splits = p.splits;
   if (torch_layout) { r.so = (long long)g.Cin * p.taps; r.si = p.taps; r.st = 1; }   // [Cout][Cin][R][S]
   else { r.so = p.K; r.si = 1; r.st = g.Cin; }                                        // packed [Cout][tap][Cin]
-  wgrad_reduce_kernel<<<dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps), dim3(32, 8), 0, st>>>(r);
+  if (p.taps == 1 && r.si == 1)
+    wgrad_reduce_linear_kernel<<<p.tiles_co * p.tiles_ci * (p.block_n / 32), 256, 0, st>>>(r);
+  else
+    wgrad_reduce_kernel<<<dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps), dim3(32, 8), 0, st>>>(r);
   S4G_KERNEL_CHECK();
   return 0;
 }
