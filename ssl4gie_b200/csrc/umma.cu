@@ -20,7 +20,8 @@
 namespace {
 
 constexpr int BLOCK_K = 64;           // bf16 elements = 128 B = one swizzle row
-constexpr int STAGES = 4;
+constexpr int STAGES = 4;              // wgrad kernel
+constexpr int MAX_STAGES = 8;          // fprop kernel: as many as fit beside the epilogue staging
 constexpr int A_STAGE_BYTES = 128 * 128;  // 128 rows x 128 B
 constexpr int NUM_THREADS = 192;          // wgrad kernel: producer, MMA issuer, 4 epilogue warps
 constexpr int EPI_WARPS = 8;              // fprop kernel: two epilogue warps per TMEM lane quarter (column slabs alternate)
@@ -95,6 +96,50 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// ---- CTA-pair (cta_group::2) variants: two CTAs of a cluster share one 256 x N MMA ------------------------------
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address -> even CTA of the pair
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// loads into this CTA's smem, transaction bytes signalled on the LEADER CTA's mbarrier
+__device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & PEER_MASK), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_pair(const CUtensorMap* m, uint64_t* bar, void* dst, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & PEER_MASK), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {   // arrive on the same barrier of cluster CTA 0
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(smem_u32(bar)));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {   // arrives on `bar` in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
@@ -138,7 +183,7 @@ __host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn, int b_
 
 // ------------------------------------------------------------------------------------------ shared layout
 struct SmemCtl {
-  uint64_t full[STAGES], empty[STAGES], tfull[2], tempty[2];
+  uint64_t full[MAX_STAGES], empty[MAX_STAGES], tfull[2], tempty[2];
   uint32_t tmem_base;
 };
 
@@ -155,7 +200,8 @@ __device__ __forceinline__ void tile_origin(const TileGeom& t, int tile, int& n0
 struct FpropParams {
   TileGeom tg;
   int taps, S, pad, chunks;  // chunks = ceil(Cin / 64)
-  int tiles_m, tiles_n, block_n, N;
+  int tiles_m, tiles_n, block_n, N;   // tiles_m: row tiles per CTA group step (pairs of row tiles when CG == 2)
+  int stages;                          // smem ring depth
   int tma_epi;       // 1: bf16 outputs staged in swizzled smem and written with TMA stores
   long long M;       // rows of the output matrix (for the aux read guard)
   EpiParams e;
@@ -264,31 +310,39 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
 }
 
 // =========================================================================================== fprop
+// CG = 1: one CTA per 128 x N tile.  CG = 2: a CTA pair (cluster of 2, one TPC) computes a 256 x N tile with
+// tcgen05.mma.cta_group::2 -- each CTA stages its own 128 rows of A and HALF of the B tile, so the L2 -> smem operand
+// traffic per FLOP drops by a third and the smaller stages give a deeper ring for the same shared memory.
+template <int CG>
 __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                     const __grid_constant__ CUtensorMap tmB,
                                                                     const __grid_constant__ CUtensorMap tmO,
                                                                     const __grid_constant__ CUtensorMap tmO2, const FpropParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
-  const int b_stage_bytes = p.block_n * 128;
+  const int bn_cta = p.block_n / CG;                // B rows staged by this CTA
+  const int b_stage_bytes = bn_cta * 128;
   const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
-  uint8_t* epi_smem = smem + STAGES * stage_bytes;  // EPI_WARPS x EPI_WARP_BYTES (1024 B aligned: stage sizes are multiples of 2 KB)
+  const int STG = p.stages;
+  uint8_t* epi_smem = smem + STG * stage_bytes;  // EPI_WARPS x EPI_WARP_BYTES (1024 B aligned: stage sizes are multiples of 1 KB)
   SmemCtl* ctl = reinterpret_cast<SmemCtl*>(epi_smem + EPI_WARPS * EPI_WARP_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int k_iters = p.taps * p.chunks;
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
+  const int group = blockIdx.x / CG, num_groups = gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (p.tma_epi) { tma_prefetch_desc(&tmO); if (p.e.out2) tma_prefetch_desc(&tmO2); }
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], EPI_WARPS); }
+    for (int i = 0; i < STG; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], EPI_WARPS * CG); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
+  if (warp == 1) { if (CG == 2) tmem_alloc_pair(&ctl->tmem_base, 512); else tmem_alloc(&ctl->tmem_base, 512); }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
 
@@ -296,8 +350,8 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
     // ------------------------------------------------------------------ TMA producer
     if (elect_one()) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+      for (int tile = group; tile < num_tiles; tile += num_groups) {
+        const int tm = (tile / p.tiles_n) * CG + rank, tn = tile % p.tiles_n;
         int n0, h0, w0;
         tile_origin(p.tg, tm, n0, h0, w0);
         for (int tap = 0; tap < p.taps; ++tap) {
@@ -305,20 +359,27 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
           for (int ch = 0; ch < p.chunks; ++ch) {
             mbar_wait(&ctl->empty[stage], phase ^ 1);
             uint8_t* sa = smem + stage * stage_bytes;
-            mbar_expect_tx(&ctl->full[stage], stage_bytes);
-            tma_load_4d(&tmA, &ctl->full[stage], sa, ch * BLOCK_K, w0 + dx, h0 + dy, n0);
-            tma_load_3d(&tmB, &ctl->full[stage], sa + A_STAGE_BYTES, ch * BLOCK_K, tap, tn * p.block_n);
-            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            if (CG == 2) {
+              // the leader's barrier collects the bytes of both CTAs' loads
+              if (rank == 0) mbar_expect_tx(&ctl->full[stage], 2 * stage_bytes);
+              tma_load_4d_pair(&tmA, &ctl->full[stage], sa, ch * BLOCK_K, w0 + dx, h0 + dy, n0);
+              tma_load_3d_pair(&tmB, &ctl->full[stage], sa + A_STAGE_BYTES, ch * BLOCK_K, tap, tn * p.block_n + rank * bn_cta);
+            } else {
+              mbar_expect_tx(&ctl->full[stage], stage_bytes);
+              tma_load_4d(&tmA, &ctl->full[stage], sa, ch * BLOCK_K, w0 + dx, h0 + dy, n0);
+              tma_load_3d(&tmB, &ctl->full[stage], sa + A_STAGE_BYTES, ch * BLOCK_K, tap, tn * p.block_n);
+            }
+            if (++stage == STG) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    const uint32_t idesc = make_idesc(128, p.block_n, 0, 0);
+    // ------------------------------------------------------------------ MMA issuer (CG == 2: the leader CTA only)
+    const uint32_t idesc = make_idesc(128 * CG, p.block_n, 0, 0);
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = group; tile < num_tiles && rank == 0; tile += num_groups) {
       mbar_wait(&ctl->tempty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * 256;
@@ -332,13 +393,19 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
           for (int kk = 0; kk < BLOCK_K / 16; ++kk) {
             const uint64_t da = make_desc(sa + kk * 32, 16, 1024);
             const uint64_t db = make_desc(sb + kk * 32, 16, 1024);
-            umma_bf16(tmem_d, da, db, idesc, (k | kk) != 0);
+            if (CG == 2) umma_bf16_pair(tmem_d, da, db, idesc, (k | kk) != 0);
+            else umma_bf16(tmem_d, da, db, idesc, (k | kk) != 0);
           }
-          umma_commit(&ctl->empty[stage]);
-          if (k == k_iters - 1) umma_commit(&ctl->tfull[acc]);
+          if (CG == 2) {
+            umma_commit_pair(&ctl->empty[stage]);
+            if (k == k_iters - 1) umma_commit_pair(&ctl->tfull[acc]);
+          } else {
+            umma_commit(&ctl->empty[stage]);
+            if (k == k_iters - 1) umma_commit(&ctl->tfull[acc]);
+          }
         }
         __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == STG) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -348,8 +415,8 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
     const int r = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
     const TileGeom& t = p.tg;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+    for (int tile = group; tile < num_tiles; tile += num_groups) {
+      const int tm = (tile / p.tiles_n) * CG + rank, tn = tile % p.tiles_n;
       int n0, h0, w0;
       tile_origin(t, tm, n0, h0, w0);
       const int dx = r % t.bw, dy = (r / t.bw) % t.bh, dn = r / (t.bw * t.bh);
@@ -381,7 +448,7 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
                 // accumulator fully read by this warp: hand the TMEM stage back to the MMA warp before the stores
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+                if (lane == 0) { if (CG == 2) mbar_arrive_leader(&ctl->tempty[acc]); else mbar_arrive(&ctl->tempty[acc]); }
                 released = true;
               }
               const int col0 = tn * p.block_n + sl * 64 + hf * 32;
@@ -455,15 +522,15 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
       if (!released) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+        if (lane == 0) { if (CG == 2) mbar_arrive_leader(&ctl->tempty[acc]); else mbar_arrive(&ctl->tempty[acc]); }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (p.tma_epi && lane == 0) tma_store_wait_all();
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  if (CG == 2) cluster_sync_all(); else __syncthreads();   // the peer may still signal this CTA's barriers until here
+  if (warp == 1) { if (CG == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
 }
 
 // =========================================================================================== wgrad
@@ -745,22 +812,15 @@ int make_act_map(CUtensorMap* map, const bf16* base, const ConvGeom& g, int C, i
   }
   return make_map(map, base, 4, dims, strides, box);
 }
-// Output-tile width.  tcgen05 time per tile is proportional to block_n (128 x N x 16 costs N/2 cycles), so the cost of
-// a persistent launch is waves * (block_n + per-tile overhead): pick the 64-multiple that minimises it.  (M = 12608
-// token rows are 99 row tiles: 99 x 3 tiles of 256 columns is 2.007 waves over 148 SMs, 99 x 4 of 192 is 2.68.)
+// Output-tile width: 256 columns whenever N allows.  Measured (profiles/r01_d): the K = 768 token GEMMs are bound by the
+// L2 -> smem operand fill (about 12 TB/s with single-CTA tiles), not by tcgen05 issue, so narrower tiles (192 / 128),
+// which would quantise better over 148 SMs, only add A-tile traffic and run slower.  S4G_FPROP_BN overrides for tests.
 int pick_block_n(int N, int tiles_m) {
   if (N <= 256) return (N + 15) / 16 * 16;
   static const int forced = getenv("S4G_FPROP_BN") ? atoi(getenv("S4G_FPROP_BN")) : 0;
   if (forced) return forced;
-  int best = 256;
-  long long best_cost = -1;
-  for (int bn = 256; bn >= 128; bn -= 64) {
-    const long long tiles = (long long)tiles_m * cdiv(N, bn);
-    const long long waves = (tiles + g_num_sms - 1) / g_num_sms;
-    const long long cost = waves * (bn + 24);
-    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
-  }
-  return best;
+  (void)tiles_m;
+  return 256;
 }
 
 }  // namespace
@@ -775,7 +835,8 @@ int umma_init() {
   int dev = 0;
   S4G_CUDA(cudaGetDevice(&dev));
   S4G_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-  S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   return 0;
 }
@@ -789,11 +850,18 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
   p.tg = matrix ? matrix_tiles(g.Nimg, 128) : make_tiles(g.Nimg, g.Hi, g.Wi, 128);
   p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
   p.chunks = cdiv(g.Cin, BLOCK_K);
-  p.tiles_m = p.tg.tw * p.tg.th * p.tg.tn;
-  p.block_n = pick_block_n(g.Cout, p.tiles_m);
+  const int row_tiles = p.tg.tw * p.tg.th * p.tg.tn;
+  p.block_n = pick_block_n(g.Cout, row_tiles);
   p.N = g.Cout;
   p.tiles_n = cdiv(g.Cout, p.block_n);
   p.e = e;
+  // CTA pairs (cta_group::2) whenever there are at least two row tiles; S4G_FPROP_CG=1 forces the single-CTA kernel
+  static const int forced_cg = getenv("S4G_FPROP_CG") ? atoi(getenv("S4G_FPROP_CG")) : 0;
+  const int cg = forced_cg ? forced_cg : (row_tiles >= 2 && p.block_n % 32 == 0 ? 2 : 1);
+  p.tiles_m = cdiv(row_tiles, cg);
+  const int stage_bytes = A_STAGE_BYTES + (p.block_n / cg) * 128;
+  const size_t fixed = 1024 + EPI_WARPS * EPI_WARP_BYTES + sizeof(SmemCtl);
+  p.stages = (int)std::min<size_t>(MAX_STAGES, (227 * 1024 - fixed) / stage_bytes);
   CUtensorMap tmA, tmB;
   S4G_TRY(make_act_map(&tmA, X, g, g.Cin, g.ldx, p.tg, matrix, g.Hi, g.Wi));
   {
@@ -801,7 +869,7 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     // TMA instead of running into the next tap
     uint64_t dims[3] = {(uint64_t)g.Cin, (uint64_t)p.taps, (uint64_t)g.Cout};
     uint64_t strides[2] = {(uint64_t)g.Cin * 2, (uint64_t)g.Cin * p.taps * 2};
-    uint32_t box[3] = {64, 1, (uint32_t)p.block_n};
+    uint32_t box[3] = {64, 1, (uint32_t)(p.block_n / cg)};
     S4G_TRY(make_map(&tmB, W, 3, dims, strides, box));
   }
   p.M = (long long)g.Nimg * g.Hi * g.Wi;
@@ -812,9 +880,22 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     S4G_TRY(make_act_map(&tmO, reinterpret_cast<const bf16*>(e.out), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
     if (e.out2) S4G_TRY(make_act_map(&tmO2, reinterpret_cast<const bf16*>(e.out2), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
   }
-  const size_t smem = 1024 + (size_t)STAGES * (A_STAGE_BYTES + p.block_n * 128) + EPI_WARPS * EPI_WARP_BYTES + sizeof(SmemCtl);
-  const int grid = std::min(p.tiles_m * p.tiles_n, g_num_sms);
-  umma_fprop_kernel<<<grid, FPROP_THREADS, smem, st>>>(tmA, tmB, tmO, tmO2, p);
+  const size_t smem = fixed + (size_t)p.stages * stage_bytes;
+  if (cg == 2) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * std::min(p.tiles_m * p.tiles_n, g_num_sms / 2));
+    cfg.blockDim = dim3(FPROP_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<2>, tmA, tmB, tmO, tmO2, p));
+  } else {
+    const int grid = std::min(p.tiles_m * p.tiles_n, g_num_sms);
+    umma_fprop_kernel<1><<<grid, FPROP_THREADS, smem, st>>>(tmA, tmB, tmO, tmO2, p);
+  }
   S4G_KERNEL_CHECK();
   return 0;
 }
