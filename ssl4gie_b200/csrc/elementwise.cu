@@ -131,85 +131,84 @@ int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y,
   return 0;
 }
 
-// LayerNorm backward.  Block = C/4 threads, thread t owns columns 4t..4t+3 for every row of the block's row range, so
-// gamma and the three column accumulators (dgamma, dbeta, and the column sum of the produced dx = bias gradient of the
-// Linear that precedes this residual branch) live in registers.  Rows go 4 at a time: all loads first, then the two
-// per-row reductions (warp shuffle + a small smem exchange), then dx.  One atomic per column per block at the end.
+// LayerNorm backward, one warp per token row: lane l owns columns 4l + 128i (i < C/128) of every row its warp visits, so
+// the three column accumulators (dgamma, dbeta, and the column sum of the produced dx = bias gradient of the Linear that
+// precedes this residual branch) stay in registers across rows, the two per-row reductions are warp shuffles, and there
+// is no block barrier inside the row loop.  At the end the warps of a block combine in shared memory and issue one
+// global atomic per column.
 template <typename T, int C>
-__global__ void __launch_bounds__(C / 4, 3) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
-                                                              const float* __restrict__ gamma,
-                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                              const float* __restrict__ dres, float* __restrict__ dx,
-                                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                              int rows, int rows_per_block, T* __restrict__ dx_cast,
-                                                              float* __restrict__ dxsum) {
-  constexpr int R = 4, NW = C / 128;
-  __shared__ float red[2][NW][2 * R];
-  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const int r0 = blockIdx.x * rows_per_block;
-  const int r1 = min(rows, r0 + rows_per_block);
-  const float4 gm = reinterpret_cast<const float4*>(gamma)[t];
-  float4 ag = make_float4(0, 0, 0, 0), ab = ag, ac = ag;
-  int buf = 0;
-  for (int rb = r0; rb < r1; rb += R, buf ^= 1) {
-    float4 xv[R], dv[R], rv[R];
-    float mu[R], rs[R];
+__global__ void __launch_bounds__(256, 1) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
+                                                               const float* __restrict__ gamma,
+                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                               const float* __restrict__ dres, float* __restrict__ dx,
+                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                               int rows, T* __restrict__ dx_cast, float* __restrict__ dxsum) {
+  constexpr int V = C / 128;
+  __shared__ float red[3][C];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int c = threadIdx.x; c < 3 * C; c += 256) (&red[0][0])[c] = 0.f;
+  __syncthreads();
+  float4 gm[V], ag[V], ab[V], ac[V];
 #pragma unroll
-    for (int u = 0; u < R; ++u) {
-      const int row = min(rb + u, r1 - 1);
-      xv[u] = reinterpret_cast<const float4*>(x + (long long)row * C)[t];
-      dv[u] = load4(dy + (long long)row * C + t * 4);
-      rv[u] = dres ? reinterpret_cast<const float4*>(dres + (long long)row * C)[t] : make_float4(0, 0, 0, 0);
-      mu[u] = mean[row]; rs[u] = rstd[row];
+  for (int i = 0; i < V; ++i) {
+    gm[i] = reinterpret_cast<const float4*>(gamma)[lane + 32 * i];
+    ag[i] = ab[i] = ac[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const int wstride = gridDim.x * 8;
+  for (int row = blockIdx.x * 8 + warp; row < rows; row += wstride) {
+    const long long o = (long long)row * C;
+    float4 xv[V], dv[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      xv[i] = reinterpret_cast<const float4*>(x + o)[lane + 32 * i];
+      dv[i] = load4(dy + o + (lane + 32 * i) * 4);
     }
-    float4 xh[R], g[R];
-    float part[2 * R];
+    const float mu = mean[row], rs = rstd[row];
+    float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int u = 0; u < R; ++u) {
-      xh[u] = make_float4((xv[u].x - mu[u]) * rs[u], (xv[u].y - mu[u]) * rs[u], (xv[u].z - mu[u]) * rs[u], (xv[u].w - mu[u]) * rs[u]);
-      g[u] = make_float4(dv[u].x * gm.x, dv[u].y * gm.y, dv[u].z * gm.z, dv[u].w * gm.w);
-      part[u] = g[u].x + g[u].y + g[u].z + g[u].w;
-      part[R + u] = g[u].x * xh[u].x + g[u].y * xh[u].y + g[u].z * xh[u].z + g[u].w * xh[u].w;
+    for (int i = 0; i < V; ++i) {
+      xv[i] = make_float4((xv[i].x - mu) * rs, (xv[i].y - mu) * rs, (xv[i].z - mu) * rs, (xv[i].w - mu) * rs);   // xhat
+      ab[i].x += dv[i].x; ab[i].y += dv[i].y; ab[i].z += dv[i].z; ab[i].w += dv[i].w;
+      ag[i].x += dv[i].x * xv[i].x; ag[i].y += dv[i].y * xv[i].y; ag[i].z += dv[i].z * xv[i].z; ag[i].w += dv[i].w * xv[i].w;
+      dv[i] = make_float4(dv[i].x * gm[i].x, dv[i].y * gm[i].y, dv[i].z * gm[i].z, dv[i].w * gm[i].w);           // g = dy * gamma
+      s1 += dv[i].x + dv[i].y + dv[i].z + dv[i].w;
+      s2 += dv[i].x * xv[i].x + dv[i].y * xv[i].y + dv[i].z * xv[i].z + dv[i].w * xv[i].w;
     }
+    s1 = warp_sum(s1) * (1.0f / C);
+    s2 = warp_sum(s2) * (1.0f / C);
 #pragma unroll
-    for (int k = 0; k < 2 * R; ++k) part[k] = warp_sum(part[k]);
-    if (lane == 0) {
-#pragma unroll
-      for (int k = 0; k < 2 * R; ++k) red[buf][warp][k] = part[k];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int u = 0; u < R; ++u) {
-      if (rb + u < r1) {
-        float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-        for (int w = 0; w < NW; ++w) { s1 += red[buf][w][u]; s2 += red[buf][w][R + u]; }
-        s1 *= (1.0f / C); s2 *= (1.0f / C);
-        float4 o = make_float4(rs[u] * (g[u].x - s1 - xh[u].x * s2) + rv[u].x, rs[u] * (g[u].y - s1 - xh[u].y * s2) + rv[u].y,
-                               rs[u] * (g[u].z - s1 - xh[u].z * s2) + rv[u].z, rs[u] * (g[u].w - s1 - xh[u].w * s2) + rv[u].w);
-        const long long row = rb + u;
-        reinterpret_cast<float4*>(dx + row * C)[t] = o;
-        if (dx_cast) store4(dx_cast + row * C + t * 4, o);
-        ag.x += dv[u].x * xh[u].x; ag.y += dv[u].y * xh[u].y; ag.z += dv[u].z * xh[u].z; ag.w += dv[u].w * xh[u].w;
-        ab.x += dv[u].x; ab.y += dv[u].y; ab.z += dv[u].z; ab.w += dv[u].w;
-        ac.x += o.x; ac.y += o.y; ac.z += o.z; ac.w += o.w;
-      }
+    for (int i = 0; i < V; ++i) {
+      const float4 rv = dres ? reinterpret_cast<const float4*>(dres + o)[lane + 32 * i] : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 r = make_float4(rs * (dv[i].x - s1 - xv[i].x * s2) + rv.x, rs * (dv[i].y - s1 - xv[i].y * s2) + rv.y,
+                                   rs * (dv[i].z - s1 - xv[i].z * s2) + rv.z, rs * (dv[i].w - s1 - xv[i].w * s2) + rv.w);
+      reinterpret_cast<float4*>(dx + o)[lane + 32 * i] = r;
+      if (dx_cast) store4(dx_cast + o + (lane + 32 * i) * 4, r);
+      ac[i].x += r.x; ac[i].y += r.y; ac[i].z += r.z; ac[i].w += r.w;
     }
   }
-  const int c = t * 4;
-  atomicAdd(&dgamma[c], ag.x); atomicAdd(&dgamma[c + 1], ag.y); atomicAdd(&dgamma[c + 2], ag.z); atomicAdd(&dgamma[c + 3], ag.w);
-  atomicAdd(&dbeta[c], ab.x); atomicAdd(&dbeta[c + 1], ab.y); atomicAdd(&dbeta[c + 2], ab.z); atomicAdd(&dbeta[c + 3], ab.w);
-  if (dxsum) { atomicAdd(&dxsum[c], ac.x); atomicAdd(&dxsum[c + 1], ac.y); atomicAdd(&dxsum[c + 2], ac.z); atomicAdd(&dxsum[c + 3], ac.w); }
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c = (lane + 32 * i) * 4;
+    atomicAdd(&red[0][c], ag[i].x); atomicAdd(&red[0][c + 1], ag[i].y); atomicAdd(&red[0][c + 2], ag[i].z); atomicAdd(&red[0][c + 3], ag[i].w);
+    atomicAdd(&red[1][c], ab[i].x); atomicAdd(&red[1][c + 1], ab[i].y); atomicAdd(&red[1][c + 2], ab[i].z); atomicAdd(&red[1][c + 3], ab[i].w);
+    atomicAdd(&red[2][c], ac[i].x); atomicAdd(&red[2][c + 1], ac[i].y); atomicAdd(&red[2][c + 2], ac[i].z); atomicAdd(&red[2][c + 3], ac[i].w);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 256) {
+    atomicAdd(&dgamma[c], red[0][c]);
+    atomicAdd(&dbeta[c], red[1][c]);
+    if (dxsum) atomicAdd(&dxsum[c], red[2][c]);
+  }
 }
 template <typename T>
 int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                     const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st, T* dx_cast,
                     float* dxsum) {
-  const int rpb = max(8, cdiv(rows, 148 * 3));
+  const int grid = std::min(cdiv(rows, 8), 148);
   if (C == 768)
-    layernorm_bwd_kernel<T, 768><<<cdiv(rows, rpb), 192, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast, dxsum);
+    layernorm_bwd_kernel<T, 768><<<grid, 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum);
   else if (C == 512)
-    layernorm_bwd_kernel<T, 512><<<cdiv(rows, rpb), 128, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, rpb, dx_cast, dxsum);
+    layernorm_bwd_kernel<T, 512><<<grid, 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum);
   else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
   S4G_KERNEL_CHECK();
   return 0;

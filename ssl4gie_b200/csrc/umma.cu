@@ -812,15 +812,23 @@ int make_act_map(CUtensorMap* map, const bf16* base, const ConvGeom& g, int C, i
   }
   return make_map(map, base, 4, dims, strides, box);
 }
-// Output-tile width: 256 columns whenever N allows.  Measured (profiles/r01_d): the K = 768 token GEMMs are bound by the
-// L2 -> smem operand fill (about 12 TB/s with single-CTA tiles), not by tcgen05 issue, so narrower tiles (192 / 128),
-// which would quantise better over 148 SMs, only add A-tile traffic and run slower.  S4G_FPROP_BN overrides for tests.
-int pick_block_n(int N, int tiles_m) {
+// Output-tile width.  Measured (profiles/r01_d): the token GEMMs are bound by the L2 -> smem operand fill (about 12 TB/s
+// chip-wide), not by tcgen05 issue, so the cost of a persistent launch is waves x bytes staged per K step (16 KB of A
+// rows plus this CTA's share of the B tile).  With CTA pairs N = 768 runs fastest as 4 x 192 columns (2.7 waves of
+// 28 KB steps instead of 2.03 -> 3 waves of 32 KB), N = 2304 / 3072 as 256-column tiles.  S4G_FPROP_BN overrides.
+int pick_block_n(int N, int row_tiles, int cg) {
   if (N <= 256) return (N + 15) / 16 * 16;
   static const int forced = getenv("S4G_FPROP_BN") ? atoi(getenv("S4G_FPROP_BN")) : 0;
   if (forced) return forced;
-  (void)tiles_m;
-  return 256;
+  const int groups = g_num_sms / cg;
+  int best = 256;
+  double best_cost = 1e30;
+  for (int bn = 256; bn >= 128; bn -= 64) {
+    const long long work = (long long)cdiv(row_tiles, cg) * cdiv(N, bn);
+    const double cost = (double)((work + groups - 1) / groups) * (A_STAGE_BYTES + bn * 128.0 / cg);
+    if (cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
 }
 
 }  // namespace
@@ -851,13 +859,14 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
   p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
   p.chunks = cdiv(g.Cin, BLOCK_K);
   const int row_tiles = p.tg.tw * p.tg.th * p.tg.tn;
-  p.block_n = pick_block_n(g.Cout, row_tiles);
+  // CTA pairs (cta_group::2) whenever there are at least two row tiles; S4G_FPROP_CG=1 forces the single-CTA kernel
+  static const int forced_cg = getenv("S4G_FPROP_CG") ? atoi(getenv("S4G_FPROP_CG")) : 0;
+  int cg = forced_cg ? forced_cg : (row_tiles >= 2 ? 2 : 1);
+  p.block_n = pick_block_n(g.Cout, row_tiles, cg);
+  if (p.block_n % 32) cg = 1;
   p.N = g.Cout;
   p.tiles_n = cdiv(g.Cout, p.block_n);
   p.e = e;
-  // CTA pairs (cta_group::2) whenever there are at least two row tiles; S4G_FPROP_CG=1 forces the single-CTA kernel
-  static const int forced_cg = getenv("S4G_FPROP_CG") ? atoi(getenv("S4G_FPROP_CG")) : 0;
-  const int cg = forced_cg ? forced_cg : (row_tiles >= 2 && p.block_n % 32 == 0 ? 2 : 1);
   p.tiles_m = cdiv(row_tiles, cg);
   const int stage_bytes = A_STAGE_BYTES + (p.block_n / cg) * 128;
   const size_t fixed = 1024 + EPI_WARPS * EPI_WARP_BYTES + sizeof(SmemCtl);
