@@ -20,8 +20,7 @@
 namespace {
 
 constexpr int BLOCK_K = 64;           // bf16 elements = 128 B = one swizzle row
-constexpr int STAGES = 4;              // wgrad kernel
-constexpr int MAX_STAGES = 8;          // fprop kernel: as many as fit beside the epilogue staging
+constexpr int MAX_STAGES = 8;          // smem ring depth: as many stages as fit, at most this
 constexpr int A_STAGE_BYTES = 128 * 128;  // 128 rows x 128 B
 constexpr int NUM_THREADS = 192;          // wgrad kernel: producer, MMA issuer, 4 epilogue warps
 constexpr int EPI_WARPS = 8;              // fprop kernel: two epilogue warps per TMEM lane quarter (column slabs alternate)
@@ -538,35 +537,42 @@ struct WgradParams {
   TileGeom tg;      // 64-pixel chunks
   int taps, S, pad;
   int Cout, Cin, K;  // K = taps * Cin (row length of dW)
-  int tiles_co, tiles_ci, block_n, splits;
+  int tiles_co, tiles_ci, block_n, splits;   // tiles_co: 128*CG-row output tiles
+  int stages;        // smem ring depth
   int chunks_total;  // pixel chunks
   int chunks_per_split;
   float* part;       // split-K partials: [split][tap][tci][tco][block_n columns (ci)][128 rows (co)] fp32
 };
 
+// CG = 2: a CTA pair owns a 256 (co) x block_n (ci) output tile (cta_group::2): each CTA stages its own 128 dY channels
+// and HALF of the X channels of every pixel chunk -- a third less L2 -> smem traffic per FLOP and a deeper ring.
+template <int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid_constant__ CUtensorMap tmY,
                                                                     const __grid_constant__ CUtensorMap tmX, const WgradParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
   const int a_bytes = 2 * BLOCK_K * 128;                   // two 64-channel groups of dY, 64 pixels each
-  const int ngroups = p.block_n / 64;
+  const int ngroups = p.block_n / 64 / CG;                 // 64-channel groups of X staged by this CTA
   const int stage_bytes = a_bytes + ngroups * BLOCK_K * 128;
-  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + STAGES * stage_bytes);
+  const int STG = p.stages;
+  SmemCtl* ctl = reinterpret_cast<SmemCtl*>(smem + STG * stage_bytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int out_tiles = p.tiles_co * p.tiles_ci * p.taps;
   const int num_work = out_tiles * p.splits;
   const int chunks_per_split = p.chunks_per_split;
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
+  const int group = blockIdx.x / CG, num_groups = gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmY);
     tma_prefetch_desc(&tmX);
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4); }
+    for (int i = 0; i < STG; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4 * CG); }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
+  if (warp == 1) { if (CG == 2) tmem_alloc_pair(&ctl->tmem_base, 512); else tmem_alloc(&ctl->tmem_base, 512); }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
 
@@ -580,9 +586,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   if (warp == 0) {
     if (elect_one()) {
       int stage = 0; uint32_t phase = 0;
-      for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+      for (int wi = group; wi < num_work; wi += num_groups) {
         int split, tap, tci, tco;
         decode(wi, split, tap, tci, tco);
+        const int co0 = (tco * CG + rank) * 128;
+        const int ci0 = tci * p.block_n + rank * (p.block_n / CG);
         const int dy = tap / p.S - p.pad, dx = tap % p.S - p.pad;
         const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
         for (int c = c_begin; c < c_end; ++c) {
@@ -590,19 +598,26 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
           tile_origin(p.tg, c, n0, h0, w0);
           mbar_wait(&ctl->empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * stage_bytes;
-          mbar_expect_tx(&ctl->full[stage], stage_bytes);
-          for (int g = 0; g < 2; ++g) tma_load_4d(&tmY, &ctl->full[stage], sa + g * BLOCK_K * 128, tco * 128 + g * 64, w0, h0, n0);
-          for (int g = 0; g < ngroups; ++g)
-            tma_load_4d(&tmX, &ctl->full[stage], sa + a_bytes + g * BLOCK_K * 128, tci * p.block_n + g * 64, w0 + dx, h0 + dy, n0);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (CG == 2) {
+            if (rank == 0) mbar_expect_tx(&ctl->full[stage], 2 * stage_bytes);   // the leader's barrier collects both CTAs' bytes
+            for (int g = 0; g < 2; ++g) tma_load_4d_pair(&tmY, &ctl->full[stage], sa + g * BLOCK_K * 128, co0 + g * 64, w0, h0, n0);
+            for (int g = 0; g < ngroups; ++g)
+              tma_load_4d_pair(&tmX, &ctl->full[stage], sa + a_bytes + g * BLOCK_K * 128, ci0 + g * 64, w0 + dx, h0 + dy, n0);
+          } else {
+            mbar_expect_tx(&ctl->full[stage], stage_bytes);
+            for (int g = 0; g < 2; ++g) tma_load_4d(&tmY, &ctl->full[stage], sa + g * BLOCK_K * 128, co0 + g * 64, w0, h0, n0);
+            for (int g = 0; g < ngroups; ++g)
+              tma_load_4d(&tmX, &ctl->full[stage], sa + a_bytes + g * BLOCK_K * 128, ci0 + g * 64, w0 + dx, h0 + dy, n0);
+          }
+          if (++stage == STG) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc(128, p.block_n, 1, 1);
+    const uint32_t idesc = make_idesc(128 * CG, p.block_n, 1, 1);
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+    for (int wi = group; wi < num_work && rank == 0; wi += num_groups) {
       int split, tap, tci, tco;
       decode(wi, split, tap, tci, tco);
       const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
@@ -621,26 +636,34 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
             // MN-major: 16 pixels = two 8-row atoms (SBO = 1024 B); 64-channel groups are LBO = 64 px * 128 B apart
             const uint64_t da = make_desc(sa + kk * 2048, BLOCK_K * 128, 1024);
             const uint64_t db = make_desc(sb + kk * 2048, BLOCK_K * 128, 1024);
-            umma_bf16(tmem_d, da, db, idesc, (c != c_begin) || kk != 0);
+            if (CG == 2) umma_bf16_pair(tmem_d, da, db, idesc, (c != c_begin) || kk != 0);
+            else umma_bf16(tmem_d, da, db, idesc, (c != c_begin) || kk != 0);
           }
-          umma_commit(&ctl->empty[stage]);
-          if (c == c_end - 1) umma_commit(&ctl->tfull[acc]);
+          if (CG == 2) {
+            umma_commit_pair(&ctl->empty[stage]);
+            if (c == c_end - 1) umma_commit_pair(&ctl->tfull[acc]);
+          } else {
+            umma_commit(&ctl->empty[stage]);
+            if (c == c_end - 1) umma_commit(&ctl->tfull[acc]);
+          }
         }
         __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == STG) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
     const int q = warp & 3;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int wi = blockIdx.x; wi < num_work; wi += gridDim.x) {
+    for (int wi = group; wi < num_work; wi += num_groups) {
       int split, tap, tci, tco;
       decode(wi, split, tap, tci, tco);
       const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
       if (c_begin >= c_end) continue;
-      // partial tile, column-major (co contiguous): each store instruction of a warp writes 128 contiguous bytes
-      float* part = p.part + (size_t)wi * 128 * p.block_n + q * 32 + lane;
+      // partial tile of this CTA's 128 rows, column-major (co contiguous): each store instruction of a warp writes 128
+      // contiguous bytes.  Scratch layout [split][tap][tci][128-row tile][column][128]: the reduce kernels see 128-row tiles.
+      const size_t ptile = (((size_t)split * p.taps + tap) * p.tiles_ci + tci) * (p.tiles_co * CG) + tco * CG + rank;
+      float* part = p.part + ptile * 128 * p.block_n + q * 32 + lane;
       mbar_wait(&ctl->tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
@@ -655,13 +678,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->tempty[acc]);
+      if (lane == 0) { if (CG == 2) mbar_arrive_leader(&ctl->tempty[acc]); else mbar_arrive(&ctl->tempty[acc]); }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 512);
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 1) { if (CG == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
 }
 
 // Deterministic split-K reduction + layout change: dW[co*so + ci*si + tap*st] = sum_split part[split][tap][tci][tco][ci][co]
@@ -845,7 +868,8 @@ int umma_init() {
   S4G_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-  S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   return 0;
 }
 
@@ -912,8 +936,9 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
 namespace {
 struct WgradPlan {
   TileGeom tg;
-  int block_n, tiles_co, tiles_ci, out_tiles, chunks_total, splits, cps;
-  size_t scratch_bytes;
+  int block_n, tiles_co, tiles_ci, out_tiles, chunks_total, splits, cps;   // tiles_co: 128*cg-row tiles
+  int cg, stages;
+  size_t scratch_bytes, smem_bytes;
 };
 // Split-K plan: enough (output tile x pixel range) work items to fill the SMs in whole waves, few enough that the
 // fp32 partials (written once, read once by the reduce kernel) stay cheap.
@@ -923,7 +948,15 @@ WgradPlan plan_wgrad(const ConvGeom& g) {
   w.tg = matrix ? matrix_tiles(g.Nimg, BLOCK_K) : make_tiles(g.Nimg, g.Hi, g.Wi, BLOCK_K);
   const int taps = g.R * g.S;
   w.block_n = std::min(256, (g.Cin + 63) / 64 * 64);
-  w.tiles_co = cdiv(g.Cout, 128);
+  // CTA pairs when a pair tile (256 co) is not mostly padding and each CTA's X share is whole 64-channel groups
+  static const int forced_cg = getenv("S4G_WGRAD_CG") ? atoi(getenv("S4G_WGRAD_CG")) : 0;
+  w.cg = forced_cg ? forced_cg : ((g.Cout > 128 && w.block_n % 128 == 0) ? 2 : 1);
+  if (w.block_n % 128) w.cg = 1;
+  const int stage_bytes = 2 * BLOCK_K * 128 + (w.block_n / 64 / w.cg) * BLOCK_K * 128;
+  w.stages = (int)std::min<size_t>(MAX_STAGES, (227 * 1024 - 1024 - sizeof(SmemCtl)) / stage_bytes);
+  w.smem_bytes = 1024 + (size_t)w.stages * stage_bytes + sizeof(SmemCtl);
+  const int groups = g_num_sms / w.cg;
+  w.tiles_co = cdiv(g.Cout, 128 * w.cg);
   w.tiles_ci = cdiv(g.Cin, w.block_n);
   w.out_tiles = w.tiles_co * w.tiles_ci * taps;
   w.chunks_total = w.tg.tw * w.tg.th * w.tg.tn;
@@ -936,11 +969,11 @@ WgradPlan plan_wgrad(const ConvGeom& g) {
     const int se = cdiv(w.chunks_total, cps);
     if (se != s) continue;
     const long long items = (long long)w.out_tiles * se;
-    const long long rounds = (items + g_num_sms - 1) / g_num_sms;
-    const double t = rounds * (cps * t_chunk + 2.0) + items * tile_bytes * 2 / 3.0e6;
+    const long long rounds = (items + groups - 1) / groups;
+    const double t = rounds * (cps * t_chunk + 2.0) + items * w.cg * tile_bytes * 2 / 3.0e6;
     if (t < best) { best = t; w.splits = se; w.cps = cps; }
   }
-  w.scratch_bytes = (size_t)w.out_tiles * w.splits * 128 * w.block_n * sizeof(float);
+  w.scratch_bytes = (size_t)w.out_tiles * w.cg * w.splits * 128 * w.block_n * sizeof(float);
   return w;
 }
 }  // namespace
@@ -967,23 +1000,36 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   p.tiles_ci = w.tiles_ci;
   p.chunks_total = w.chunks_total;
   p.splits = w.splits;
+  p.stages = w.stages;
   p.chunks_per_split = w.cps;
   p.part = scratch;
   CUtensorMap tmY, tmX;
   S4G_TRY(make_act_map(&tmY, dY, g, g.Cout, g.ldy, p.tg, matrix, g.Hi, g.Wi));
   S4G_TRY(make_act_map(&tmX, X, g, g.Cin, g.ldx, p.tg, matrix, g.Hi, g.Wi));
-  const size_t smem = 1024 + (size_t)STAGES * (2 * BLOCK_K * 128 + (p.block_n / 64) * BLOCK_K * 128) + sizeof(SmemCtl);
-  const int grid = std::min(w.out_tiles * p.splits, g_num_sms);
-  umma_wgrad_kernel<<<grid, NUM_THREADS, smem, st>>>(tmY, tmX, p);
+  if (w.cg == 2) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * std::min(w.out_tiles * p.splits, g_num_sms / 2));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = w.smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_wgrad_kernel<2>, tmY, tmX, p));
+  } else {
+    const int grid = std::min(w.out_tiles * p.splits, g_num_sms);
+    umma_wgrad_kernel<1><<<grid, NUM_THREADS, w.smem_bytes, st>>>(tmY, tmX, p);
+  }
   S4G_KERNEL_CHECK();
   WgradReduceParams r{};
   r.part = scratch; r.dW = dW;
-  r.Cout = g.Cout; r.Cin = g.Cin; r.taps = p.taps; r.tiles_co = p.tiles_co; r.tiles_ci = p.tiles_ci; r.block_n = p.block_n;
+  r.Cout = g.Cout; r.Cin = g.Cin; r.taps = p.taps; r.tiles_co = p.tiles_co * w.cg; r.tiles_ci = p.tiles_ci; r.block_n = p.block_n;
   r.splits = p.splits;
   if (torch_layout) { r.so = (long long)g.Cin * p.taps; r.si = p.taps; r.st = 1; }   // [Cout][Cin][R][S]
   else { r.so = p.K; r.si = 1; r.st = g.Cin; }                                        // packed [Cout][tap][Cin]
   if (p.taps == 1 && r.si == 1)
-    wgrad_reduce_linear_kernel<<<p.tiles_co * p.tiles_ci * (p.block_n / 32), 256, 0, st>>>(r);
+    wgrad_reduce_linear_kernel<<<r.tiles_co * r.tiles_ci * (r.block_n / 32), 256, 0, st>>>(r);
   else
     wgrad_reduce_kernel<<<dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps), dim3(32, 8), 0, st>>>(r);
   S4G_KERNEL_CHECK();
