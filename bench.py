@@ -19,7 +19,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GFLOP_PER_IMG = {"seg": 225.97, "depth": 214.86}  # fwd+bwd = 3 x fwd, BASELINE.md §2
+GFLOP_PER_IMG = {"seg": 225.97, "depth": 214.86, "cls": 105.38}  # fwd+bwd = 3 x fwd, BASELINE.md §2 / SURVEY.md §8d
 METRIC = "ViT-B/DPT seg train img/s @1/2/4/8 B200; % tensor-pipe peak; CPU baseline"
 
 
@@ -78,6 +78,8 @@ def synth(task, B, seed):
     x = torch.randn(B, 3, 224, 224, generator=g)
     if task == "seg":
         t = (torch.rand(B, 1, 224, 224, generator=g) > 0.5).float()
+    elif task == "cls":
+        t = torch.randint(0, 23, (B,), generator=g)
     else:
         t = torch.rand(B, 1, 224, 224, generator=g)
         t[torch.rand(B, 1, 224, 224, generator=g) < 0.1] = 0.0
@@ -92,7 +94,7 @@ def cpu_step_time(task, steps, warmup, batch=2):
     import torch
     from oracle import ref_port
     torch.set_num_threads(os.cpu_count())
-    sd = ref_port.make_state(task, seed=42)
+    sd = ref_port.make_state(None, seed=42, head_classes=23) if task == "cls" else ref_port.make_state(task, seed=42)
     params = {k: v.clone().requires_grad_(True) for k, v in ref_port.trainable(sd).items()}
     full = dict(sd)
     full.update(params)
@@ -102,8 +104,11 @@ def cpu_step_time(task, steps, warmup, batch=2):
     for i in range(warmup + steps):
         t0 = time.perf_counter()
         opt.zero_grad()
-        out = ref_port.forward(full, x, task, True, None)
-        loss = ref_port.soft_dice_loss(out, t) if task == "seg" else ref_port.ssi_loss(out, t, 0.1)
+        out = ref_port.forward(full, x, None if task == "cls" else task, True, None)
+        if task == "cls":
+            loss = ref_port.weighted_ce_loss(out, t, torch.ones(23))
+        else:
+            loss = ref_port.soft_dice_loss(out, t) if task == "seg" else ref_port.ssi_loss(out, t, 0.1)
         loss.backward()
         opt.step()
         if i >= warmup:
@@ -131,6 +136,10 @@ def run_reference(args):
 
 # --------------------------------------------------------------------------------------------- GPU arm
 def run_ours(args):
+    # ONE JSON line on stdout: route everything else written to fd 1 (NCCL's version banner, ...) to stderr
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -140,19 +149,25 @@ def run_ours(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    from ssl4gie_b200 import FusedAdamW, ScaleAndShiftInvariantLoss, SoftDiceLoss, utils
+    from ssl4gie_b200 import CrossEntropyLoss, FusedAdamW, ScaleAndShiftInvariantLoss, SoftDiceLoss, utils
     from ssl4gie_b200.ddp import GradientAllReduce
     from ssl4gie_b200.engine import Engine
 
     task, B = args.task, args.batch
     torch.manual_seed(42)
-    model = utils.get_ImageNet_or_random_ViT(False, 1 if task == "seg" else None, False, task, False, False)
+    if task == "cls":  # BASELINE.json configs[3]: 23-class Hyperkvasir-labelled fine-tune
+        model = utils.get_ImageNet_or_random_ViT(True, 23, False, None, False, False)
+    else:
+        model = utils.get_ImageNet_or_random_ViT(False, 1 if task == "seg" else None, False, task, False, False)
     model.precision, model.backend = "bf16", "tensor"
     model = model.cuda(local)
     if world > 1 and task == "seg":
         model = torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)  # reference train_segmentation.py:199
     model.train()
-    loss_fn = SoftDiceLoss() if task == "seg" else ScaleAndShiftInvariantLoss(alpha=0.1)
+    if task == "cls":
+        loss_fn = CrossEntropyLoss(torch.ones(23)).cuda(local)
+    else:
+        loss_fn = SoftDiceLoss() if task == "seg" else ScaleAndShiftInvariantLoss(alpha=0.1)
     opt = FusedAdamW(model, lr=1e-4, grad_scale=1.0 / world)
     ddp = GradientAllReduce(model)
     ddp.prepare(B)
@@ -174,7 +189,7 @@ def run_ours(args):
         launches["n"] += h.launches()
         loss = loss_fn(out, t)
         loss.backward()
-        launches["n"] += h.launches() + (4 if task == "seg" else 8)
+        launches["n"] += h.launches() + {"seg": 4, "depth": 8, "cls": 2}[task]
         ddp.reduce()
         opt.step()
         launches["n"] += 1
@@ -212,7 +227,7 @@ def run_ours(args):
         step(True)
     ms_e2e, _ = timed(args.steps, True)
 
-    roof = kernel_roofline(B) if rank == 0 else None
+    roof = kernel_roofline(min(B, 64)) if rank == 0 else None
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sec, cores = cpu_step_time(task, 8, 2)
@@ -232,9 +247,11 @@ def run_ours(args):
                 "peaks_source": src, "loss": float(loss.item()),
                 "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
                 "e2e": {"value": world * B * args.steps / (ms_e2e / 1e3), "unit": "img/s",
-                        "h2d_bytes_per_step": (x_h.numel() + t_h.numel()) * 4, "d2h_bytes_per_step": 4},
+                        "h2d_bytes_per_step": x_h.numel() * x_h.element_size() + t_h.numel() * t_h.element_size(),
+                        "d2h_bytes_per_step": 4},
                 "gpu_launches": n_launch}
-        print(json.dumps(line), flush=True)
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     if world > 1:
         dist.destroy_process_group()
 
@@ -277,10 +294,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--task", default="seg", choices=["seg", "depth"])
-    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--task", default="seg", choices=["seg", "depth", "cls"])
+    ap.add_argument("--batch", type=int, default=0, help="images per GPU (default: 64 seg/depth, 128 cls as BASELINE.json)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.batch <= 0:
+        args.batch = 128 if args.task == "cls" else 64
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -145,6 +145,12 @@ int s4g_ssi_fwd(const float* pred, const float* target, void* scratch, float* lo
                 int W, float alpha, int scales, void* stream);
 int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const float* grad_out, float* dpred, int B,
                 int H, int W, float alpha, int scales, void* stream);
+/* nn.CrossEntropyLoss(weight) of the classification fine-tune (Classification/train_classification.py:278):
+ * loss = sum_i w[y_i] * -log softmax(x_i)[y_i] / sum_i w[y_i].  labels int64 [B]; class_weight [num_classes] or NULL.
+ * dlogits_unit [B,num_classes] receives dloss/dlogits for grad_out = 1 (kept between fwd and bwd). */
+int s4g_ce_fwd(const float* logits, const long long* labels, const float* class_weight, float* loss, float* dlogits_unit,
+               int B, int num_classes, void* stream);
+int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits, int B, int num_classes, void* stream);
 
 /* torch.optim.AdamW step over a flat fp32 arena (train_segmentation.py:204). grad_scale multiplies g first
  * (1/world_size after a sum-all-reduce). step counts from 1. */

@@ -115,6 +115,38 @@ def run(dense):
     return model
 
 
+def run_cls(out_token):
+    """Classification branch (Models/models.py:338,348-354) with the 23-class weighted CE of
+    Classification/train_classification.py:157,278, through the UNMODIFIED reference module."""
+    torch.manual_seed(42)
+    model = ref_utils.get_ImageNet_or_random_ViT(True, 23, False, None, False, False, out_token=out_token)
+    sd = ref_port.make_state(None, seed=42, head_classes=23)
+    missing, unexpected = model.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+    model.train()
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(2, 3, 224, 224, generator=g)
+    y = torch.tensor([3, 17])
+    cw = torch.linspace(0.5, 2.0, 23)
+    out = model(x)
+    loss = torch.nn.CrossEntropyLoss(cw)(out, y)
+    loss.backward()
+    grads = {n: p.grad for n, p in model.named_parameters() if p.grad is not None}
+    o2, l2, g2 = ref_port.loss_and_grads(sd, x, y, None, out_token=out_token, class_weights=cw)
+    err = (o2 - out.detach()).abs().max().item() / out.detach().abs().max().item()
+    assert err < 1e-5, err
+    assert abs(l2.item() - loss.item()) < 1e-6 * max(1, abs(loss.item()))
+    worst = max((g2[n] - g).abs().max().item() / (g.abs().max().item() + 1e-20) for n, g in grads.items())
+    assert worst < 1e-4, worst
+    assert sorted(n for n, gg in g2.items() if gg is None) == sorted(n for n, p in model.named_parameters() if p.grad is None)
+    print(f"[cls/{out_token}] ref_port vs reference: out {err:.2e} loss {abs(l2.item()-loss.item()):.2e} grads {worst:.2e}")
+    names = sorted(grads)
+    fix = {"loss": np.float64(loss.item()), "logits": out.detach().numpy(), "labels": y.numpy(), "class_weights": cw.numpy(),
+           "grad_names": np.array(names), "grad_norm": np.array([grads[n].double().norm().item() for n in names]),
+           "grad_head": np.stack([np.pad(grads[n].flatten()[:8].numpy(), (0, max(0, 8 - grads[n].numel()))) for n in names])}
+    np.savez_compressed(os.path.join(OUT, f"step_cls_{out_token}_b2.npz"), **fix)
+
+
 def loss_kats():
     """RNG-free known-answer tests straight from the reference loss code."""
     kat = {}
@@ -193,8 +225,13 @@ if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
     loss_kats()
-    run("seg")
-    run("depth")
+    if "--cls-only" not in sys.argv:
+        run("seg")
+        run("depth")
+    run_cls("cls")
+    run_cls("spatial")
+    if "--cls-only" in sys.argv:
+        sys.exit(0)
     try:
         variants_manifest()
     except Exception as e:  # variants are informational; the step fixtures above are the pins

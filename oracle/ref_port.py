@@ -325,12 +325,29 @@ def trainable(sd):
     return {k: v for k, v in sd.items() if not k.endswith(NON_TRAINABLE_SUFFIXES)}
 
 
-def loss_and_grads(sd, x, target, dense="seg", dropout_mask=None, alpha=0.1, stats_out=None):
-    """One reference fwd+loss+bwd (Binary_segmentation/train_segmentation.py:44-47 without AMP scaling)."""
+def weighted_ce_loss(logits, labels, class_weights=None):
+    """nn.CrossEntropyLoss(torch.tensor(class_weights)) as built at Classification/train_classification.py:278:
+    sum_i w[y_i] * (-log softmax(x_i)[y_i]) / sum_i w[y_i]."""
+    logp = torch.log_softmax(logits.float(), dim=1)
+    nll = -logp.gather(1, labels.view(-1, 1)).squeeze(1)
+    if class_weights is None:
+        return nll.mean()
+    w = class_weights.to(nll.dtype)[labels]
+    return (w * nll).sum() / w.sum()
+
+
+def loss_and_grads(sd, x, target, dense="seg", dropout_mask=None, alpha=0.1, stats_out=None, out_token="cls",
+                   class_weights=None):
+    """One reference fwd+loss+bwd (Binary_segmentation/train_segmentation.py:44-47 without AMP scaling; dense=None:
+    Classification/train_classification.py:44-47 with integer class labels as target)."""
     params = {k: v.detach().clone().requires_grad_(True) for k, v in trainable(sd).items()}
     full = dict(sd)
     full.update(params)
-    out = forward(full, x, dense, True, dropout_mask, stats_out)
+    out = forward(full, x, dense, True, dropout_mask, stats_out, out_token)
+    if not dense:
+        loss = weighted_ce_loss(out, target, class_weights)
+        loss.backward()
+        return out.detach(), loss.detach(), {k: v.grad for k, v in params.items()}
     loss = soft_dice_loss(out, target) if dense == "seg" else ssi_loss(out, target, alpha)
     loss.backward()
     grads = {k: v.grad for k, v in params.items()}

@@ -54,6 +54,8 @@ SIGNATURES = {
     "s4g_ssi_scratch_bytes": (_sz, [_i]),
     "s4g_ssi_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp]),
     "s4g_ssi_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp]),
+    "s4g_ce_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "s4g_ce_bwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "s4g_adamw_step": (_i, [_vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _f, _i, _f, _vp]),
 }
 

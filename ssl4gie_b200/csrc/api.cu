@@ -129,6 +129,14 @@ int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const flo
                 int W, float alpha, int scales, void* stream) {
   return k_ssi_bwd(pred, target, (const float*)scratch, grad_out, dpred, B, H, W, alpha, scales, ST(stream));
 }
+int s4g_ce_fwd(const float* logits, const long long* labels, const float* class_weight, float* loss, float* dlogits_unit, int B,
+               int num_classes, void* stream) {
+  if (!logits || !labels || !loss || !dlogits_unit || B <= 0 || num_classes <= 0) { s4g_set_error("ce_fwd: bad argument"); return S4G_ERR_SHAPE; }
+  return k_ce_fwd(logits, labels, class_weight, loss, dlogits_unit, B, num_classes, ST(stream));
+}
+int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits, int B, int num_classes, void* stream) {
+  return k_ce_bwd(dlogits_unit, grad_out, dlogits, B, num_classes, ST(stream));
+}
 int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
                    float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
   return k_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, grad_scale, ST(stream));

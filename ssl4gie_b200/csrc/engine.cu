@@ -709,20 +709,37 @@ struct Builder {
     S4GModel* mm = m;
     bwd = &m->bwd_dec;
     const long long Tk = (long long)B * 197;
+    const bool train_enc = !m->d.frozen;
+    const int nc = m->d.num_classes;
+    const int spatial = m->d.out_token;
     Param* nw = P("norm.weight");
     Param* nb = P("norm.bias");
+    Param* hw = nc > 0 ? P("lin_head.weight") : nullptr;
+    Param* hb = nc > 0 ? P("lin_head.bias") : nullptr;
     const size_t hn = alloc(sizeof(T) * Tk * 768), mean = alloc(sizeof(float) * Tk), rstd = alloc(sizeof(float) * Tk);
-    const size_t pooled = alloc(sizeof(T) * (size_t)B * 768), dpooled = alloc(sizeof(T) * (size_t)B * 768);
-    const size_t dhn = alloc(sizeof(T) * Tk * 768), logit_t = alloc(sizeof(T) * (size_t)B * std::max(1, m->d.num_classes));
-    const bool has_head = m->d.num_classes > 0;
-    Lin head{};
-    if (has_head) head = linear("lin_head", m->d.num_classes, 768);
-    (void)hn; (void)mean; (void)rstd; (void)pooled; (void)dpooled; (void)dhn; (void)logit_t; (void)head; (void)nw; (void)nb;
-    (void)self; (void)mm;
-    s4g_set_error("classification branch (S4G_DENSE_NONE) is scheduled for the next round");
-    unsupported = true;
+    const size_t pooled = alloc(sizeof(float) * (size_t)B * 768);
+    const size_t dhn = train_enc ? alloc(sizeof(T) * Tk * 768) : 0;
+    const size_t xlast = xs[24];
+    m->fwd.push_back([=](cudaStream_t st) {
+      mm->launches += 3;
+      S4G_TRY(k_layernorm_fwd<T>(mm->template at<float>(xlast), nw->p, nb->p, mm->template at<T>(hn), mm->template at<float>(mean),
+                                 mm->template at<float>(rstd), (int)Tk, 768, 1e-6f, st));
+      return k_cls_head_fwd<T>(mm->template at<T>(hn), hw ? hw->p : nullptr, hb ? hb->p : nullptr, mm->template at<float>(pooled),
+                               mm->out, self->B, nc, 768, spatial, st);
+    });
+    bwd->push_back([=](cudaStream_t st) {
+      mm->launches += 3;
+      S4G_TRY(k_cls_head_bwd<T>(mm->dout, mm->template at<float>(pooled), hw ? hw->p : nullptr, hw ? hw->g : nullptr,
+                                hb ? hb->g : nullptr, train_enc ? mm->template at<T>(dhn) : nullptr, self->B, nc, 768, spatial, st));
+      if (!train_enc) return 0;
+      if (nw->g) S4G_CUDA(cudaMemsetAsync(nw->g, 0, sizeof(float) * 768, st));
+      if (nb->g) S4G_CUDA(cudaMemsetAsync(nb->g, 0, sizeof(float) * 768, st));
+      // gradient of the last block's output lands in dxa, where the encoder backward expects it
+      return k_layernorm_bwd<T>(mm->template at<T>(dhn), mm->template at<float>(xlast), nw->p, mm->template at<float>(mean),
+                                mm->template at<float>(rstd), nullptr, mm->template at<float>(self->dxa), nw->g, nb->g, (int)Tk, 768, st,
+                                nullptr, nullptr);
+    });
   }
-  bool unsupported = false;
 
   int finish() {
     dwp_scratch = alloc(dwp_bytes);
@@ -734,7 +751,7 @@ struct Builder {
       s4g_set_error(s);
       return S4G_ERR_NAME;
     }
-    return unsupported ? S4G_ERR_STATE : 0;
+    return 0;
   }
 };
 

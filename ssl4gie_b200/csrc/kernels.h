@@ -48,6 +48,13 @@ template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t s
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st);  // out zeroed by caller
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out = nullptr);  // inverse of above (+ optional T copy of the result)
+// classification tail (cls_head.cu): token pooling + lin_head on fp32 master weights; W == nullptr: no head (out = pooled)
+template <typename T>
+int k_cls_head_fwd(const T* hn, const float* W, const float* bias, float* pooled, float* out, int B, int N, int C,
+                   int spatial, cudaStream_t st);
+template <typename T>
+int k_cls_head_bwd(const float* dout, const float* pooled, const float* W, float* dW, float* db, T* dhn, int B, int N,
+                   int C, int spatial, cudaStream_t st);
 template <typename T> int k_cast_f32(const float* in, T* out, long long n, cudaStream_t st);
 template <typename T> int k_relu(const T* x, T* y, long long n, cudaStream_t st);
 // dx = (dskip ? dskip : 0) + (x > 0 ? dr : 0)
@@ -130,6 +137,9 @@ int k_dice_bwd(const float* logits, const float* targets, const float* sums, con
                int HW, float smooth, cudaStream_t st);
 int k_ssi_fwd(const float* pred, const float* targ, float* scratch, float* loss, float* ssi_out, int B, int H, int W,
               float alpha, int scales, cudaStream_t st);
+int k_ce_fwd(const float* logits, const long long* labels, const float* weight, float* loss, float* dlogits_unit, int B, int N,
+             cudaStream_t st);
+int k_ce_bwd(const float* dlogits_unit, const float* gout, float* dlogits, int B, int N, cudaStream_t st);
 int k_ssi_bwd(const float* pred, const float* targ, const float* scratch, const float* gout, float* dpred, int B, int H,
               int W, float alpha, int scales, cudaStream_t st);
 size_t ssi_scratch_floats(int B);

@@ -249,3 +249,60 @@ int k_ssi_bwd(const float* pred, const float* targ, const float* scratch, const 
   S4G_KERNEL_CHECK();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------ weighted cross-entropy
+// nn.CrossEntropyLoss(weight) as used at Classification/train_classification.py:278:
+//   loss = sum_i w[y_i] * (logsumexp(x_i) - x_i[y_i]) / sum_i w[y_i];  dL/dx_i = w[y_i] * (softmax(x_i) - onehot(y_i)) / sum w
+// One block (B <= a few hundred rows, N ~ 23 classes): a warp per row, block reduction of the two sums, and in the same
+// launch the gradient (scaled by grad_out = 1 when called from forward; backward only rescales).
+namespace {
+__global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                                                 const float* __restrict__ weight, float* __restrict__ loss,
+                                                 float* __restrict__ dlogits, int B, int N) {
+  __shared__ float s_num[8], s_den[8];
+  __shared__ float s_inv;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float num = 0.f, den = 0.f;
+  for (int b = warp; b < B; b += 8) {
+    const float* x = logits + (long long)b * N;
+    float mx = -INFINITY;
+    for (int c = lane; c < N; c += 32) mx = fmaxf(mx, x[c]);
+    mx = warp_max(mx);
+    float se = 0.f;
+    for (int c = lane; c < N; c += 32) se += __expf(x[c] - mx);
+    se = warp_sum(se);
+    const int y = (int)labels[b];
+    const float w = weight ? weight[y] : 1.f;
+    const float lse = mx + __logf(se);
+    num += w * (lse - x[y]);
+    den += w;
+    for (int c = lane; c < N; c += 32) dlogits[(long long)b * N + c] = w * (__expf(x[c] - lse) - (c == y ? 1.f : 0.f));
+  }
+  if (lane == 0) { s_num[warp] = num; s_den[warp] = den; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, d = 0.f;
+    for (int k = 0; k < 8; ++k) { a += s_num[k]; d += s_den[k]; }
+    *loss = a / d;
+    s_inv = 1.f / d;
+  }
+  __syncthreads();
+  const float inv = s_inv;
+  for (int i = threadIdx.x; i < B * N; i += 256) dlogits[i] *= inv;
+}
+__global__ void scale_kernel(const float* __restrict__ in, const float* __restrict__ g, float* __restrict__ out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i] * g[0];
+}
+}  // namespace
+int k_ce_fwd(const float* logits, const long long* labels, const float* weight, float* loss, float* dlogits_unit, int B, int N,
+             cudaStream_t st) {
+  ce_kernel<<<1, 256, 0, st>>>(logits, labels, weight, loss, dlogits_unit, B, N);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+int k_ce_bwd(const float* dlogits_unit, const float* gout, float* dlogits, int B, int N, cudaStream_t st) {
+  scale_kernel<<<cdiv((long long)B * N, 256), 256, 0, st>>>(dlogits_unit, gout, dlogits, B * N);
+  S4G_KERNEL_CHECK();
+  return 0;
+}

@@ -80,6 +80,8 @@ class Engine:
                 return False
             if getattr(model, "frozen", False) and not name.startswith("decoder."):
                 return False
+        elif getattr(model, "frozen", False) and not name.startswith("lin_head."):
+            return False  # frozen classification: the encoder runs under no_grad (Models/models.py:341-343)
         return True
 
     @torch.no_grad()
@@ -172,6 +174,7 @@ class _Handle:
         self.ptr = ctypes.c_void_p()
         _C.check(lib.s4g_model_create(ctypes.byref(desc), ctypes.byref(self.ptr)))
         self.batch, self.dense = batch, dense
+        self.out_features = int(getattr(model, "num_classes_head", 0) or 0) or 768
         for name, p in model.named_parameters():
             g = engine.grad_views.get(name)
             _C.check(lib.s4g_model_bind(self.ptr, name.encode(), _C.ptr(p.data), _C.ptr(g), p.numel()))
@@ -222,7 +225,7 @@ class _Handle:
         if self.dense:
             out = torch.empty((B, 1, 224, 224), dtype=torch.float32, device=x.device)
         else:
-            raise NotImplementedError("classification branch is scheduled for the next round")
+            out = torch.empty((B, self.out_features), dtype=torch.float32, device=x.device)
         _C.check(_C.lib().s4g_model_forward(self.ptr, _C.ptr(x), _C.ptr(out), int(training), seed, _C.ptr(mask), _C.stream_ptr()))
         return out
 
@@ -261,7 +264,7 @@ class _ModelFn(torch.autograd.Function):
 
 
 def run_model(model, x):
-    """model(x) for the dense branches: [B,3,224,224] float -> [B,1,224,224] float32."""
+    """model(x): [B,3,224,224] float -> [B,1,224,224] float32 (dense) or [B,num_classes] / [B,768] (classification)."""
     _C.require_cuda(x, "input")
     if x.dim() != 4 or x.shape[1] != 3 or x.shape[2] != 224 or x.shape[3] != 224:
         # timm PatchEmbed asserts the input size (reference Models/models.py:326)

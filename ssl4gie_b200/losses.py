@@ -96,3 +96,42 @@ class ScaleAndShiftInvariantLoss(nn.Module):
         return self.__prediction_ssi
 
     prediction_ssi = property(__get_prediction_ssi)
+
+
+class _CEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, weight):
+        _C.require_cuda(logits, "logits")
+        lg = logits.detach().float().contiguous()
+        B, N = lg.shape
+        lab = labels.detach().to(device=lg.device, dtype=torch.int64).contiguous()
+        w = weight.detach().to(device=lg.device, dtype=torch.float32).contiguous() if weight is not None else None
+        loss = torch.empty((), dtype=torch.float32, device=lg.device)
+        unit = torch.empty_like(lg)
+        _C.check(_C.lib().s4g_ce_fwd(_C.ptr(lg), _C.ptr(lab), _C.ptr(w), _C.ptr(loss), _C.ptr(unit), B, N, _C.stream_ptr()))
+        ctx.save_for_backward(unit)
+        ctx.cfg = (logits.shape, logits.dtype)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (unit,) = ctx.saved_tensors
+        shape, dtype = ctx.cfg
+        g = gout.detach().float().contiguous()
+        d = torch.empty_like(unit)
+        _C.check(_C.lib().s4g_ce_bwd(_C.ptr(unit), _C.ptr(g), _C.ptr(d), unit.shape[0], unit.shape[1], _C.stream_ptr()))
+        return d.view(shape).to(dtype), None, None
+
+
+class CrossEntropyLoss(nn.Module):
+    """The loss of the classification fine-tune, nn.CrossEntropyLoss(torch.tensor(class_weights))
+    (reference Classification/train_classification.py:157,278): weighted mean over the batch, integer class labels."""
+
+    def __init__(self, weight=None):
+        super().__init__()
+        self.register_buffer("weight", None if weight is None else torch.as_tensor(weight, dtype=torch.float32))
+
+    def forward(self, logits, labels):
+        if logits.dim() != 2 or labels.dim() != 1:
+            raise ValueError("CrossEntropyLoss: logits [B, num_classes] and integer labels [B] expected")
+        return _CEFn.apply(logits, labels, self.weight)

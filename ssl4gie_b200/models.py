@@ -75,8 +75,8 @@ class _Backbone(nn.Module):
         self.backend = "auto"
 
     def forward(self, x):
-        if not self.dense:
-            raise NotImplementedError("classification branch (dense=None) is scheduled for the next round (SURVEY.md §8f-1)")
+        """dense: [B,1,224,224]; otherwise final norm + cls / mean-token pooling (+ lin_head): [B,num_classes] or [B,768]
+        (reference Models/models.py:340-357)."""
         return run_model(self, x)
 
 

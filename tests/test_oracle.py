@@ -145,3 +145,31 @@ def test_adamw_restatement_matches_torch():
         opt.step()
         ref_port.adamw_step(q, grad, m, v, step)
     assert torch.allclose(q, p.detach(), rtol=1e-6, atol=1e-8)
+
+
+@pytest.mark.parametrize("out_token", ["cls", "spatial"])
+def test_cls_step_matches_reference_fixture(out_token, golden_dir):
+    """Classification branch (Models/models.py:338,348-354) + the weighted CE of train_classification.py:278 at B=2:
+    the restatement reproduces the unmodified reference's logits, loss and every gradient."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    fix = np.load(os.path.join(golden_dir, f"step_cls_{out_token}_b2.npz"))
+    sd = ref_port.make_state(None, seed=42, head_classes=23)
+    x = torch.randn(2, 3, 224, 224, generator=torch.Generator().manual_seed(0))
+    y, cw = torch.from_numpy(fix["labels"]), torch.from_numpy(fix["class_weights"])
+    out, loss, grads = ref_port.loss_and_grads(sd, x, y, None, out_token=out_token, class_weights=cw)
+    assert (out - torch.from_numpy(fix["logits"])).abs().max().item() < 1e-5 * float(np.abs(fix["logits"]).max())
+    assert abs(loss.item() - float(fix["loss"])) < 1e-5 * abs(float(fix["loss"]))
+    assert all(g is not None for g in grads.values())  # the final norm and the head are live in this branch
+    floor = 1e-3 * float(np.median(fix["grad_norm"]))
+    for i, n in enumerate(fix["grad_names"].tolist()):
+        rn = float(fix["grad_norm"][i])
+        assert abs(grads[n].double().norm().item() - rn) < 2e-3 * max(rn, floor), n
+
+
+def test_weighted_ce_restatement_matches_torch():
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(16, 23, generator=g) * 2
+    y = torch.randint(0, 23, (16,), generator=g)
+    w = torch.rand(23, generator=g) + 0.5
+    assert torch.allclose(ref_port.weighted_ce_loss(x, y, w), torch.nn.CrossEntropyLoss(w)(x, y), rtol=1e-6)
+    assert torch.allclose(ref_port.weighted_ce_loss(x, y), torch.nn.CrossEntropyLoss()(x, y), rtol=1e-6)
