@@ -1,0 +1,104 @@
+"""Training-loop parity (north_star: "the loss curve tracking the reference to within 1% over 200 steps"; SURVEY.md §8c
+fixture 4): 200 AdamW steps (lr 1e-4, torch defaults, train_segmentation.py:204) on a fixed synthetic batch, the bf16
+tensor-core product path + FusedAdamW against the oracle restatement + torch.optim.AdamW in fp32 on the same GPU, same
+initial state, dropout p = 0."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import ref_port  # noqa: E402  (checker only)
+
+STEPS = 200
+
+
+def _curve_ours(task, sd, x, t, precision):
+    from ssl4gie_b200 import CrossEntropyLoss, FusedAdamW, ScaleAndShiftInvariantLoss, SoftDiceLoss, utils
+    if task == "cls":
+        m = utils.get_ImageNet_or_random_ViT(True, 23, False, None, False, False)
+        loss_fn = CrossEntropyLoss(torch.ones(23)).cuda()
+    else:
+        m = utils.get_ImageNet_or_random_ViT(False, 1 if task == "seg" else None, False, task, False, False)
+        loss_fn = SoftDiceLoss() if task == "seg" else ScaleAndShiftInvariantLoss(alpha=0.1)
+    m.load_state_dict(sd, strict=True)
+    if task == "seg":
+        m.decoder.output_conv[3].p = 0.0
+    m.precision = precision
+    m = m.cuda().train()
+    opt = FusedAdamW(m, lr=1e-4)
+    losses = []
+    for _ in range(STEPS):
+        loss = loss_fn(m(x), t)
+        loss.backward()
+        opt.step()
+        losses.append(loss.detach())
+    return torch.stack(losses).cpu()
+
+
+def _curve_oracle(task, sd, x, t):
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    sdg = {k: v.cuda() for k, v in sd.items()}
+    params = {k: v.clone().requires_grad_(True) for k, v in ref_port.trainable(sdg).items()}
+    full = dict(sdg)
+    full.update(params)
+    dense = None if task == "cls" else task
+    # parameters the reference never reaches keep grad None and are skipped by torch.optim.AdamW, as in the product
+    opt = torch.optim.AdamW(list(params.values()), lr=1e-4)
+    losses = []
+    for _ in range(STEPS):
+        opt.zero_grad(set_to_none=True)
+        out = ref_port.forward(full, x, dense, True, None)
+        if task == "cls":
+            loss = ref_port.weighted_ce_loss(out, t, torch.ones(23, device="cuda"))
+        else:
+            loss = ref_port.soft_dice_loss(out, t) if task == "seg" else ref_port.ssi_loss(out, t, 0.1)
+        loss.backward()
+        opt.step()
+        losses.append(loss.detach())
+    return torch.stack(losses).cpu()
+
+
+def _data(task, B):
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(B, 3, 224, 224, generator=g)
+    if task == "seg":
+        t = (torch.rand(B, 1, 224, 224, generator=g) > 0.5).float()
+    elif task == "cls":
+        t = torch.randint(0, 23, (B,), generator=g)
+    else:
+        t = torch.rand(B, 1, 224, 224, generator=g)
+        t[torch.rand(B, 1, 224, 224, generator=g) < 0.1] = 0.0
+        t[:, :, :8, :] = 0.0
+    return x.cuda(), t.cuda()
+
+
+@pytest.mark.parametrize("task", ["seg", "cls"])
+def test_bf16_loss_curve_tracks_reference_over_200_steps(task):
+    sd = ref_port.make_state(None, seed=42, head_classes=23) if task == "cls" else ref_port.make_state(task, seed=42)
+    x, t = _data(task, 4)
+    ours = _curve_ours(task, sd, x, t, "bf16")
+    ref = _curve_oracle(task, sd, x, t)
+    assert torch.isfinite(ours).all()
+    assert ref[-1] < ref[0]  # the reference does train on this batch
+    # 1 % of the reference loss at every step; for the cross-entropy curve, which falls towards 0, relative to the
+    # larger of the current loss and 5 % of the initial one
+    scale = torch.maximum(ref.abs(), 0.05 * ref[0].abs()) if task == "cls" else ref.abs()
+    dev = ((ours - ref).abs() / scale).max().item()
+    assert dev < 1e-2, (dev, ours[::20].tolist(), ref[::20].tolist())
+
+
+def test_fp32_loss_curve_matches_reference_closely():
+    """fp32 validation mode over 20 steps: the optimizer + schedule reproduce the reference trajectory.  A single step
+    matches to 1e-4 (test_gpu_model.py); over a trajectory Adam's g / sqrt(v) amplifies fp32 summation-order noise in
+    the near-zero gradient entries, so the bound here is 5e-4 (measured 1.3e-4 after 20 steps)."""
+    global STEPS
+    sd = ref_port.make_state("seg", seed=42)
+    x, t = _data("seg", 2)
+    keep, STEPS = STEPS, 20
+    try:
+        ours = _curve_ours("seg", sd, x, t, "fp32")
+        ref = _curve_oracle("seg", sd, x, t)
+    finally:
+        STEPS = keep
+    assert ((ours - ref).abs() / ref.abs()).max().item() < 5e-4, (ours.tolist(), ref.tolist())
