@@ -202,6 +202,7 @@ struct FpropParams {
   int tiles_m, tiles_n, block_n, N;   // tiles_m: row tiles per CTA group step (pairs of row tiles when CG == 2)
   int stages;                          // smem ring depth
   int tma_epi;       // 1: bf16 outputs staged in swizzled smem and written with TMA stores
+  int f32_epi;       // 1: fp32 outputs (+ fp32 residual) of a plain matrix, transposed through the staging slab (coalesced)
   long long M;       // rows of the output matrix (for the aux read guard)
   EpiParams e;
 };
@@ -507,6 +508,58 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
               }
             }
           }
+        }
+      } else if (p.f32_epi) {
+        // fp32 output (+ fp32 residual, the token residual stream): a thread owns a ROW of the accumulator, but rows are
+        // 3 KB apart in memory, so the 32 x 32 chunk goes through the warp's swizzled staging slab and is added to the
+        // residual / written with each warp instruction covering 4 rows x 128 contiguous bytes.  The residual loads
+        // are issued before the accumulator is read, so their latency hides behind tcgen05.ld.
+        const EpiParams& e = p.e;
+        float* outp = reinterpret_cast<float*>(e.out);
+        const float* resp = reinterpret_cast<const float*>(e.res);
+        uint8_t* buf = epi_smem + (warp - 2) * EPI_WARP_BYTES;
+        const long long row_base = (long long)tm * 128 + q * 32;
+        const int sub = lane >> 3, c4 = lane & 7;
+        for (int c0 = half * 32; c0 < p.block_n; c0 += 64) {
+          const int col0 = tn * p.block_n + c0;
+          const int col = col0 + c4 * 4;
+          float4 rv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const long long grow = row_base + i * 4 + sub;
+            rv[i] = (resp && grow < p.M && col < p.N) ? *reinterpret_cast<const float4*>(resp + grow * e.ldr + col)
+                                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          uint32_t v[32];
+          tmem_ld32(taddr + c0, v);
+          tmem_ld_wait();
+          if (c0 + 64 >= p.block_n) {   // last chunk of this warp: hand the TMEM stage back before the stores
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (CG == 2) mbar_arrive_leader(&ctl->tempty[acc]); else mbar_arrive(&ctl->tempty[acc]); }
+            released = true;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 f = make_float4(__uint_as_float(v[4 * j]) * e.alpha, __uint_as_float(v[4 * j + 1]) * e.alpha,
+                                   __uint_as_float(v[4 * j + 2]) * e.alpha, __uint_as_float(v[4 * j + 3]) * e.alpha);
+            if (e.bias && col0 + 4 * j < p.N) {
+              const float4 bb = *reinterpret_cast<const float4*>(e.bias + col0 + 4 * j);
+              f.x += bb.x; f.y += bb.y; f.z += bb.z; f.w += bb.w;
+            }
+            if (e.mode == EPI_RELU) { f.x = fmaxf(f.x, 0.f); f.y = fmaxf(f.y, 0.f); f.z = fmaxf(f.z, 0.f); f.w = fmaxf(f.w, 0.f); }
+            *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = f;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = i * 4 + sub;
+            const long long grow = row_base + rr;
+            float4 a = *reinterpret_cast<const float4*>(buf + rr * 128 + ((c4 ^ (rr & 7)) << 4));
+            a.x += rv[i].x; a.y += rv[i].y; a.z += rv[i].z; a.w += rv[i].w;
+            if (grow < p.M && col < p.N) *reinterpret_cast<float4*>(outp + grow * e.ldo + col) = a;
+          }
+          __syncwarp();
         }
       } else if (half == 0) {
         for (int c0 = 0; c0 < p.block_n; c0 += 32) {
@@ -908,6 +961,10 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
   p.M = (long long)g.Nimg * g.Hi * g.Wi;
   p.tma_epi = !(e.out_f32 || e.res || e.accumulate) && e.ldo % 8 == 0 && (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 &&
               (!e.out2 || (reinterpret_cast<uintptr_t>(e.out2) & 15) == 0);
+  p.f32_epi = matrix && e.out_f32 && !e.accumulate && (!e.res || e.res_f32) && !e.out2 &&
+              (e.mode == EPI_NONE || e.mode == EPI_RELU) && e.ldo % 4 == 0 && (!e.res || e.ldr % 4 == 0) && g.Cout % 4 == 0 &&
+              (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 && (reinterpret_cast<uintptr_t>(e.res) & 15) == 0 &&
+              (!e.bias || (reinterpret_cast<uintptr_t>(e.bias) & 15) == 0);
   CUtensorMap tmO = tmA, tmO2 = tmA;
   if (p.tma_epi) {
     S4G_TRY(make_act_map(&tmO, reinterpret_cast<const bf16*>(e.out), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
