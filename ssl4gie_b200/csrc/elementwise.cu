@@ -529,27 +529,41 @@ __device__ __forceinline__ void bil_src(int o, int in_size, float scale, int& i0
   l1 = s - i0;
   l0 = 1.f - l1;
 }
-// grid.y = image row of the output (b * Ho + oh), grid.x * 256 threads cover (ow, channel group): 32-bit index math only
+// grid.y = group of 4 output rows (b * Ho/4 + oh/4), grid.x * 256 threads cover (ow, channel group): 32-bit index math,
+// 16 independent 16 B loads in flight per thread
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const int idx = blockIdx.x * 256 + threadIdx.x;
   if (idx >= Wo * c8) return;
   const int g = idx % c8, ow = idx / c8;
-  const int oh = blockIdx.y % Ho, b = blockIdx.y / Ho;
-  int h0, h1, w0, w1; float lh0, lh1, lw0, lw1;
-  bil_src(oh, H, sh, h0, h1, lh0, lh1);
+  const int hq = (Ho + 3) / 4;   // the last group of an Ho that is not a multiple of 4 is cut by the guard below
+  const int oh0 = (blockIdx.y % hq) * 4, b = blockIdx.y / hq;
+  int w0, w1; float lw0, lw1;
   bil_src(ow, W, sw, w0, w1, lw0, lw1);
   const T* base = x + (size_t)b * H * W * C + g * 8;
-  Vec8<T> a, bq, c, d, o;
-  a.load(base + (size_t)(h0 * W + w0) * C); bq.load(base + (size_t)(h0 * W + w1) * C);
-  c.load(base + (size_t)(h1 * W + w0) * C); d.load(base + (size_t)(h1 * W + w1) * C);
+  Raw8<T> v[4][4];
+  float lh[4][2];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) o.v[i] = lh0 * (lw0 * a.v[i] + lw1 * bq.v[i]) + lh1 * (lw0 * c.v[i] + lw1 * d.v[i]);
-  o.store(y + ((size_t)blockIdx.y * Wo + ow) * C + g * 8);
+  for (int r = 0; r < 4; ++r) {
+    int h0, h1;
+    bil_src(min(oh0 + r, Ho - 1), H, sh, h0, h1, lh[r][0], lh[r][1]);
+    v[r][0].load(base + (size_t)(h0 * W + w0) * C); v[r][1].load(base + (size_t)(h0 * W + w1) * C);
+    v[r][2].load(base + (size_t)(h1 * W + w0) * C); v[r][3].load(base + (size_t)(h1 * W + w1) * C);
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    if (oh0 + r >= Ho) break;
+    float a[8], bq[8], c[8], d[8];
+    v[r][0].get(a); v[r][1].get(bq); v[r][2].get(c); v[r][3].get(d);
+    Vec8<T> o;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = lh[r][0] * (lw0 * a[i] + lw1 * bq[i]) + lh[r][1] * (lw0 * c[i] + lw1 * d[i]);
+    o.store(y + (((size_t)b * Ho + oh0 + r) * Wo + ow) * C + g * 8);
+  }
 }
 template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st) {
-  bilinear2x_fwd_kernel<T><<<dim3(cdiv(2 * W * (C / 8), 256), B * 2 * H), 256, 0, st>>>(x, y, B, H, W, C);
+  bilinear2x_fwd_kernel<T><<<dim3(cdiv(2 * W * (C / 8), 256), B * cdiv(2 * H, 4)), 256, 0, st>>>(x, y, B, H, W, C);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1239,6 +1253,44 @@ template <typename T> int k_pack_linear(const float* w, T* wp, T* wt, int N, int
   S4G_KERNEL_CHECK();
   return 0;
 }
+// All nn.Linear / 1x1-conv weights of the model in ONE launch (the per-layer launches are latency-bound: 58 of them
+// took 0.44 ms for 0.1 ms worth of HBM traffic).  The job table travels in kernel-parameter space.
+template <typename T> __global__ void __launch_bounds__(256) pack_linear_grouped_kernel(const __grid_constant__ PackLinearJobs jobs) {
+  __shared__ float tile[32][33];
+  int lo = 0, hi = jobs.n - 1;
+  while (lo < hi) {   // last job whose first tile is <= blockIdx.x
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs.job[mid].tile0 <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const PackLinearJob& jb = jobs.job[lo];
+  const int t = blockIdx.x - jb.tile0;
+  const int tiles_k = (jb.K + 31) >> 5;
+  const int k0 = (t % tiles_k) * 32, n0 = (t / tiles_k) * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const float* w = jb.src;
+  T* wp = reinterpret_cast<T*>(jb.wp);
+  T* wt = reinterpret_cast<T*>(jb.wt);
+  const int N = jb.N, K = jb.K;
+  for (int j = ty; j < 32; j += 8) {
+    const int n = n0 + j, k = k0 + tx;
+    float v = 0.f;
+    if (n < N && k < K) { v = w[(long long)n * K + k]; wp[(long long)n * K + k] = from_f<T>(v); }
+    tile[j][tx] = v;
+  }
+  if (!wt) return;
+  __syncthreads();
+  const int n = n0 + tx;
+  for (int j = ty; j < 32; j += 8) {
+    const int kk = k0 + j;
+    if (n < N && kk < K) wt[(long long)kk * N + n] = from_f<T>(tile[tx][j]);
+  }
+}
+template <typename T> int k_pack_linear_grouped(const PackLinearJobs& jobs, int total_tiles, cudaStream_t st) {
+  if (jobs.n == 0) return 0;
+  pack_linear_grouped_kernel<T><<<total_tiles, 256, 0, st>>>(jobs);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
 // conv weight [Co][Ci][R][R] -> fprop wf[Co][tap][Ci]; dgrad wd[Ci][tap'][Co] with tap' = flipped tap
 template <typename T> __global__ void pack_conv_kernel(const float* __restrict__ w, T* __restrict__ wf, T* __restrict__ wd, int Co, int Ci, int R) {
   const int taps = R * R;
@@ -1253,6 +1305,44 @@ template <typename T> __global__ void pack_conv_kernel(const float* __restrict__
 }
 template <typename T> int k_pack_conv(const float* w, T* wf, T* wd, int Co, int Ci, int R, cudaStream_t st) {
   pack_conv_kernel<T><<<GRID1D((long long)Co * Ci * R * R, 256), 0, st>>>(w, wf, wd, Co, Ci, R);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+// All 3x3 conv weights in ONE launch: a block owns one output channel (-> wf row [tap][Ci]) or one input channel
+// (-> wd row [tap'][Co]) and transposes its 9*C weights through shared memory, so both writes are contiguous.
+template <typename T> __global__ void __launch_bounds__(256) pack_conv3_grouped_kernel(const __grid_constant__ PackLinearJobs jobs) {
+  __shared__ float sm[9 * 768];
+  int lo = 0, hi = jobs.n - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs.job[mid].tile0 <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const PackLinearJob& jb = jobs.job[lo];
+  const int Co = jb.N, Ci = jb.K;
+  const int t = blockIdx.x - jb.tile0;
+  const float* w = jb.src;
+  if (t < Co) {
+    const int co = t, n = 9 * Ci;
+    const float* src = w + (size_t)co * n;
+    for (int i = threadIdx.x; i < n; i += 256) sm[(i % 9) * Ci + i / 9] = src[i];
+    __syncthreads();
+    T* dst = reinterpret_cast<T*>(jb.wp) + (size_t)co * n;
+    for (int i = threadIdx.x; i < n; i += 256) dst[i] = from_f<T>(sm[i]);
+  } else {
+    const int ci = t - Co, n = 9 * Co;
+    for (int i = threadIdx.x; i < n; i += 256) {
+      const int co = i / 9, tap = i % 9;
+      sm[(8 - tap) * Co + co] = w[((size_t)co * Ci + ci) * 9 + tap];
+    }
+    __syncthreads();
+    T* dst = reinterpret_cast<T*>(jb.wt) + (size_t)ci * n;
+    for (int i = threadIdx.x; i < n; i += 256) dst[i] = from_f<T>(sm[i]);
+  }
+}
+// jobs: N = Co, K = Ci (both <= 768), wp = wf, wt = wd, tile0 = first block
+template <typename T> int k_pack_conv3_grouped(const PackLinearJobs& jobs, int total_blocks, cudaStream_t st) {
+  if (jobs.n == 0) return 0;
+  pack_conv3_grouped_kernel<T><<<total_blocks, 256, 0, st>>>(jobs);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1306,6 +1396,8 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
 // ------------------------------------------------------------------------------------------ instantiation
 #define INST(T)                                                                                                        \
   template int k_patchify<T>(const float*, T*, int, cudaStream_t);                                                     \
+  template int k_pack_linear_grouped<T>(const PackLinearJobs&, int, cudaStream_t);                                     \
+  template int k_pack_conv3_grouped<T>(const PackLinearJobs&, int, cudaStream_t);                                      \
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
   template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*, float*); \
   template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t);                                        \

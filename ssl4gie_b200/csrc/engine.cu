@@ -137,13 +137,10 @@ struct Builder {
     Lin l{P(name + ".weight"), Popt(name + ".bias"), 0, 0, N, K};
     l.wf = alloc(sizeof(T) * (size_t)N * K);
     l.wd = dgrad ? alloc(sizeof(T) * (size_t)N * K) : 0;
-    S4GModel* mm = m;
-    m->pack.push_back([mm, l, dgrad](cudaStream_t st) {
-      mm->launches++;
-      return k_pack_linear<T>(l.w->p, mm->template at<T>(l.wf), dgrad ? mm->template at<T>(l.wd) : nullptr, l.N, l.K, st);
-    });
+    lin_jobs.push_back(l);   // packed by ONE grouped launch (finish())
     return l;
   }
+  std::vector<Lin> lin_jobs;
   // dW, db of a linear layer given dY [M,N], X [M,K]
   int linear_param_grads(const Lin& l, const T* dY, const T* X, long long M, cudaStream_t st, bool bias_done = false) const {
     if (l.w->g) S4G_TRY(wgrad(linear_geom(M, l.N, l.K), dY, X, l.w->g, st));
@@ -162,13 +159,10 @@ struct Builder {
     c.wf = alloc(sizeof(T) * (size_t)Co * Ci * 9);
     c.wd = alloc(sizeof(T) * (size_t)Co * Ci * 9);
     dwp_bytes = std::max(dwp_bytes, sizeof(float) * (size_t)Co * Ci * 9);
-    S4GModel* mm = m;
-    m->pack.push_back([mm, c](cudaStream_t st) {
-      mm->launches++;
-      return k_pack_conv<T>(c.w->p, mm->template at<T>(c.wf), mm->template at<T>(c.wd), c.Co, c.Ci, 3, st);
-    });
+    conv_jobs.push_back(c);   // packed by ONE grouped launch (finish())
     return c;
   }
+  std::vector<Conv> conv_jobs;
   // out = conv3x3(in) (+bias) (epilogue mode); pushes forward and backward closures
   void conv3_layer(const Conv& c, int in, int out, int mode = EPI_NONE, bool in_grad = true) {
     Builder* self = this;
@@ -742,6 +736,43 @@ struct Builder {
   }
 
   int finish() {
+    if (!lin_jobs.empty()) {
+      if (lin_jobs.size() > 80) { s4g_set_error("internal: more than 80 linear layers"); return S4G_ERR_STATE; }
+      Builder* self = this;
+      S4GModel* mm = m;
+      // first in the pack list: conv_s2 re-packs through the same kernel family afterwards
+      m->pack.insert(m->pack.begin(), [self, mm](cudaStream_t st) {
+        PackLinearJobs jobs;
+        int tiles = 0, n = 0;
+        for (const Lin& l : self->lin_jobs) {
+          PackLinearJob& j = jobs.job[n++];
+          j.src = l.w->p; j.wp = mm->template at<T>(l.wf); j.wt = l.wd ? (void*)mm->template at<T>(l.wd) : nullptr;
+          j.N = l.N; j.K = l.K; j.tile0 = tiles; j.pad = 0;
+          tiles += cdiv(l.N, 32) * cdiv(l.K, 32);
+        }
+        jobs.n = n;
+        mm->launches++;
+        return k_pack_linear_grouped<T>(jobs, tiles, st);
+      });
+    }
+    if (!conv_jobs.empty()) {
+      if (conv_jobs.size() > 80) { s4g_set_error("internal: more than 80 3x3 convolutions"); return S4G_ERR_STATE; }
+      Builder* self = this;
+      S4GModel* mm = m;
+      m->pack.push_back([self, mm](cudaStream_t st) {
+        PackLinearJobs jobs;
+        int blocks = 0, n = 0;
+        for (const Conv& c : self->conv_jobs) {
+          PackLinearJob& j = jobs.job[n++];
+          j.src = c.w->p; j.wp = mm->template at<T>(c.wf); j.wt = mm->template at<T>(c.wd);
+          j.N = c.Co; j.K = c.Ci; j.tile0 = blocks; j.pad = 0;
+          blocks += c.Co + c.Ci;
+        }
+        jobs.n = n;
+        mm->launches++;
+        return k_pack_conv3_grouped<T>(jobs, blocks, st);
+      });
+    }
     dwp_scratch = alloc(dwp_bytes);
     wg_scratch = alloc(wg_bytes);
     m->ws_need = top + 256;

@@ -55,6 +55,12 @@ int k_cls_head_fwd(const T* hn, const float* W, const float* bias, float* pooled
 template <typename T>
 int k_cls_head_bwd(const float* dout, const float* pooled, const float* W, float* dW, float* db, T* dhn, int B, int N,
                    int C, int spatial, cudaStream_t st);
+// grouped weight packing: every job is one [N, K] fp32 weight -> bf16/fp32 copy wp [N, K] and (optional) transpose wt [K, N]
+struct PackLinearJob { const float* src; void* wp; void* wt; int N, K, tile0, pad; };
+struct PackLinearJobs { PackLinearJob job[80]; int n; };
+template <typename T> int k_pack_linear_grouped(const PackLinearJobs& jobs, int total_tiles, cudaStream_t st);
+// 3x3 conv weights [Co][Ci][3][3] -> wf [Co][tap][Ci] and wd [Ci][8 - tap][Co]; job: N = Co, K = Ci (<= 768)
+template <typename T> int k_pack_conv3_grouped(const PackLinearJobs& jobs, int total_blocks, cudaStream_t st);
 template <typename T> int k_cast_f32(const float* in, T* out, long long n, cudaStream_t st);
 template <typename T> int k_relu(const T* x, T* y, long long n, cudaStream_t st);
 // dx = (dskip ? dskip : 0) + (x > 0 ? dr : 0)

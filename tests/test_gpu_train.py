@@ -81,11 +81,19 @@ def test_bf16_loss_curve_tracks_reference_over_200_steps(task):
     ref = _curve_oracle(task, sd, x, t)
     assert torch.isfinite(ours).all()
     assert ref[-1] < ref[0]  # the reference does train on this batch
-    # 1 % of the reference loss at every step; for the cross-entropy curve, which falls towards 0, relative to the
-    # larger of the current loss and 5 % of the initial one
+    # 1 % of the reference loss (for the cross-entropy curve, which falls towards 0: of the larger of the current loss and
+    # 5 % of the initial one).  Pointwise over the first 100 steps and on the 10-step moving average over all 200: late
+    # in this 4-image overfit the trajectory is chaotic -- two runs of the SAME bf16 path (fp32 atomics in the norm /
+    # bias gradient reductions) differ from each other by up to 1.1 % pointwise after step 150 (scripts/dev_curve.py),
+    # while agreeing to 1e-4 over the first 30 steps -- so single late steps are held to 3 %.
     scale = torch.maximum(ref.abs(), 0.05 * ref[0].abs()) if task == "cls" else ref.abs()
-    dev = ((ours - ref).abs() / scale).max().item()
-    assert dev < 1e-2, (dev, ours[::20].tolist(), ref[::20].tolist())
+    dev = (ours - ref).abs() / scale
+    assert dev[:100].max().item() < 1e-2, (dev[:100].max().item(), dev[:100].argmax().item())
+    assert dev.max().item() < 3e-2, (dev.max().item(), dev.argmax().item())
+    k = torch.ones(1, 1, 10) / 10
+    smooth = lambda c: torch.nn.functional.conv1d(c.view(1, 1, -1), k).flatten()  # noqa: E731
+    sdev = ((smooth(ours) - smooth(ref)).abs() / smooth(scale)).max().item()
+    assert sdev < 1e-2, (sdev, ours[::20].tolist(), ref[::20].tolist())
 
 
 def test_fp32_loss_curve_matches_reference_closely():
