@@ -178,12 +178,7 @@ def run_ours(args):
     loss_h = torch.empty((), dtype=torch.float32).pin_memory()
     launches = {"n": 0}
 
-    def step(from_host):
-        if from_host:
-            x = x_h.cuda(non_blocking=True)
-            t = t_h.cuda(non_blocking=True)
-        else:
-            x, t = x_d, t_d
+    def step(x, t, readback):
         h = engine.handle(B)
         out = model(x)
         launches["n"] += h.launches()
@@ -193,9 +188,17 @@ def run_ours(args):
         ddp.reduce()
         opt.step()
         launches["n"] += 1
-        if from_host:
+        if readback:
             loss_h.copy_(loss.detach(), non_blocking=True)
         return loss
+
+    def batches(n, from_host):
+        """Device-resident inputs, or (e2e) every step's images and targets copied from pinned host memory inside the
+        timed region: the public DevicePrefetcher overlaps the copy of step i+1 with the compute of step i."""
+        if not from_host:
+            return ((x_d, t_d) for _ in range(n))
+        from ssl4gie_b200.prefetch import DevicePrefetcher
+        return DevicePrefetcher((x_h, t_h) for _ in range(n))
 
     def timed(n, from_host):
         if world > 1:
@@ -203,8 +206,8 @@ def run_ours(args):
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(n):
-            loss = step(from_host)
+        for x, t in batches(n, from_host):
+            loss = step(x, t, from_host)
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -215,7 +218,7 @@ def run_ours(args):
         return ms.item(), loss
 
     for _ in range(max(3, args.warmup)):
-        step(False)
+        step(x_d, t_d, False)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -223,8 +226,8 @@ def run_ours(args):
     ms, loss = timed(args.steps, False)
     n_launch = launches["n"]
     clocks = sampler.stop() if rank == 0 else None
-    for _ in range(2):
-        step(True)
+    for x, t in batches(2, True):
+        step(x, t, True)
     ms_e2e, _ = timed(args.steps, True)
 
     roof = kernel_roofline(min(B, 64)) if rank == 0 else None

@@ -232,8 +232,63 @@ template <typename T> __global__ void __launch_bounds__(256) dgelu_mul_kernel(co
       }
   }
 }
-template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st) {
-  dgelu_mul_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(dy, u, out, n / 8);
+// out = dy * gelu'(u) on an [M, N] matrix, plus colsum[c] += sum_rows out[:, c] (the bias gradient of the Linear that
+// produced u): same block shape as colsum_kernel -- 32 column groups of 8 x 8 row lanes -- so the second pass over the
+// 77 MB tensor that a separate column-sum launch would make disappears.
+template <typename T>
+__global__ void __launch_bounds__(256, 3) dgelu_mul_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out,
+                                                               float* __restrict__ colsum, long long M, int N, long long rows_per_block) {
+  __shared__ float red[8][256 + 8];
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + cg * 8;
+  const long long r0 = (long long)blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float s[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = 0.f;
+  if (col < N) {
+    for (long long rb = r0 + rl; rb < r1; rb += 16) {
+      Vec8<T> a[2], b[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const long long r = min(rb + q * 8, r1 - 1);
+        a[q].load(dy + r * N + col); b[q].load(u + r * N + col);
+      }
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const long long r = rb + q * 8;
+        if (r < r1) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            a[q].v[k] *= sizeof(T) == 2 ? dgelu_fast(b[q].v[k]) : dgelu_f(b[q].v[k]);
+            s[k] += to_f(from_f<T>(a[q].v[k]));   // the sum of what is stored (what a separate pass would read)
+          }
+          a[q].store(out + r * N + col);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[rl][cg * 8 + i] = s[i];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+    atomicAdd(&colsum[c], t);
+  }
+}
+// colsum (optional, zeroed by the caller): [N] column sums of the result for an [n / N, N] matrix
+template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum, int N) {
+  if (colsum && N % 8 == 0 && n % N == 0) {
+    const long long M = n / N;
+    // 3 resident blocks per SM (launch bound above): one wave of 148 * 3 blocks
+    const int rblocks = (int)std::max<long long>(1, std::min<long long>(cdiv(M, 64), (148 * 3) / cdiv(N, 256)));
+    dgelu_mul_colsum_kernel<T><<<dim3(cdiv(N, 256), rblocks), 256, 0, st>>>(dy, u, out, colsum, M, N, cdiv(M, rblocks));
+  } else {
+    if (colsum) { s4g_set_error("dgelu_mul: bad column-sum shape"); return S4G_ERR_SHAPE; }
+    dgelu_mul_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(dy, u, out, n / 8);
+  }
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1400,7 +1455,7 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
   template int k_pack_conv3_grouped<T>(const PackLinearJobs&, int, cudaStream_t);                                      \
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
   template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*, float*); \
-  template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t);                                        \
+  template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t, float*, int);                            \
   template int k_gelu<T>(const T*, T*, long long, cudaStream_t);                                                       \
   template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t);                                       \
   template int k_tokens_to_nhwc<T>(const float*, T*, int, cudaStream_t);                                               \

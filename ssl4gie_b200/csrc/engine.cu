@@ -499,7 +499,9 @@ struct Builder {
         if (self->umma_path()) {
           S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), epi(dub, 3072), st));
           mm->launches++;
-          S4G_TRY(k_dgelu_mul<T>(dub, mm->template at<T>(b.u), dub, Tk * 3072, st));
+          // fc1's bias gradient (column sums of du) comes out of the same pass
+          if (b.fc1.b->g) S4G_CUDA(cudaMemsetAsync(b.fc1.b->g, 0, sizeof(float) * 3072, st));
+          S4G_TRY(k_dgelu_mul<T>(dub, mm->template at<T>(b.u), dub, Tk * 3072, st, b.fc1.b->g, 3072));
         } else {
           EpiParams e = epi(dub, 3072, nullptr, EPI_DGELU);
           e.aux = mm->template at<T>(b.u);
@@ -507,7 +509,7 @@ struct Builder {
         }
         S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st, fc2_bias_fused));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 3072), dub, mm->template at<T>(b.fc1.wd), epi(dhb, 768), st));
-        S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st));
+        S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st, self->umma_path()));
         S4G_CUDA(cudaMemsetAsync(b.n2w->g, 0, sizeof(float) * 768, st));
         S4G_CUDA(cudaMemsetAsync(b.n2b->g, 0, sizeof(float) * 768, st));
         S4G_CUDA(cudaMemsetAsync(b.proj.b->g, 0, sizeof(float) * 768, st));

@@ -43,7 +43,7 @@ int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float
                     const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st,
                     T* dx_cast = nullptr, float* dxsum = nullptr);
 // dx_cast: optional T copy of dx (the next GEMM's operand); dxsum: optional [C] += column sums of dx (must be zeroed)
-template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st);
+template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum = nullptr, int N = 0);
 template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st);
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st);  // out zeroed by caller
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast

@@ -595,6 +595,8 @@ struct WgradParams {
   int chunks_total;  // pixel chunks
   int chunks_per_split;
   float* part;       // split-K partials: [split][tap][tci][tco][block_n columns (ci)][128 rows (co)] fp32
+  float* dW;         // direct mode (splits == 1, linear layer): the epilogue writes dW [Cout][Cin] itself
+  int direct;
 };
 
 // CG = 2: a CTA pair owns a 256 (co) x block_n (ci) output tile (cta_group::2): each CTA stages its own 128 dY channels
@@ -720,11 +722,22 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
       mbar_wait(&ctl->tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + ((uint32_t)(q * 32) << 16);
+      const int co = (tco * CG + rank) * 128 + q * 32 + lane;
+      float* drow = p.dW + (size_t)co * p.Cin + tci * p.block_n;   // direct mode: this thread's row of dW
       for (int c0 = 0; c0 < p.block_n; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
-        if (tci * p.block_n + c0 < p.Cin) {
+        if (p.direct) {
+          // 128 contiguous bytes per thread: whole lines, no partials, no reduce launch
+          if (co < p.Cout) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              if (tci * p.block_n + c0 + i < p.Cin)
+                *reinterpret_cast<float4*>(drow + c0 + i) = make_float4(__uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                                                                         __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+          }
+        } else if (tci * p.block_n + c0 < p.Cin) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) part[(size_t)(c0 + i) * 128] = __uint_as_float(v[i]);
         }
@@ -995,16 +1008,17 @@ struct WgradPlan {
   TileGeom tg;
   int block_n, tiles_co, tiles_ci, out_tiles, chunks_total, splits, cps;   // tiles_co: 128*cg-row tiles
   int cg, stages;
+  bool direct;
   size_t scratch_bytes, smem_bytes;
 };
-// Split-K plan: enough (output tile x pixel range) work items to fill the SMs in whole waves, few enough that the
-// fp32 partials (written once, read once by the reduce kernel) stay cheap.
-WgradPlan plan_wgrad(const ConvGeom& g) {
+// One candidate: tile width block_n, best pixel split for it.  direct = the whole pixel range in one work item of a
+// linear layer: the epilogue writes dW itself, no partials and no reduce launch.
+WgradPlan plan_wgrad_bn(const ConvGeom& g, int block_n, double& cost) {
   WgradPlan w;
   const bool matrix = g.Hi == 1 && g.Wi == 1;
   w.tg = matrix ? matrix_tiles(g.Nimg, BLOCK_K) : make_tiles(g.Nimg, g.Hi, g.Wi, BLOCK_K);
   const int taps = g.R * g.S;
-  w.block_n = std::min(256, (g.Cin + 63) / 64 * 64);
+  w.block_n = block_n;
   // CTA pairs when a pair tile (256 co) is not mostly padding and each CTA's X share is whole 64-channel groups
   static const int forced_cg = getenv("S4G_WGRAD_CG") ? atoi(getenv("S4G_WGRAD_CG")) : 0;
   w.cg = forced_cg ? forced_cg : ((g.Cout > 128 && w.block_n % 128 == 0) ? 2 : 1);
@@ -1027,11 +1041,25 @@ WgradPlan plan_wgrad(const ConvGeom& g) {
     if (se != s) continue;
     const long long items = (long long)w.out_tiles * se;
     const long long rounds = (items + groups - 1) / groups;
-    const double t = rounds * (cps * t_chunk + 2.0) + items * w.cg * tile_bytes * 2 / 3.0e6;
+    const bool direct = se == 1 && taps == 1;
+    // partials are written once and read once by the reduce kernel, whose launch costs ~8 us on top
+    const double t = rounds * (cps * t_chunk + 2.0) + (direct ? 0.0 : items * w.cg * tile_bytes * 2 / 3.0e6 + 8.0);
     if (t < best) { best = t; w.splits = se; w.cps = cps; }
   }
-  w.scratch_bytes = (size_t)w.out_tiles * w.cg * w.splits * 128 * w.block_n * sizeof(float);
+  w.direct = w.splits == 1 && taps == 1;
+  w.scratch_bytes = w.direct ? 0 : (size_t)w.out_tiles * w.cg * w.splits * 128 * w.block_n * sizeof(float);
+  cost = best;
   return w;
+}
+// Split-K plan: enough (output tile x pixel range) work items to fill the SMs in whole waves, few enough that the
+// fp32 partials stay cheap.  Tiles are as wide as Cin allows (<= 256 columns): measured, 128-column tiles run the
+// channel-major (MN-major) operands at less than half the rate per FLOP (fc1 weight gradient as 72 unsplit 256 x 128
+// pair tiles: 83 us, against 48 + 9 us for 2-way split 256 x 256 tiles plus the reduce).  S4G_WGRAD_BN overrides.
+WgradPlan plan_wgrad(const ConvGeom& g) {
+  const int bn0 = std::min(256, (g.Cin + 63) / 64 * 64);
+  static const int forced_bn = getenv("S4G_WGRAD_BN") ? atoi(getenv("S4G_WGRAD_BN")) : 0;
+  double cost;
+  return plan_wgrad_bn(g, forced_bn && forced_bn <= bn0 ? forced_bn : bn0, cost);
 }
 }  // namespace
 
@@ -1047,7 +1075,7 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   if (g.Cin % 8 || g.ldx % 8 || g.Cout % 8 || g.ldy % 8) { s4g_set_error("umma_conv_wgrad: channel counts must be multiples of 8"); return S4G_ERR_SHAPE; }
   const bool matrix = g.Hi == 1 && g.Wi == 1;
   const WgradPlan w = plan_wgrad(g);
-  if (!scratch || scratch_bytes < w.scratch_bytes) { s4g_set_error("umma_conv_wgrad: split-K scratch too small (see s4g_wgrad_scratch_bytes)"); return S4G_ERR_WORKSPACE; }
+  if (w.scratch_bytes && (!scratch || scratch_bytes < w.scratch_bytes)) { s4g_set_error("umma_conv_wgrad: split-K scratch too small (see s4g_wgrad_scratch_bytes)"); return S4G_ERR_WORKSPACE; }
   WgradParams p{};
   p.tg = w.tg;
   p.taps = g.R * g.S; p.S = g.S; p.pad = g.pad;
@@ -1060,6 +1088,9 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   p.stages = w.stages;
   p.chunks_per_split = w.cps;
   p.part = scratch;
+  p.dW = dW;
+  p.direct = w.direct;
+  if (w.direct && (reinterpret_cast<uintptr_t>(dW) & 15)) { s4g_set_error("umma_conv_wgrad: dW must be 16 B aligned"); return S4G_ERR_ALIGN; }
   CUtensorMap tmY, tmX;
   S4G_TRY(make_act_map(&tmY, dY, g, g.Cout, g.ldy, p.tg, matrix, g.Hi, g.Wi));
   S4G_TRY(make_act_map(&tmX, X, g, g.Cin, g.ldx, p.tg, matrix, g.Hi, g.Wi));
@@ -1079,6 +1110,7 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
     umma_wgrad_kernel<1><<<grid, NUM_THREADS, w.smem_bytes, st>>>(tmY, tmX, p);
   }
   S4G_KERNEL_CHECK();
+  if (w.direct) return 0;
   WgradReduceParams r{};
   r.part = scratch; r.dW = dW;
   r.Cout = g.Cout; r.Cin = g.Cin; r.taps = p.taps; r.tiles_co = p.tiles_co * w.cg; r.tiles_ci = p.tiles_ci; r.block_n = p.block_n;

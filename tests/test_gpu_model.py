@@ -236,3 +236,15 @@ def test_wrong_input_size_and_cpu_input_raise():
         m(torch.randn(1, 3, 192, 192).cuda())
     with pytest.raises(RuntimeError):
         m(torch.randn(1, 3, 224, 224))
+
+
+def test_device_prefetcher_yields_the_batches_in_order():
+    from ssl4gie_b200.prefetch import DevicePrefetcher
+    g = torch.Generator().manual_seed(3)
+    host = [(torch.randn(4, 3, 8, 8, generator=g).pin_memory(), torch.randint(0, 5, (4,), generator=g).pin_memory()) for _ in range(5)]
+    got = list(DevicePrefetcher(iter(host)))
+    assert len(got) == 5
+    for (x, t), (xh, th) in zip(got, host):
+        assert x.is_cuda and t.is_cuda
+        torch.cuda.current_stream().synchronize()
+        assert torch.equal(x.cpu(), xh) and torch.equal(t.cpu(), th)
