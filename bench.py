@@ -50,14 +50,26 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def stop(self):
+        """Call after ALL timed regions: nvidia-smi attaching to / detaching from the driver can stall a running
+        process for tens of ms, so the sampler starts before warm-up and ends after the last timed step."""
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:  # noqa: BLE001
+                pass
+
+    def window(self, t0, t1):
+        """Clocks and throttle reasons of the samples taken in [t0, t1] (host time.time())."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
         sm, mx, reasons = [], None, set()
-        for ln in self.lines:
+        for ts, ln in list(self.lines):
+            if ts < t0 or ts > t1 + 0.2:
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -205,30 +217,51 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        marks = [e0]
+        w0 = time.time()
         e0.record()
         for x, t in batches(n, from_host):
             loss = step(x, t, from_host)
+            marks.append(torch.cuda.Event(enable_timing=True))
+            marks[-1].record()
         e1.record()
         torch.cuda.synchronize()
+        w1 = time.time()
         if world > 1:
             dist.barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return ms.item(), loss
+        per = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(n))  # rank 0's steps: shows a one-off stall
+        return ms.item(), loss, {"median": per[n // 2], "max": per[-1]}, (w0, w1)
 
-    for _ in range(max(3, args.warmup)):
-        step(x_d, t_d, False)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+        t_wait = time.time()
+        while sampler.proc and not sampler.lines and time.time() - t_wait < 5.0:  # attached and polling before any timing
+            time.sleep(0.05)
+    for _ in range(max(3, args.warmup)):
+        step(x_d, t_d, False)
     launches["n"] = 0
-    ms, loss = timed(args.steps, False)
+    ms, loss, per_step, win = timed(args.steps, False)
     n_launch = launches["n"]
-    clocks = sampler.stop() if rank == 0 else None
-    for x, t in batches(2, True):
+    for x, t in batches(4, True):  # untimed: the caching allocator reaches its steady set of staging buffers
         step(x, t, True)
-    ms_e2e, _ = timed(args.steps, True)
+    ms_e2e, _, per_step_e2e, win_e2e = timed(args.steps, True)
+    clocks = e2e_clocks = None
+    if rank == 0:
+        sampler.stop()
+        clocks, e2e_clocks = sampler.window(*win), sampler.window(*win_e2e)
+    # pinned host -> device bandwidth of this box (explains an e2e far below `value`: the copies are overlapped, not free)
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(4):
+        x_d.copy_(x_h, non_blocking=True)
+    c1.record()
+    torch.cuda.synchronize()
+    h2d_gbps = 4 * x_h.numel() * x_h.element_size() / (c0.elapsed_time(c1) * 1e-3) / 1e9
 
     roof = kernel_roofline(min(B, 64)) if rank == 0 else None
     cpu = None
@@ -251,7 +284,9 @@ def run_ours(args):
                 "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
                 "e2e": {"value": world * B * args.steps / (ms_e2e / 1e3), "unit": "img/s",
                         "h2d_bytes_per_step": x_h.numel() * x_h.element_size() + t_h.numel() * t_h.element_size(),
-                        "d2h_bytes_per_step": 4},
+                        "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps, "step_ms": per_step_e2e,
+                        "h2d_pinned_gbps": h2d_gbps, "clocks": e2e_clocks},
+                "step_ms": per_step,
                 "gpu_launches": n_launch}
         real_stdout.write(json.dumps(line) + "\n")
         real_stdout.flush()
@@ -287,7 +322,11 @@ def kernel_roofline(B):
     burst, sustained, hbm, src = peaks()
     ach = flops / (ms * 1e-3) / 1e12
     return {"kernel": "umma_fprop_kernel (conv3x3 256->256 @112x112, B=%d)" % B, "bound": "tensor", "achieved": ach, "peak": burst,
-            "unit": "TFLOP/s", "frac": ach / burst, "traffic": None, "ms_per_launch": ms, "flops_per_launch": flops,
+            "unit": "TFLOP/s", "frac": ach / burst,
+            # dram__bytes_read.sum + dram__bytes_write.sum of this launch from the ncu --set full capture summarised in
+            # profiles/r01_d_ncu_full_fprop_head112.txt (782.3 MB at B=64; algorithmic 823.2 MB), bytes per launch
+            "traffic": 782.3e6 * B / 64, "traffic_source": "profiles/r01_d_ncu_full_fprop_head112.txt",
+            "ms_per_launch": ms, "flops_per_launch": flops,
             "peak_source": src + " burst (kernel timed alone)"}
 
 

@@ -88,6 +88,24 @@ int s4g_model_backward(S4GModel* m, const float* dout, void* stream);
  * on the host while enqueueing; must enqueue an in-place sum-all-reduce of `count` doubles on `stream`. */
 typedef int (*s4g_allreduce_fn)(void* user, void* device_doubles, int count, void* stream);
 int s4g_model_set_allreduce(S4GModel* m, s4g_allreduce_fn fn, void* user);
+/* The same cross-rank sum without the host callback: a one-CTA kernel that exchanges the statistic vector through
+ * NVLink peer memory (P2P stores into every rank's mailbox + system-scope flags; csrc/peer.cu).  Replaces the NCCL
+ * all_gather / all_reduce pair inside torch.nn.SyncBatchNorm (train_segmentation.py:199).  Every rank allocates one
+ * mailbox per model handle (s4g_peer_alloc: zero-filled device memory + a 64-byte cudaIpc handle to send to the peers
+ * by any host channel), opens the peers' (s4g_peer_open), and passes the `world` device pointers in rank order
+ * (mailboxes[rank] = its own).  All ranks must have set the pointers (host barrier) before the first forward. */
+#define S4G_PEER_MAX_WORLD 8
+#define S4G_PEER_HANDLE_BYTES 64
+size_t s4g_peer_mailbox_bytes(void);
+int s4g_peer_alloc(size_t bytes, void** dptr, unsigned char handle[S4G_PEER_HANDLE_BYTES]);
+int s4g_peer_open(const unsigned char handle[S4G_PEER_HANDLE_BYTES], void** dptr);
+int s4g_peer_close(void* dptr);
+int s4g_peer_free(void* dptr);
+int s4g_model_set_peer_exchange(S4GModel* m, void* const* mailboxes, int rank, int world);
+/* Stand-alone exchange (tests): in-place sum over ranks of `count` <= 512 doubles; `seq` counts the exchanges made
+ * through these mailboxes so far (0, 1, 2, ... identically on every rank). */
+int s4g_peer_sum_f64(double* data, int count, void* const* mailboxes, int rank, int world, unsigned long long seq,
+                     void* stream);
 /* Gradient-bucket boundaries for overlapping the data-parallel all-reduce with backward (DDP reducer,
  * train_segmentation.py:203).  The library records events[i] (cudaEvent_t) on `stream` during backward once every
  * parameter gradient of bucket i is final: bucket 0 = DPT decoder, buckets 1..n-1 = encoder blocks from the last

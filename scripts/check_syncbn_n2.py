@@ -1,0 +1,112 @@
+"""torchrun --nproc-per-node 2 scripts/check_syncbn_n2.py
+SyncBatchNorm statistic exchange over NVLink peer memory (csrc/peer.cu) on 2 GPUs:
+  1. s4g_peer_sum_f64 against dist.all_reduce over 200 back-to-back exchanges (both parities, flag reuse);
+  2. the seg model with SyncBN, half a batch per rank, peer exchange vs the NCCL callback (S4G_SYNCBN=nccl);
+  3. the same against ONE plain-BatchNorm model over the concatenated batch (what SyncBN is defined to equal):
+     outputs row for row, parameter gradients = sum over ranks."""
+import ctypes
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def rel(a, b):
+    return ((a.double() - b.double()).abs().max() / (b.double().abs().max() + 1e-30)).item()
+
+
+def main():
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    from ssl4gie_b200 import _C, utils
+    from ssl4gie_b200.peer import PeerMailboxes
+    lib = _C.lib()
+    _C.check(lib.s4g_init(local))
+
+    # 1. raw exchange
+    boxes = PeerMailboxes()
+    assert boxes.ok, getattr(boxes, "error", "")
+    g = torch.Generator(device="cuda").manual_seed(100 + rank)
+    worst = 0.0
+    for seq in range(200):
+        n = 512 if seq % 3 else 256
+        v = torch.randn(n, dtype=torch.float64, device="cuda", generator=g)
+        ref = v.clone()
+        dist.all_reduce(ref)
+        _C.check(lib.s4g_peer_sum_f64(_C.ptr(v), n, boxes.ptrs, rank, world, seq, _C.stream_ptr()))
+        worst = max(worst, (v - ref).abs().max().item())
+        # bit-identical on every rank (fixed summation order)
+        other = [torch.empty_like(v) for _ in range(world)]
+        dist.all_gather(other, v)
+        assert all(torch.equal(o, other[0]) for o in other), seq
+    torch.cuda.synchronize()
+    assert worst < 1e-12, worst
+    boxes.close()
+    if rank == 0:
+        print("raw exchange ok: 200 exchanges, max |peer - nccl| = %.3g, bit-identical across ranks" % worst, flush=True)
+
+    # 2./3. model
+    B = 2
+    gcpu = torch.Generator().manual_seed(7)
+    x_all = torch.randn(world * B, 3, 224, 224, generator=gcpu)
+    w_all = torch.randn(world * B, 1, 224, 224, generator=gcpu)
+    x, w = x_all[rank * B:(rank + 1) * B].cuda(), w_all[rank * B:(rank + 1) * B].cuda()
+
+    def build(sync):
+        torch.manual_seed(42)
+        m = utils.get_ImageNet_or_random_ViT(False, 1, False, "seg", False, False)
+        m.decoder.output_conv[3].p = 0.0
+        m.precision = "fp32"
+        m = m.cuda()
+        if sync:
+            m = torch.nn.SyncBatchNorm.convert_sync_batchnorm(m)
+        return m.train()
+
+    def run(m, xx, ww):
+        out = m(xx)
+        (out * ww).sum().backward()
+        return out.detach(), {n: p.grad.clone() for n, p in m.named_parameters() if p.grad is not None}
+
+    os.environ["S4G_SYNCBN"] = "peer"
+    m_peer = build(True)
+    o_peer, g_peer = run(m_peer, x, w)
+    from ssl4gie_b200.engine import Engine
+    assert Engine.of(m_peer).handle(B).peer is not None, "peer exchange not installed"
+    os.environ["S4G_SYNCBN"] = "nccl"
+    m_nccl = build(True)
+    o_nccl, g_nccl = run(m_nccl, x, w)
+    assert Engine.of(m_nccl).handle(B).peer is None
+    e = rel(o_peer, o_nccl)
+    eg = max(rel(g_peer[n], g_nccl[n]) for n in g_peer)
+    rm = max(rel(a, b) for (_, a), (_, b) in zip(m_peer.named_buffers(), m_nccl.named_buffers()) if a.is_floating_point())
+    if rank == 0:
+        print("peer vs nccl: out %.3g grads %.3g running stats %.3g" % (e, eg, rm), flush=True)
+    assert e < 1e-5 and eg < 1e-4 and rm < 1e-6, (e, eg, rm)
+
+    for n in g_peer:
+        dist.all_reduce(g_peer[n])
+    if rank == 0:
+        m_one = build(False)
+        o_one, g_one = run(m_one, x_all.cuda(), w_all.cuda())
+        e = rel(o_peer, o_one[:B])
+        eg, worst_n = max((rel(g_peer[n], g_one[n]), n) for n in g_one)
+        cos = min(torch.nn.functional.cosine_similarity(g_peer[n].double().flatten(), g_one[n].double().flatten(), dim=0).item() for n in g_one)
+        print("SyncBN over 2 ranks vs one BatchNorm model over the whole batch: out %.3g grads %.3g (%s) min cosine %.7f" % (e, eg, worst_n, cos), flush=True)
+        # running statistics (global count, unbiased variance) and affine gradients follow torch's SyncBatchNorm + DDP
+        rm = max(rel(a, b) for (_, a), (_, b) in zip(m_peer.named_buffers(), m_one.named_buffers()) if a.is_floating_point())
+        print("running stats vs one-model BatchNorm: %.3g" % rm, flush=True)
+        # gradients: fp32 sums over 4 x 112 x 112 rows in a different order (2 + 2 images vs 4): 1e-2 of the largest entry,
+        # direction to 1e-6 (a wrong SyncBN scale shows as a relative error of 1.0 on the BN affine gradients)
+        assert e < 1e-4 and eg < 1e-2 and cos > 0.999999 and rm < 1e-5, (e, eg, worst_n, cos, rm)
+        print("CHECK_SYNCBN_N2 OK", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

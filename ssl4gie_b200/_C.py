@@ -34,6 +34,13 @@ SIGNATURES = {
     "s4g_model_forward": (_i, [_vp, _vp, _vp, _i, _u64, _vp, _vp]),
     "s4g_model_backward": (_i, [_vp, _vp, _vp]),
     "s4g_model_set_allreduce": (_i, [_vp, ALLREDUCE_FN, _vp]),
+    "s4g_peer_mailbox_bytes": (_sz, []),
+    "s4g_peer_alloc": (_i, [_sz, ctypes.POINTER(_vp), ctypes.c_char_p]),
+    "s4g_peer_open": (_i, [ctypes.c_char_p, ctypes.POINTER(_vp)]),
+    "s4g_peer_close": (_i, [_vp]),
+    "s4g_peer_free": (_i, [_vp]),
+    "s4g_model_set_peer_exchange": (_i, [_vp, ctypes.POINTER(_vp), _i, _i]),
+    "s4g_peer_sum_f64": (_i, [_vp, _i, ctypes.POINTER(_vp), _i, _i, _u64, _vp]),
     "s4g_model_set_bucket_events": (_i, [_vp, ctypes.POINTER(_vp), _i]),
     "s4g_model_bucket_params": (ctypes.c_char_p, [_vp, _i, _i]),
     "s4g_model_last_launches": (_i, [_vp]),

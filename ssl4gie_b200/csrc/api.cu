@@ -1,4 +1,5 @@
 // C-ABI plumbing: error state, device check, operator-level entry points declared in include/ssl4gie_b200.h.
+#include <cstring>
 #include "kernels.h"
 
 static thread_local std::string g_err;
@@ -140,6 +141,32 @@ int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits,
 int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
                    float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
   return k_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, grad_scale, ST(stream));
+}
+
+size_t s4g_peer_mailbox_bytes(void) { return k_peer_mailbox_bytes(); }
+int s4g_peer_alloc(size_t bytes, void** dptr, unsigned char handle[S4G_PEER_HANDLE_BYTES]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == S4G_PEER_HANDLE_BYTES, "cudaIpcMemHandle_t size");
+  if (!dptr || !handle) { s4g_set_error("peer_alloc: null argument"); return S4G_ERR_STATE; }
+  S4G_CUDA(cudaMalloc(dptr, bytes));
+  S4G_CUDA(cudaMemset(*dptr, 0, bytes));
+  S4G_CUDA(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t h;
+  S4G_CUDA(cudaIpcGetMemHandle(&h, *dptr));
+  memcpy(handle, &h, sizeof(h));
+  return 0;
+}
+int s4g_peer_open(const unsigned char handle[S4G_PEER_HANDLE_BYTES], void** dptr) {
+  if (!dptr || !handle) { s4g_set_error("peer_open: null argument"); return S4G_ERR_STATE; }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  S4G_CUDA(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int s4g_peer_close(void* dptr) { S4G_CUDA(cudaIpcCloseMemHandle(dptr)); return 0; }
+int s4g_peer_free(void* dptr) { S4G_CUDA(cudaFree(dptr)); return 0; }
+int s4g_peer_sum_f64(double* data, int count, void* const* mailboxes, int rank, int world, unsigned long long seq,
+                     void* stream) {
+  return k_peer_sum_f64(data, count, mailboxes, rank, world, seq, ST(stream));
 }
 
 }  // extern "C"

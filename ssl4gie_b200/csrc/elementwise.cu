@@ -955,8 +955,12 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const T* __restric
                                                               long long M, int C) {
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
-  if (blockIdx.x == 0 && dgamma)
-    for (int c = threadIdx.x; c < C; c += blockDim.x) { dbeta[c] = (float)sums[c]; dgamma[c] = (float)sums[C + c]; }
+  // SyncBatchNorm (count = M * world): torch keeps grad_weight / grad_bias LOCAL and DDP averages them over ranks; the
+  // sums here are already global, so hand the gradient all-reduce (sum, then 1/world) the global sum / world.
+  if (blockIdx.x == 0 && dgamma) {
+    const double gs = (double)M / count;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) { dbeta[c] = (float)(sums[c] * gs); dgamma[c] = (float)(sums[C + c] * gs); }
+  }
   const float inv = (float)(1.0 / count);
   float sc[8], sh[8], c0[8], c1[8];
 #pragma unroll
@@ -1166,7 +1170,10 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_apply_kernel(const float* 
                                                                    double count, T* __restrict__ dx, float* dgamma, float* dbeta,
                                                                    long long M) {
   const int lane = threadIdx.x & 31;
-  if (blockIdx.x == 0) { dbeta[threadIdx.x] = (float)sums[threadIdx.x]; dgamma[threadIdx.x] = (float)sums[256 + threadIdx.x]; }
+  if (blockIdx.x == 0) {  // global sums / world under SyncBatchNorm, see bn_bwd_apply_kernel
+    const double gs = (double)M / count;
+    dbeta[threadIdx.x] = (float)(sums[threadIdx.x] * gs); dgamma[threadIdx.x] = (float)(sums[256 + threadIdx.x] * gs);
+  }
   const float inv = (float)(1.0 / count);
   // dx = sc*dy - (c0 + x*c1), see bn_bwd_apply_kernel; scw = sc * w folds the 1x1 conv weight into the dy term
   float sc[8], sh[8], scw[8], c0[8], c1[8];

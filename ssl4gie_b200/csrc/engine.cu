@@ -48,6 +48,15 @@ struct S4GModel {
   size_t grad_arena_bytes = 0;
   s4g_allreduce_fn allreduce = nullptr;
   void* allreduce_user = nullptr;
+  void* peer_boxes[S4G_PEER_MAX_WORLD] = {};  // SyncBN exchange through NVLink peer memory (peer.cu) when peer_world > 1
+  int peer_rank = 0, peer_world = 0;
+  unsigned long long peer_seq = 0;
+  // in-place sum over ranks of `count` doubles: the peer-memory kernel when mailboxes are set, else the host callback
+  int exchange(double* v, int count, cudaStream_t st) {
+    if (peer_world > 1) { launches++; return k_peer_sum_f64(v, count, peer_boxes, peer_rank, peer_world, peer_seq++, st); }
+    if (!allreduce) { s4g_set_error("SyncBatchNorm needs s4g_model_set_peer_exchange or s4g_model_set_allreduce"); return S4G_ERR_STATE; }
+    return allreduce(allreduce_user, v, count, st);
+  }
   std::vector<cudaEvent_t> events;
   std::string bucket_str;
   int launches = 0;
@@ -241,10 +250,7 @@ struct Builder {
     S4G_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 512, st));
     m->launches += 2;
     S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st));
-    if (m->d.world_size > 1) {
-      if (!m->allreduce) { s4g_set_error("SyncBatchNorm needs s4g_model_set_allreduce"); return S4G_ERR_STATE; }
-      S4G_TRY(m->allreduce(m->allreduce_user, stats, 512, st));
-    }
+    if (m->d.world_size > 1) S4G_TRY(m->exchange(stats, 512, st));
     return k_bn_finalize(stats, (double)M * m->d.world_size, mean, rstd, n.rm->p, n.rv->p,
                          reinterpret_cast<long long*>(n.nbt->p), 0.1f, 1e-5f, 256, st);
   }
@@ -255,7 +261,7 @@ struct Builder {
     S4G_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 512, st));
     m->launches += 2;
     S4G_TRY(k_bn_bwd_reduce<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, relu, M, 256, st));
-    if (m->d.world_size > 1) S4G_TRY(m->allreduce(m->allreduce_user, sums, 512, st));
+    if (m->d.world_size > 1) S4G_TRY(m->exchange(sums, 512, st));
     return k_bn_bwd_apply<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, (double)M * m->d.world_size, dx, n.w->g, n.b->g,
                              relu, M, 256, st);
   }
@@ -597,7 +603,7 @@ struct Builder {
         S4G_CUDA(cudaMemsetAsync(b4->g, 0, sizeof(float), st));
         S4G_TRY(k_seghead_bwd_reduce<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
                                         mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, w4->g, b4->g, M1, 256, st));
-        if (mm->d.world_size > 1) S4G_TRY(mm->allreduce(mm->allreduce_user, sums, 512, st));
+        if (mm->d.world_size > 1) S4G_TRY(mm->exchange(sums, 512, st));
         return k_seghead_bwd_apply<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
                                       mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, (double)M1 * mm->d.world_size, self->G(c),
                                       n.w->g, n.b->g, M1, 256, st);
@@ -859,6 +865,14 @@ int s4g_model_set_workspace(S4GModel* m, void* workspace, size_t bytes) {
   if (reinterpret_cast<uintptr_t>(workspace) & 255) { s4g_set_error("model_set_workspace: need 256 B alignment"); return S4G_ERR_ALIGN; }
   m->ws = reinterpret_cast<char*>(workspace);
   m->ws_bytes = bytes;
+  return 0;
+}
+int s4g_model_set_peer_exchange(S4GModel* m, void* const* mailboxes, int rank, int world) {
+  if (!m || !mailboxes || world < 1 || world > S4G_PEER_MAX_WORLD || rank < 0 || rank >= world) {
+    s4g_set_error("model_set_peer_exchange: bad argument (world <= 8)"); return S4G_ERR_STATE;
+  }
+  for (int r = 0; r < world; ++r) m->peer_boxes[r] = mailboxes[r];
+  m->peer_rank = rank; m->peer_world = world; m->peer_seq = 0;
   return 0;
 }
 int s4g_model_set_allreduce(S4GModel* m, s4g_allreduce_fn fn, void* user) {

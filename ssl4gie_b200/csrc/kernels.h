@@ -153,3 +153,7 @@ size_t ssi_scratch_floats(int B);
 // ---- optimizer: optim.cu
 int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps, float wd,
             int step, float grad_scale, cudaStream_t st);
+
+// peer.cu: SyncBN statistic exchange over NVLink peer memory
+size_t k_peer_mailbox_bytes();
+int k_peer_sum_f64(double* data, int count, void* const* boxes, int rank, int world, unsigned long long seq, cudaStream_t st);

@@ -7,6 +7,8 @@ cls_token / pos_embed).  Each bucket is a contiguous slice of the flat fp32 grad
 a side stream that waits on the bucket's event, so the exchange overlaps the rest of backward.  The unused
 parameters (norm.*, decoder.refinenet4.resConfUnit1.*) are known statically and are simply not in the arena —
 no find_unused_parameters graph walk."""
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -47,6 +49,7 @@ class GradientAllReduce:
         self.group = process_group
         self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.n_buckets = n_buckets
+        self.overlap = os.environ.get("S4G_DDP_OVERLAP", "1") != "0"
         self.comm_stream = None
         self.slices = None
         self.events = None
@@ -78,6 +81,9 @@ class GradientAllReduce:
             return
         flat = self.engine.flat_grads
         cur = torch.cuda.current_stream()
+        if not self.overlap:  # one all-reduce of the whole arena after backward (S4G_DDP_OVERLAP=0)
+            dist.all_reduce(flat, group=self.group)
+            return
         with torch.cuda.stream(self.comm_stream):
             allreduce_buckets(flat, self.slices, self.group, self.events, self.comm_stream)
         cur.wait_stream(self.comm_stream)

@@ -194,6 +194,16 @@ class _Handle:
 
     def _install_allreduce(self):
         import torch.distributed as dist
+        from .peer import PeerMailboxes, use_peer_exchange
+        self.peer = None
+        if use_peer_exchange() and dist.get_world_size() <= 8 and dist.get_backend() == "nccl":
+            # one-CTA NVLink exchange kernel instead of an NCCL collective per statistic vector (csrc/peer.cu)
+            boxes = PeerMailboxes()
+            if boxes.ok:
+                _C.check(_C.lib().s4g_model_set_peer_exchange(self.ptr, boxes.ptrs, boxes.rank, boxes.world))
+                self.peer = boxes
+                return
+            print("ssl4gie_b200: peer mailboxes unavailable (%s); SyncBN statistics go through NCCL" % getattr(boxes, "error", "a peer failed"))
         ws_f64 = self.workspace[self.ws_off:self.ws_off + (self.workspace.numel() - 256) // 8 * 8].view(torch.float64)
         base = self.workspace.data_ptr() + self.ws_off
 
@@ -210,6 +220,9 @@ class _Handle:
         _C.check(_C.lib().s4g_model_set_allreduce(self.ptr, self._cb, None))
 
     def destroy(self):
+        if getattr(self, "peer", None) is not None:
+            self.peer.close()
+            self.peer = None
         if self.ptr:
             _C.lib().s4g_model_destroy(self.ptr)
             self.ptr = None
