@@ -9,6 +9,7 @@ One JSON line on stdout (rank 0).  Timing: CUDA events on the launching stream, 
 sides, max over ranks.
 """
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -215,24 +216,41 @@ def run_ours(args):
     def timed(n, from_host):
         if world > 1:
             dist.barrier()
+        gc.collect()
+        gc.disable()  # a generation-2 collection is a 50-100 ms host pause; right after the synchronize nothing hides it
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         marks = [e0]
         w0 = time.time()
         e0.record()
-        for x, t in batches(n, from_host):
+        host = [time.perf_counter()]
+        it = iter(batches(n, from_host))
+        while True:
+            try:
+                x, t = next(it)
+            except StopIteration:
+                break
+            host.append(time.perf_counter())
             loss = step(x, t, from_host)
+            host.append(time.perf_counter())
             marks.append(torch.cuda.Event(enable_timing=True))
             marks[-1].record()
         e1.record()
         torch.cuda.synchronize()
+        gc.enable()
         w1 = time.time()
         if world > 1:
             dist.barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        per = sorted(marks[i].elapsed_time(marks[i + 1]) for i in range(n))  # rank 0's steps: shows a one-off stall
+        raw = [marks[i].elapsed_time(marks[i + 1]) for i in range(n)]
+        if os.environ.get("S4G_BENCH_TRACE") and rank == 0:
+            k = max(range(n), key=lambda i: raw[i])
+            sys.stderr.write("trace from_host=%s slowest step %d: gpu %.2f ms; host next() %.2f ms, enqueue %.2f ms; gpu ms/step: %s\n" % (
+                from_host, k, raw[k], 1e3 * (host[2 * k + 1] - host[2 * k]), 1e3 * (host[2 * k + 2] - host[2 * k + 1]),
+                " ".join("%.1f" % v for v in raw)))
+        per = sorted(raw)  # rank 0's steps: shows a one-off stall
         return ms.item(), loss, {"median": per[n // 2], "max": per[-1]}, (w0, w1)
 
     sampler = ClockSampler(local)
@@ -333,8 +351,8 @@ def kernel_roofline(B):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--task", default="seg", choices=["seg", "depth", "cls"])
     ap.add_argument("--batch", type=int, default=0, help="images per GPU (default: 64 seg/depth, 128 cls as BASELINE.json)")

@@ -10,5 +10,6 @@ from .dpt_decoder import DPT_decoder  # noqa: F401
 from .losses import CrossEntropyLoss, ScaleAndShiftInvariantLoss, SoftDiceLoss  # noqa: F401
 from .models import ViT_from_MAE, ViT_from_MoCoV3, VisionTransformer_from_Any  # noqa: F401
 from .optim import FusedAdamW  # noqa: F401
+from .prefetch import DevicePrefetcher  # noqa: F401
 
 __version__ = "0.1.0"

@@ -18,7 +18,9 @@ class FusedAdamW(torch.optim.Optimizer):
         self.engine = Engine.of(core)
         self.engine.materialize()
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
-        super().__init__([p for p in core.parameters() if p.requires_grad], defaults)
+        # every parameter, in model.parameters() order, as the reference's torch.optim.AdamW(model.parameters()) holds
+        # them: the indices in state_dict() are then the reference checkpoint's indices
+        super().__init__(list(core.parameters()), defaults)
         n = self.engine.n_active
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=self.engine.flat_params.device)
         self.exp_avg_sq = torch.zeros_like(self.exp_avg)
@@ -38,11 +40,61 @@ class FusedAdamW(torch.optim.Optimizer):
         # gradients are overwritten by every backward; nothing to clear (keeps the flat views alive)
         return None
 
-    def state_dict(self):
-        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
-                "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]}
+    def _slots(self):
+        """(index in model.parameters(), offset, parameter) of every parameter that has optimizer state."""
+        e = self.engine
+        base = e.flat_grads.data_ptr()
+        out = []
+        for i, (n, p) in enumerate(e.model_ref().named_parameters()):
+            g = e.grad_views.get(n)
+            if g is not None:
+                out.append((i, (g.data_ptr() - base) // 4, p))
+        return out
 
+    def state_dict(self):
+        """torch.optim.AdamW's format (what the reference stores under "optimizer_state_dict",
+        train_segmentation.py:333): per-parameter step / exp_avg / exp_avg_sq keyed by the index in
+        model.parameters(); parameters that never received a gradient have no entry, as in torch."""
+        n_params = len(self.param_groups[0]["params"])
+        proto = torch.optim.AdamW([torch.nn.Parameter(torch.zeros(1))]).state_dict()["param_groups"][0]
+        group = dict(proto)
+        group.update({k: v for k, v in self.param_groups[0].items() if k != "params"})
+        group["params"] = list(range(n_params))
+        state = {}
+        if self.step_count > 0:
+            for i, off, p in self._slots():
+                state[i] = {"step": torch.tensor(float(self.step_count)),
+                            "exp_avg": self.exp_avg[off:off + p.numel()].view_as(p).clone(),
+                            "exp_avg_sq": self.exp_avg_sq[off:off + p.numel()].view_as(p).clone()}
+        return {"state": state, "param_groups": [group]}
+
+    @torch.no_grad()
     def load_state_dict(self, sd):
-        self.step_count = sd["step"]
-        self.exp_avg.copy_(sd["exp_avg"])
-        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        """Accepts a torch.optim.AdamW state_dict of the same model (a reference checkpoint) or this class's."""
+        if "state" not in sd:  # flat format written by earlier versions of this class
+            self.step_count = sd["step"]
+            self.exp_avg.copy_(sd["exp_avg"])
+            self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+            return
+        g = sd["param_groups"][0]
+        if len(g["params"]) != len(self.param_groups[0]["params"]):
+            raise ValueError("loaded state dict contains a parameter group that doesn't match the size of optimizer's group")
+        for k in ("lr", "betas", "eps", "weight_decay"):
+            if k in g:
+                self.param_groups[0][k] = tuple(g[k]) if k == "betas" else g[k]
+        order = {pid: i for i, pid in enumerate(g["params"])}
+        self.exp_avg.zero_()
+        self.exp_avg_sq.zero_()
+        steps = set()
+        slots = {i: (off, p) for i, off, p in self._slots()}
+        for pid, st in sd["state"].items():
+            i = order[pid]
+            if i not in slots:
+                continue  # state of a parameter this schedule never updates
+            off, p = slots[i]
+            self.exp_avg[off:off + p.numel()].copy_(st["exp_avg"].reshape(-1))
+            self.exp_avg_sq[off:off + p.numel()].copy_(st["exp_avg_sq"].reshape(-1))
+            steps.add(int(st["step"]))
+        if len(steps) > 1:
+            raise ValueError("FusedAdamW keeps one step count; the loaded state has %s" % sorted(steps))
+        self.step_count = steps.pop() if steps else 0

@@ -239,12 +239,23 @@ def test_wrong_input_size_and_cpu_input_raise():
 
 
 def test_device_prefetcher_yields_the_batches_in_order():
+    """Ring of depth + 1 reused staging sets: every batch arrives intact and in order even when the consumer is slow
+    (the copy of batch i + 3 must wait for the step that read batch i), including a ragged last batch."""
     from ssl4gie_b200.prefetch import DevicePrefetcher
     g = torch.Generator().manual_seed(3)
-    host = [(torch.randn(4, 3, 8, 8, generator=g).pin_memory(), torch.randint(0, 5, (4,), generator=g).pin_memory()) for _ in range(5)]
-    got = list(DevicePrefetcher(iter(host)))
-    assert len(got) == 5
-    for (x, t), (xh, th) in zip(got, host):
+    host = [(torch.randn(4, 3, 64, 64, generator=g).pin_memory(), torch.randint(0, 5, (4,), generator=g).pin_memory()) for _ in range(9)]
+    host.append((torch.randn(3, 3, 64, 64, generator=g).pin_memory(), torch.randint(0, 5, (3,), generator=g).pin_memory()))
+    sums, labels, ptrs = [], [], set()
+    for x, t in DevicePrefetcher(iter(host)):
         assert x.is_cuda and t.is_cuda
-        torch.cuda.current_stream().synchronize()
-        assert torch.equal(x.cpu(), xh) and torch.equal(t.cpu(), th)
+        ptrs.add(x.data_ptr())
+        torch.cuda._sleep(20_000_000)  # ~10 ms: the host is several batches ahead of the device
+        sums.append(x.double().sum())
+        labels.append(t.clone())
+    torch.cuda.synchronize()
+    assert len(sums) == 10 and len(ptrs) <= 4  # 3 ring slots + the ragged batch
+    for s_d, t_d, (xh, th) in zip(sums, labels, host):
+        assert abs(s_d.item() - xh.double().sum().item()) < 1e-9 and torch.equal(t_d.cpu(), th)
+    single = list(x.clone() for x in DevicePrefetcher(iter([h[0] for h in host[:3]]), depth=1))
+    assert all(torch.equal(a.cpu(), h[0]) for a, h in zip(single, host))
+
