@@ -254,7 +254,7 @@ def run_ours(args):
         return ms.item(), loss, {"median": per[n // 2], "max": per[-1]}, (w0, w1)
 
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and not os.environ.get("S4G_BENCH_NOSMI"):
         sampler.start()
         t_wait = time.time()
         while sampler.proc and not sampler.lines and time.time() - t_wait < 5.0:  # attached and polling before any timing

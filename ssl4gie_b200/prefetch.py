@@ -26,6 +26,13 @@ def _copy_stream(device):
     return s
 
 
+_SLOT_POOL = {}  # (device index, ((shape, dtype), ...)) -> idle slots of finished prefetchers, staging buffers included
+
+
+def _signature(device, host):
+    return (device.index, tuple((tuple(h.shape), h.dtype) for h in host))
+
+
 class _Slot:
     __slots__ = ("dev", "host", "ready", "free")
 
@@ -60,7 +67,13 @@ class DevicePrefetcher:
             fits = slot.dev is not None and len(slot.dev) == len(host) and all(
                 d.shape == h.shape and d.dtype == h.dtype for d, h in zip(slot.dev, host))
             if not fits:  # first use of the slot, or a ragged last batch
-                slot.dev = tuple(torch.empty(h.shape, dtype=h.dtype, device=self.device) for h in host)
+                idle = _SLOT_POOL.get(_signature(self.device, host))
+                if idle:  # a finished prefetcher's slot: same buffers, its `free` event orders the overwrite
+                    old = idle.pop()
+                    slot.dev, slot.free, slot.ready = old.dev, old.free, old.ready
+                else:
+                    slot.dev = tuple(torch.empty(h.shape, dtype=h.dtype, device=self.device) for h in host)
+                    slot.free = None
             if slot.free is not None:
                 self.stream.wait_event(slot.free)  # the step that read this slot's previous batch has been enqueued before it
             for d, h in zip(slot.dev, host):
@@ -84,6 +97,7 @@ class DevicePrefetcher:
         while len(self.queue) < self.depth and self._issue():
             pass
         if not self.queue:
+            self._retire()
             raise StopIteration
         slot, single = self.queue.pop(0)
         cur.wait_event(slot.ready)
@@ -92,3 +106,14 @@ class DevicePrefetcher:
         self.current = slot
         self._issue()
         return slot.dev[0] if single else slot.dev
+
+    def _retire(self):
+        """Loader exhausted: every slot's last reader is ordered by its `free` event, so the staging buffers can serve the
+        next prefetcher (next epoch) without touching the allocator."""
+        for slot in self.slots:
+            if slot.dev is not None and slot.free is not None:
+                slot.host = None
+                idle = _SLOT_POOL.setdefault(_signature(self.device, slot.dev), [])
+                if len(idle) < 8:
+                    idle.append(slot)
+        self.slots = [_Slot() for _ in range(self.depth + 1)]
