@@ -7,6 +7,7 @@
 //             phase B per 16-key tile   : S^T = K Q^T, dP^T = V dO^T, dS^T ; dV = P^T dO, dK = dS^T Q
 //             (scores are recomputed in both phases: no atomics, no cross-warp reduction, deterministic)
 // Reference semantics: timm 0.6.12 Attention.forward (called from Models/models.py:333-334), scale = 64^-0.5.
+#include <cstdlib>
 #include "kernels.h"
 
 namespace {
@@ -375,6 +376,7 @@ static int attn_grid(int total) {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_attn_sms, cudaDevAttrMultiProcessorCount, dev);
     if (g_attn_sms <= 0) g_attn_sms = 148;
+    if (const char* lim = getenv("S4G_SM_LIMIT")) { const int v = atoi(lim); if (v >= 2 && v < g_attn_sms) g_attn_sms = v; }
   }
   return total < g_attn_sms ? total : g_attn_sms;
 }

@@ -15,6 +15,7 @@
 //               bias / GELU / GELU' / ReLU / residual, vectorised global stores
 #include <cuda.h>
 
+#include <cstdlib>
 #include "kernels.h"
 
 namespace {
@@ -932,6 +933,8 @@ int umma_init() {
   int dev = 0;
   S4G_CUDA(cudaGetDevice(&dev));
   S4G_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  // S4G_SM_LIMIT: persistent grids leave SMs free for a concurrently running collective (experiment knob)
+  if (const char* lim = getenv("S4G_SM_LIMIT")) { const int v = atoi(lim); if (v >= 2 && v < g_num_sms) g_num_sms = v & ~1; }
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
