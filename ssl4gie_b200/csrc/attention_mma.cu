@@ -147,6 +147,7 @@ __device__ __forceinline__ void fwd_block(const uint32_t (&a)[4][4], uint32_t uK
 
 __global__ void __launch_bounds__(THREADS, 1) attn_fwd_mma_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ o,
                                                                   float* __restrict__ lse, int N, int H, int total) {
+  pdl_trigger();
   extern __shared__ __align__(128) uint8_t sm[];
   const int C = H * D, C3 = 3 * C;
   const uint32_t sm_u = (uint32_t)__cvta_generic_to_shared(sm);
@@ -263,6 +264,7 @@ constexpr int BWD_STAGE_BYTES = 4 * TILE_BYTES + 2 * NP * (int)sizeof(float);
 __global__ void __launch_bounds__(THREADS, 1) attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ o,
                                                                   const bf16* __restrict__ dout, const float* __restrict__ lse,
                                                                   bf16* __restrict__ dqkv, int N, int H, int total) {
+  pdl_trigger();
   extern __shared__ __align__(128) uint8_t sm[];
   const int C = H * D, C3 = 3 * C;
   const uint32_t sm_u = (uint32_t)__cvta_generic_to_shared(sm);

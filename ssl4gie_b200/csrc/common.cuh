@@ -100,6 +100,11 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// Programmatic dependent launch: a kernel launched with programmaticStreamSerializationAllowed may start (barrier init, TMEM
+// allocation, descriptor prefetch) while the previous kernel of the stream drains; pdl_wait() returns once that kernel has
+// completed and its writes are visible.  pdl_trigger() lets the NEXT kernel of the stream do the same with this one.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 __device__ __forceinline__ float dgelu_f(float x) {
   const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));

@@ -14,6 +14,7 @@
 // timm PatchEmbed (reference Models/models.py:326): Conv2d(3,768,k16,s16) == GEMM over k = c*256 + i*16 + j
 template <typename T>
 __global__ void patchify_kernel(const float* __restrict__ img, T* __restrict__ out, int B) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const long long n = (long long)B * 196 * 96;  // 768/8 groups per patch
   FOR_GRID(t, n) {
     const int g = (int)(t % 96);
@@ -38,6 +39,7 @@ template <typename T> int k_patchify(const float* img, T* out, int B, cudaStream
 // _pos_embed (Models/models.py:330 / :445-448): x[b,0] = cls + pos[0]; x[b,1+p] = pe[b,p] + pos[1+p]
 __global__ void assemble_tokens_kernel(const float* __restrict__ pe, const float* __restrict__ cls,
                                        const float* __restrict__ pos, float* __restrict__ x, int B) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const long long n = (long long)B * 197 * 192;
   FOR_GRID(t, n) {
     const int c4 = (int)(t % 192);
@@ -96,6 +98,7 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const float* __restr
                                                             const float* __restrict__ beta, T* __restrict__ y,
                                                             float* __restrict__ mean, float* __restrict__ rstd, int rows,
                                                             float eps) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   constexpr int V = C / 128;  // float4 per lane
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -143,6 +146,7 @@ __global__ void __launch_bounds__(256, 1) layernorm_bwd_kernel(const T* __restri
                                                                const float* __restrict__ dres, float* __restrict__ dx,
                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                                int rows, T* __restrict__ dx_cast, float* __restrict__ dxsum) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   constexpr int V = C / 128;
   __shared__ float red[3][C];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -217,6 +221,7 @@ int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float
 // ------------------------------------------------------------------------------------------ small elementwise
 // out = dy * gelu'(u)   (bf16: A&S erf, error far below bf16 resolution; fp32: erff)
 template <typename T> __global__ void __launch_bounds__(256) dgelu_mul_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out, long long n8) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
     Vec8<T> a[2], b[2];
@@ -238,6 +243,7 @@ template <typename T> __global__ void __launch_bounds__(256) dgelu_mul_kernel(co
 template <typename T>
 __global__ void __launch_bounds__(256, 3) dgelu_mul_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out,
                                                                float* __restrict__ colsum, long long M, int N, long long rows_per_block) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   __shared__ float red[8][256 + 8];
   const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cg * 8;
@@ -294,6 +300,7 @@ template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long
 }
 // a = gelu(u)
 template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T* __restrict__ u, T* __restrict__ out, long long n8) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
     Vec8<T> b[2];
@@ -318,6 +325,7 @@ template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t s
 // column sums of a [M, N] matrix (bias gradients); out must be zeroed.  Block = 32 column groups (8 columns, one
 // 16 B load each) x 8 row lanes, rows walked with a 4-deep unroll; one atomic per column per block.
 template <typename T> __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, long long M, int N, int ld, long long rows_per_block) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   __shared__ float red[8][256 + 8];
   const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cg * 8;
@@ -367,6 +375,7 @@ template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, 
 
 // Slice(1)+Transpose+Unflatten (Models/DPT_decoder.py:503-515): token rows 1..196 ARE the NHWC map
 template <typename T> __global__ void tokens_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ out, int B) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const long long n = (long long)B * 196 * 96;
   FOR_GRID(t, n) {
     const int g = (int)(t % 96);
@@ -386,6 +395,7 @@ template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaSt
   return 0;
 }
 template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap, float* __restrict__ dx, int B, int accumulate, T* __restrict__ cast_out) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const long long n = (long long)B * 197 * 96;
   FOR_GRID(t, n) {
     const int g = (int)(t % 96);
@@ -431,6 +441,7 @@ template <typename T> int k_cast_f32(const float* in, T* out, long long n, cudaS
 }
 
 template <typename T> __global__ void relu_kernel(const T* __restrict__ x, T* __restrict__ y, long long n8) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   FOR_GRID(i, n8) {
     Vec8<T> a;
     a.load(x + i * 8);
@@ -445,6 +456,7 @@ template <typename T> int k_relu(const T* x, T* y, long long n, cudaStream_t st)
   return 0;
 }
 template <typename T> __global__ void relu_bwd_add_kernel(const T* __restrict__ dr, const T* __restrict__ x, const T* __restrict__ dskip, T* __restrict__ dx, long long n8) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   FOR_GRID(i, n8) {
     Vec8<T> a, b, c;
     a.load(dr + i * 8); b.load(x + i * 8);
@@ -460,6 +472,7 @@ template <typename T> int k_relu_bwd_add(const T* dr, const T* x, const T* dskip
   return 0;
 }
 template <typename T> __global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, long long n8) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   FOR_GRID(i, n8) {
     Vec8<T> u, v;
     u.load(a + i * 8); v.load(b + i * 8);
@@ -477,6 +490,7 @@ template <typename T> int k_add(const T* a, const T* b, T* y, long long n, cudaS
 // ConvTranspose2d with kernel == stride (Models/DPT_decoder.py:341-350,365-374) = GEMM to
 // ycol[p][(kh,kw,co)] then this scatter: out[b, h*k+kh, w*k+kw, co] = ycol + bias[co]
 template <typename T> __global__ void pixel_shuffle_kernel(const T* __restrict__ ycol, const float* __restrict__ bias, T* __restrict__ out, int B, int H, int W, int C, int k, int unshuffle) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int c8 = C / 8;
   const long long n = (long long)B * H * k * W * k * c8;
   FOR_GRID(t, n) {
@@ -513,6 +527,7 @@ template <typename T> int k_pixel_unshuffle(const T* dout, T* dycol, int B, int 
 
 // Conv2d 3x3 stride 2 pad 1 (Models/DPT_decoder.py:403-409) as explicit im2col + GEMM (only one small layer)
 template <typename T> __global__ void im2col_s2_kernel(const T* __restrict__ x, T* __restrict__ col, int B, int H, int W, int C) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2, c8 = C / 8;
   const long long n = (long long)B * Ho * Wo * 9 * c8;
   FOR_GRID(t, n) {
@@ -539,6 +554,7 @@ template <typename T> int k_im2col_s2(const T* x, T* col, int B, int H, int W, i
   return 0;
 }
 template <typename T> __global__ void col2im_s2_kernel(const T* __restrict__ dcol, T* __restrict__ dx, int B, int H, int W, int C) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2, c8 = C / 8;
   const long long n = (long long)B * H * W * c8;
   FOR_GRID(t, n) {
@@ -587,6 +603,7 @@ __device__ __forceinline__ void bil_src(int o, int in_size, float scale, int& i0
 // grid.y = group of 4 output rows (b * Ho/4 + oh/4), grid.x * 256 threads cover (ow, channel group): 32-bit index math,
 // 16 independent 16 B loads in flight per thread
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const int idx = blockIdx.x * 256 + threadIdx.x;
@@ -643,6 +660,7 @@ __device__ __forceinline__ void bil_taps(int i, int in_size, float scale, float 
 }
 // grid.y = input row (b * H + h); the separable weights are computed once per thread
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const int idx = blockIdx.x * 256 + threadIdx.x;
@@ -895,6 +913,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, 
                                                        const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                        const float* __restrict__ beta, const T* __restrict__ skip,
                                                        T* __restrict__ y, int relu, long long M, int C) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
   float sc[8], sh[8];
@@ -953,6 +972,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const T* __restric
                                                               const double* __restrict__ sums, double count,
                                                               T* __restrict__ dx, float* dgamma, float* dbeta, int relu,
                                                               long long M, int C) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
   // SyncBatchNorm (count = M * world): torch keeps grad_weight / grad_bias LOCAL and DDP averages them over ranks; the
@@ -1169,6 +1189,7 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_apply_kernel(const float* 
                                                                    float p, uint64_t seed, const double* __restrict__ sums,
                                                                    double count, T* __restrict__ dx, float* dgamma, float* dbeta,
                                                                    long long M) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   const int lane = threadIdx.x & 31;
   if (blockIdx.x == 0) {  // global sums / world under SyncBatchNorm, see bn_bwd_apply_kernel
     const double gs = (double)M / count;
@@ -1318,6 +1339,7 @@ template <typename T> int k_pack_linear(const float* w, T* wp, T* wt, int N, int
 // All nn.Linear / 1x1-conv weights of the model in ONE launch (the per-layer launches are latency-bound: 58 of them
 // took 0.44 ms for 0.1 ms worth of HBM traffic).  The job table travels in kernel-parameter space.
 template <typename T> __global__ void __launch_bounds__(256) pack_linear_grouped_kernel(const __grid_constant__ PackLinearJobs jobs) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   __shared__ float tile[32][33];
   int lo = 0, hi = jobs.n - 1;
   while (lo < hi) {   // last job whose first tile is <= blockIdx.x
@@ -1373,6 +1395,7 @@ template <typename T> int k_pack_conv(const float* w, T* wf, T* wd, int Co, int 
 // All 3x3 conv weights in ONE launch: a block owns one output channel (-> wf row [tap][Ci]) or one input channel
 // (-> wd row [tap'][Co]) and transposes its 9*C weights through shared memory, so both writes are contiguous.
 template <typename T> __global__ void __launch_bounds__(256) pack_conv3_grouped_kernel(const __grid_constant__ PackLinearJobs jobs) {
+  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
   __shared__ float sm[9 * 768];
   int lo = 0, hi = jobs.n - 1;
   while (lo < hi) {

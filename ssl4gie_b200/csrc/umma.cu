@@ -345,6 +345,8 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
+  pdl_wait();     // everything above overlapped the previous kernel's tail; global memory is touched only below
+  pdl_trigger();
   const uint32_t tmem_base = ctl->tmem_base;
 
   if (warp == 0) {
@@ -630,6 +632,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
+  pdl_wait();     // everything above overlapped the previous kernel's tail; global memory is touched only below
+  pdl_trigger();
   const uint32_t tmem_base = ctl->tmem_base;
 
   // work item -> (split, tap, ci tile, co tile); consecutive CTAs share the pixel range (L2 reuse of dY / X)
@@ -762,6 +766,7 @@ struct WgradReduceParams {
   long long so, si, st;
 };
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReduceParams p) {
+  pdl_trigger();
   __shared__ float tile[32][33];
   const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
   const int co0 = blockIdx.x * 32, ci0 = blockIdx.y * 32, tap = blockIdx.z;
@@ -793,6 +798,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReducePara
 // output tile, 16 independent 128 B-coalesced loads per thread and split, transposed through a conflict-free smem
 // panel so that every warp store is a full 128 B row segment of dW.
 __global__ void __launch_bounds__(256) wgrad_reduce_linear_kernel(const WgradReduceParams p) {
+  pdl_trigger();
   __shared__ float tile[32][129];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int subs = p.block_n >> 5;
@@ -834,6 +840,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 int g_num_sms = 148;
+int g_pdl = 1;  // programmatic dependent launch of the tcgen05 kernels (S4G_PDL=0 turns it off)
 
 int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
              const uint32_t* box) {
@@ -933,6 +940,7 @@ int umma_init() {
   int dev = 0;
   S4G_CUDA(cudaGetDevice(&dev));
   S4G_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  if (const char* e = getenv("S4G_PDL")) g_pdl = atoi(e) != 0;
   // S4G_SM_LIMIT: persistent grids leave SMs free for a concurrently running collective (experiment knob)
   if (const char* lim = getenv("S4G_SM_LIMIT")) { const int v = atoi(lim); if (v >= 2 && v < g_num_sms) g_num_sms = v & ~1; }
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -993,14 +1001,24 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     cfg.blockDim = dim3(FPROP_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g_pdl ? 2 : 1;
     S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<2>, tmA, tmB, tmO, tmO2, p));
   } else {
-    const int grid = std::min(p.tiles_m * p.tiles_n, g_num_sms);
-    umma_fprop_kernel<1><<<grid, FPROP_THREADS, smem, st>>>(tmA, tmB, tmO, tmO2, p);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(std::min(p.tiles_m * p.tiles_n, g_num_sms));
+    cfg.blockDim = dim3(FPROP_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g_pdl ? 1 : 0;
+    S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<1>, tmA, tmB, tmO, tmO2, p));
   }
   S4G_KERNEL_CHECK();
   return 0;
@@ -1103,14 +1121,24 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = w.smem_bytes;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g_pdl ? 2 : 1;
     S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_wgrad_kernel<2>, tmY, tmX, p));
   } else {
-    const int grid = std::min(w.out_tiles * p.splits, g_num_sms);
-    umma_wgrad_kernel<1><<<grid, NUM_THREADS, w.smem_bytes, st>>>(tmY, tmX, p);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(std::min(w.out_tiles * p.splits, g_num_sms));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = w.smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = g_pdl ? 1 : 0;
+    S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_wgrad_kernel<1>, tmY, tmX, p));
   }
   S4G_KERNEL_CHECK();
   if (w.direct) return 0;
