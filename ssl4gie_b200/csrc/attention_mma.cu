@@ -147,6 +147,7 @@ __device__ __forceinline__ void fwd_block(const uint32_t (&a)[4][4], uint32_t uK
 
 __global__ void __launch_bounds__(THREADS, 1) attn_fwd_mma_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ o,
                                                                   float* __restrict__ lse, int N, int H, int total) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   extern __shared__ __align__(128) uint8_t sm[];
   const int C = H * D, C3 = 3 * C;
@@ -264,6 +265,7 @@ constexpr int BWD_STAGE_BYTES = 4 * TILE_BYTES + 2 * NP * (int)sizeof(float);
 __global__ void __launch_bounds__(THREADS, 1) attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ o,
                                                                   const bf16* __restrict__ dout, const float* __restrict__ lse,
                                                                   bf16* __restrict__ dqkv, int N, int H, int total) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   extern __shared__ __align__(128) uint8_t sm[];
   const int C = H * D, C3 = 3 * C;
@@ -388,7 +390,7 @@ int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int N, int H, cuda
   const size_t smem = 2 * 3 * TILE_BYTES;
   static bool attr = false;
   if (!attr) { S4G_CUDA(cudaFuncSetAttribute(attn_fwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  attn_fwd_mma_kernel<<<attn_grid(B * H), THREADS, smem, st>>>(qkv, o, lse, N, H, B * H);
+  S4G_CUDA(launch_dep(attn_fwd_mma_kernel, dim3(attn_grid(B * H)), dim3(THREADS), smem, st, qkv, o, lse, N, H, B * H));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -398,7 +400,7 @@ int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* 
   const size_t smem = 2 * BWD_STAGE_BYTES;
   static bool attr = false;
   if (!attr) { S4G_CUDA(cudaFuncSetAttribute(attn_bwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  attn_bwd_mma_kernel<<<attn_grid(B * H), THREADS, smem, st>>>(qkv, o, dout, lse, dqkv, N, H, B * H);
+  S4G_CUDA(launch_dep(attn_bwd_mma_kernel, dim3(attn_grid(B * H)), dim3(THREADS), smem, st, qkv, o, dout, lse, dqkv, N, H, B * H));
   S4G_KERNEL_CHECK();
   return 0;
 }

@@ -1,5 +1,6 @@
 // Shared device/host helpers for libssl4gie_b200 (sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -105,6 +106,22 @@ __device__ __forceinline__ float warp_max(float v) {
 // completed and its writes are visible.  pdl_trigger() lets the NEXT kernel of the stream do the same with this one.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Host side of the same: launch `kernel` so that it may begin before the previous kernel of `st` has drained.  Only for
+// kernels that execute pdl_wait() before their first global-memory access.  S4G_PDL=0 launches them the ordinary way.
+inline int pdl_enabled() {
+  static const int v = [] { const char* e = getenv("S4G_PDL"); return e ? (atoi(e) != 0) : 1; }();
+  return v;
+}
+template <typename... KA, typename... A>
+inline cudaError_t launch_dep(void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KA>(args)...);
+}
 __device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 __device__ __forceinline__ float dgelu_f(float x) {
   const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));

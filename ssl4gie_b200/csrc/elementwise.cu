@@ -98,7 +98,8 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const float* __restr
                                                             const float* __restrict__ beta, T* __restrict__ y,
                                                             float* __restrict__ mean, float* __restrict__ rstd, int rows,
                                                             float eps) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   constexpr int V = C / 128;  // float4 per lane
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -127,8 +128,8 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(const float* __restr
 template <typename T>
 int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y, float* mean, float* rstd, int rows,
                     int C, float eps, cudaStream_t st) {
-  if (C == 768) layernorm_fwd_kernel<T, 768><<<cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, y, mean, rstd, rows, eps);
-  else if (C == 512) layernorm_fwd_kernel<T, 512><<<cdiv(rows, 8), 256, 0, st>>>(x, gamma, beta, y, mean, rstd, rows, eps);
+  if (C == 768) S4G_CUDA(launch_dep(layernorm_fwd_kernel<T, 768>, dim3(cdiv(rows, 8)), dim3(256), 0, st, x, gamma, beta, y, mean, rstd, rows, eps));
+  else if (C == 512) S4G_CUDA(launch_dep(layernorm_fwd_kernel<T, 512>, dim3(cdiv(rows, 8)), dim3(256), 0, st, x, gamma, beta, y, mean, rstd, rows, eps));
   else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
   S4G_KERNEL_CHECK();
   return 0;
@@ -146,7 +147,8 @@ __global__ void __launch_bounds__(256, 1) layernorm_bwd_kernel(const T* __restri
                                                                const float* __restrict__ dres, float* __restrict__ dx,
                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                                int rows, T* __restrict__ dx_cast, float* __restrict__ dxsum) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   constexpr int V = C / 128;
   __shared__ float red[3][C];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -210,9 +212,9 @@ int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float
                     float* dxsum) {
   const int grid = std::min(cdiv(rows, 8), 148);
   if (C == 768)
-    layernorm_bwd_kernel<T, 768><<<grid, 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum);
+    S4G_CUDA(launch_dep(layernorm_bwd_kernel<T, 768>, dim3(grid), dim3(256), 0, st, dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum));
   else if (C == 512)
-    layernorm_bwd_kernel<T, 512><<<grid, 256, 0, st>>>(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum);
+    S4G_CUDA(launch_dep(layernorm_bwd_kernel<T, 512>, dim3(grid), dim3(256), 0, st, dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum));
   else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
   S4G_KERNEL_CHECK();
   return 0;
@@ -243,7 +245,8 @@ template <typename T> __global__ void __launch_bounds__(256) dgelu_mul_kernel(co
 template <typename T>
 __global__ void __launch_bounds__(256, 3) dgelu_mul_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out,
                                                                float* __restrict__ colsum, long long M, int N, long long rows_per_block) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   __shared__ float red[8][256 + 8];
   const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cg * 8;
@@ -290,7 +293,7 @@ template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long
     const long long M = n / N;
     // 3 resident blocks per SM (launch bound above): one wave of 148 * 3 blocks
     const int rblocks = (int)std::max<long long>(1, std::min<long long>(cdiv(M, 64), (148 * 3) / cdiv(N, 256)));
-    dgelu_mul_colsum_kernel<T><<<dim3(cdiv(N, 256), rblocks), 256, 0, st>>>(dy, u, out, colsum, M, N, cdiv(M, rblocks));
+    S4G_CUDA(launch_dep(dgelu_mul_colsum_kernel<T>, dim3(dim3(cdiv(N, 256), rblocks)), dim3(256), 0, st, dy, u, out, colsum, M, N, cdiv(M, rblocks)));
   } else {
     if (colsum) { s4g_set_error("dgelu_mul: bad column-sum shape"); return S4G_ERR_SHAPE; }
     dgelu_mul_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(dy, u, out, n / 8);
@@ -300,7 +303,8 @@ template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long
 }
 // a = gelu(u)
 template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T* __restrict__ u, T* __restrict__ out, long long n8) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
     Vec8<T> b[2];
@@ -317,7 +321,7 @@ template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T
   }
 }
 template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st) {
-  gelu_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(u, out, n / 8);
+  S4G_CUDA(launch_dep(gelu_kernel<T>, GRID1D(n / 16, 256), 0, st, u, out, n / 8));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -325,7 +329,8 @@ template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t s
 // column sums of a [M, N] matrix (bias gradients); out must be zeroed.  Block = 32 column groups (8 columns, one
 // 16 B load each) x 8 row lanes, rows walked with a 4-deep unroll; one atomic per column per block.
 template <typename T> __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, long long M, int N, int ld, long long rows_per_block) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   __shared__ float red[8][256 + 8];
   const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + cg * 8;
@@ -368,7 +373,7 @@ template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, 
   const long long want = std::max<long long>(1, (148 * 4) / gx);
   const long long rpb = std::max<long long>(64, (M + want - 1) / want);
   dim3 grid(gx, cdiv(M, rpb));
-  colsum_kernel<T><<<grid, 256, 0, st>>>(dy, out, M, N, ld, rpb);
+  S4G_CUDA(launch_dep(colsum_kernel<T>, dim3(grid), dim3(256), 0, st, dy, out, M, N, ld, rpb));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -441,7 +446,8 @@ template <typename T> int k_cast_f32(const float* in, T* out, long long n, cudaS
 }
 
 template <typename T> __global__ void relu_kernel(const T* __restrict__ x, T* __restrict__ y, long long n8) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   FOR_GRID(i, n8) {
     Vec8<T> a;
     a.load(x + i * 8);
@@ -451,12 +457,13 @@ template <typename T> __global__ void relu_kernel(const T* __restrict__ x, T* __
   }
 }
 template <typename T> int k_relu(const T* x, T* y, long long n, cudaStream_t st) {
-  relu_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(x, y, n / 8);
+  S4G_CUDA(launch_dep(relu_kernel<T>, GRID1D(n / 8, 256), 0, st, x, y, n / 8));
   S4G_KERNEL_CHECK();
   return 0;
 }
 template <typename T> __global__ void relu_bwd_add_kernel(const T* __restrict__ dr, const T* __restrict__ x, const T* __restrict__ dskip, T* __restrict__ dx, long long n8) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   FOR_GRID(i, n8) {
     Vec8<T> a, b, c;
     a.load(dr + i * 8); b.load(x + i * 8);
@@ -467,12 +474,13 @@ template <typename T> __global__ void relu_bwd_add_kernel(const T* __restrict__ 
   }
 }
 template <typename T> int k_relu_bwd_add(const T* dr, const T* x, const T* dskip, T* dx, long long n, cudaStream_t st) {
-  relu_bwd_add_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(dr, x, dskip, dx, n / 8);
+  S4G_CUDA(launch_dep(relu_bwd_add_kernel<T>, GRID1D(n / 8, 256), 0, st, dr, x, dskip, dx, n / 8));
   S4G_KERNEL_CHECK();
   return 0;
 }
 template <typename T> __global__ void add_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, long long n8) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   FOR_GRID(i, n8) {
     Vec8<T> u, v;
     u.load(a + i * 8); v.load(b + i * 8);
@@ -482,7 +490,7 @@ template <typename T> __global__ void add_kernel(const T* __restrict__ a, const 
   }
 }
 template <typename T> int k_add(const T* a, const T* b, T* y, long long n, cudaStream_t st) {
-  add_kernel<T><<<GRID1D(n / 8, 256), 0, st>>>(a, b, y, n / 8);
+  S4G_CUDA(launch_dep(add_kernel<T>, GRID1D(n / 8, 256), 0, st, a, b, y, n / 8));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -603,7 +611,8 @@ __device__ __forceinline__ void bil_src(int o, int in_size, float scale, int& i0
 // grid.y = group of 4 output rows (b * Ho/4 + oh/4), grid.x * 256 threads cover (ow, channel group): 32-bit index math,
 // 16 independent 16 B loads in flight per thread
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const int idx = blockIdx.x * 256 + threadIdx.x;
@@ -635,7 +644,7 @@ template <typename T> __global__ void __launch_bounds__(256) bilinear2x_fwd_kern
   }
 }
 template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st) {
-  bilinear2x_fwd_kernel<T><<<dim3(cdiv(2 * W * (C / 8), 256), B * cdiv(2 * H, 4)), 256, 0, st>>>(x, y, B, H, W, C);
+  S4G_CUDA(launch_dep(bilinear2x_fwd_kernel<T>, dim3(dim3(cdiv(2 * W * (C / 8), 256), B * cdiv(2 * H, 4))), dim3(256), 0, st, x, y, B, H, W, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -660,7 +669,8 @@ __device__ __forceinline__ void bil_taps(int i, int in_size, float scale, float 
 }
 // grid.y = input row (b * H + h); the separable weights are computed once per thread
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const int idx = blockIdx.x * 256 + threadIdx.x;
@@ -694,7 +704,7 @@ template <typename T> __global__ void __launch_bounds__(256) bilinear2x_bwd_kern
   o.store(dx + ((size_t)blockIdx.y * W + w) * C + g * 8);
 }
 template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int W, int C, cudaStream_t st) {
-  bilinear2x_bwd_kernel<T><<<dim3(cdiv(W * (C / 8), 256), B * H), 256, 0, st>>>(dy, dx, B, H, W, C);
+  S4G_CUDA(launch_dep(bilinear2x_bwd_kernel<T>, dim3(dim3(cdiv(W * (C / 8), 256), B * H)), dim3(256), 0, st, dy, dx, B, H, W, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -913,7 +923,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, 
                                                        const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                        const float* __restrict__ beta, const T* __restrict__ skip,
                                                        T* __restrict__ y, int relu, long long M, int C) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
   float sc[8], sh[8];
@@ -958,7 +969,7 @@ template <typename T>
 int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta, const T* skip,
                T* y, int relu, long long M, int C, cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
-  bn_apply_kernel<T><<<bn_grid(M, C), 256, 0, st>>>(x, mean, rstd, gamma, beta, skip, y, relu, M, C);
+  S4G_CUDA(launch_dep(bn_apply_kernel<T>, dim3(bn_grid(M, C)), dim3(256), 0, st, x, mean, rstd, gamma, beta, skip, y, relu, M, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -972,7 +983,8 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const T* __restric
                                                               const double* __restrict__ sums, double count,
                                                               T* __restrict__ dx, float* dgamma, float* dbeta, int relu,
                                                               long long M, int C) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
   // SyncBatchNorm (count = M * world): torch keeps grad_weight / grad_bias LOCAL and DDP averages them over ranks; the
@@ -1027,7 +1039,7 @@ int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd
                    const double* sums, double count, T* dx, float* dgamma, float* dbeta, int relu, long long M, int C,
                    cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
-  bn_bwd_apply_kernel<T><<<bn_grid(M, C), 256, 0, st>>>(dy, x, mean, rstd, gamma, beta, sums, count, dx, dgamma, dbeta, relu, M, C);
+  S4G_CUDA(launch_dep(bn_bwd_apply_kernel<T>, dim3(bn_grid(M, C)), dim3(256), 0, st, dy, x, mean, rstd, gamma, beta, sums, count, dx, dgamma, dbeta, relu, M, C));
   S4G_KERNEL_CHECK();
   return 0;
 }

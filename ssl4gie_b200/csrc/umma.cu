@@ -766,6 +766,7 @@ struct WgradReduceParams {
   long long so, si, st;
 };
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReduceParams p) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   __shared__ float tile[32][33];
   const int tx = threadIdx.x, ty = threadIdx.y;   // 32 x 8
@@ -798,6 +799,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReducePara
 // output tile, 16 independent 128 B-coalesced loads per thread and split, transposed through a conflict-free smem
 // panel so that every warp store is a full 128 B row segment of dW.
 __global__ void __launch_bounds__(256) wgrad_reduce_linear_kernel(const WgradReduceParams p) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   __shared__ float tile[32][129];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1149,9 +1151,9 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   if (torch_layout) { r.so = (long long)g.Cin * p.taps; r.si = p.taps; r.st = 1; }   // [Cout][Cin][R][S]
   else { r.so = p.K; r.si = 1; r.st = g.Cin; }                                        // packed [Cout][tap][Cin]
   if (p.taps == 1 && r.si == 1)
-    wgrad_reduce_linear_kernel<<<r.tiles_co * r.tiles_ci * (r.block_n / 32), 256, 0, st>>>(r);
+    S4G_CUDA(launch_dep(wgrad_reduce_linear_kernel, dim3(r.tiles_co * r.tiles_ci * (r.block_n / 32)), dim3(256), 0, st, r));
   else
-    wgrad_reduce_kernel<<<dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps), dim3(32, 8), 0, st>>>(r);
+    S4G_CUDA(launch_dep(wgrad_reduce_kernel, dim3(dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps)), dim3(dim3(32, 8)), 0, st, r));
   S4G_KERNEL_CHECK();
   return 0;
 }
