@@ -51,6 +51,10 @@ struct S4GModel {
   void* peer_boxes[S4G_PEER_MAX_WORLD] = {};  // SyncBN exchange through NVLink peer memory (peer.cu) when peer_world > 1
   int peer_rank = 0, peer_world = 0;
   unsigned long long peer_seq = 0;
+  // BatchNorm accumulators of all layers live in two contiguous pools, zeroed by ONE memset at the top of forward
+  // (sum / sumsq) and ONE at the top of backward (sum dy / sum dy*xhat) instead of one memset per layer
+  size_t bn_stats_pool = 0, bn_sums_pool = 0;
+  int bn_count = 0;
   // in-place sum over ranks of `count` doubles: the peer-memory kernel when mailboxes are set, else the host callback
   int exchange(double* v, int count, cudaStream_t st) {
     if (peer_world > 1) { launches++; return k_peer_sum_f64(v, count, peer_boxes, peer_rank, peer_world, peer_seq++, st); }
@@ -235,8 +239,14 @@ struct Builder {
   BN bn(const std::string& name) {
     BN n{P(name + ".weight"), P(name + ".bias"), P(name + ".running_mean"), P(name + ".running_var"),
          P(name + ".num_batches_tracked"), 0, 0, 0, 0};
-    n.stats = alloc(sizeof(double) * 512);
-    n.sums = alloc(sizeof(double) * 512);
+    constexpr int MAX_BN = 17;  // DPT_decoder.py:204-206,492
+    if (m->bn_count == 0) {
+      m->bn_stats_pool = alloc(sizeof(double) * 512 * MAX_BN);
+      m->bn_sums_pool = alloc(sizeof(double) * 512 * MAX_BN);
+    }
+    n.stats = m->bn_stats_pool + sizeof(double) * 512 * m->bn_count;
+    n.sums = m->bn_sums_pool + sizeof(double) * 512 * m->bn_count;
+    m->bn_count++;
     n.mean = alloc(sizeof(float) * 256);
     n.rstd = alloc(sizeof(float) * 256);
     return n;
@@ -246,8 +256,7 @@ struct Builder {
     float* mean = m->template at<float>(n.mean);
     float* rstd = m->template at<float>(n.rstd);
     if (!m->training) { m->launches++; return k_bn_eval_prepare(n.rm->p, n.rv->p, mean, rstd, 1e-5f, 256, st); }
-    double* stats = m->template at<double>(n.stats);
-    S4G_CUDA(cudaMemsetAsync(stats, 0, sizeof(double) * 512, st));
+    double* stats = m->template at<double>(n.stats);  // zeroed at the top of forward
     m->launches += 2;
     S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st));
     if (m->d.world_size > 1) S4G_TRY(m->exchange(stats, 512, st));
@@ -258,8 +267,7 @@ struct Builder {
     double* sums = m->template at<double>(n.sums);
     const float* mean = m->template at<float>(n.mean);
     const float* rstd = m->template at<float>(n.rstd);
-    S4G_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 512, st));
-    m->launches += 2;
+    m->launches += 2;  // sums: zeroed at the top of backward
     S4G_TRY(k_bn_bwd_reduce<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, relu, M, 256, st));
     if (m->d.world_size > 1) S4G_TRY(m->exchange(sums, 512, st));
     return k_bn_bwd_apply<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, (double)M * m->d.world_size, dx, n.w->g, n.b->g,
@@ -598,7 +606,6 @@ struct Builder {
         double* sums = mm->template at<double>(n.sums);
         mm->launches += 3;
         S4G_TRY(k_bilinear2x_f32_bwd(mm->dout, ds, self->B, 112, 112, st));
-        S4G_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 512, st));
         S4G_CUDA(cudaMemsetAsync(w4->g, 0, sizeof(float) * 256, st));
         S4G_CUDA(cudaMemsetAsync(b4->g, 0, sizeof(float), st));
         S4G_TRY(k_seghead_bwd_reduce<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
@@ -815,6 +822,7 @@ int build(S4GModel* m, std::unique_ptr<Builder<T>>& slot) {
 int ensure_built(S4GModel* m) {
   if (m->built) return 0;
   m->pack.clear(); m->fwd.clear(); m->bwd_dec.clear(); m->bwd_enc.clear(); m->acts.clear();
+  m->bn_count = 0;
   int r;
   if (m->d.dtype == S4G_DTYPE_F32) r = build<float>(m, g_builders[m].f);
   else r = build<bf16>(m, g_builders[m].h);
@@ -913,6 +921,7 @@ int s4g_model_forward(S4GModel* m, const float* images, float* out, int training
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   m->images = images; m->out = out; m->training = training; m->seed = seed; m->dropout_mask = dropout_mask;
   m->launches = 0;
+  if (m->bn_count && training) S4G_CUDA(cudaMemsetAsync(m->ws + m->bn_stats_pool, 0, sizeof(double) * 512 * m->bn_count, st));
   for (auto& op : m->pack) S4G_TRY(op(st));
   for (auto& op : m->fwd) S4G_TRY(op(st));
   return 0;
@@ -925,6 +934,7 @@ int s4g_model_backward(S4GModel* m, const float* dout, void* stream) {
   m->dout = dout;
   m->launches = 0;
   const int nb = (int)m->events.size();
+  if (m->bn_count) S4G_CUDA(cudaMemsetAsync(m->ws + m->bn_sums_pool, 0, sizeof(double) * 512 * m->bn_count, st));
   for (size_t i = m->bwd_dec.size(); i-- > 0;) S4G_TRY(m->bwd_dec[i](st));
   if (nb > 0) S4G_CUDA(cudaEventRecord(m->events[0], st));
   // bwd_enc[0] = patch-embed, bwd_enc[1 + i] = block i
