@@ -380,7 +380,8 @@ template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, 
 
 // Slice(1)+Transpose+Unflatten (Models/DPT_decoder.py:503-515): token rows 1..196 ARE the NHWC map
 template <typename T> __global__ void tokens_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ out, int B) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const long long n = (long long)B * 196 * 96;
   FOR_GRID(t, n) {
     const int g = (int)(t % 96);
@@ -395,12 +396,13 @@ template <typename T> __global__ void tokens_to_nhwc_kernel(const float* __restr
   }
 }
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st) {
-  tokens_to_nhwc_kernel<T><<<GRID1D((long long)B * 196 * 96, 256), 0, st>>>(x, out, B);
+  S4G_CUDA(launch_dep(tokens_to_nhwc_kernel<T>, GRID1D((long long)B * 196 * 96, 256), 0, st, x, out, B));
   S4G_KERNEL_CHECK();
   return 0;
 }
 template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap, float* __restrict__ dx, int B, int accumulate, T* __restrict__ cast_out) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const long long n = (long long)B * 197 * 96;
   FOR_GRID(t, n) {
     const int g = (int)(t % 96);
@@ -431,7 +433,7 @@ template <typename T> __global__ void tap_grad_kernel(const T* __restrict__ dtap
   }
 }
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out) {
-  tap_grad_kernel<T><<<GRID1D((long long)B * 197 * 96, 256), 0, st>>>(dtap, dx, B, accumulate, cast_out);
+  S4G_CUDA(launch_dep(tap_grad_kernel<T>, GRID1D((long long)B * 197 * 96, 256), 0, st, dtap, dx, B, accumulate, cast_out));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -498,7 +500,8 @@ template <typename T> int k_add(const T* a, const T* b, T* y, long long n, cudaS
 // ConvTranspose2d with kernel == stride (Models/DPT_decoder.py:341-350,365-374) = GEMM to
 // ycol[p][(kh,kw,co)] then this scatter: out[b, h*k+kh, w*k+kw, co] = ycol + bias[co]
 template <typename T> __global__ void pixel_shuffle_kernel(const T* __restrict__ ycol, const float* __restrict__ bias, T* __restrict__ out, int B, int H, int W, int C, int k, int unshuffle) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int c8 = C / 8;
   const long long n = (long long)B * H * k * W * k * c8;
   FOR_GRID(t, n) {
@@ -522,13 +525,13 @@ template <typename T> __global__ void pixel_shuffle_kernel(const T* __restrict__
 }
 template <typename T> int k_pixel_shuffle(const T* ycol, const float* bias, T* out, int B, int H, int W, int C, int k, cudaStream_t st) {
   const long long n = (long long)B * H * k * W * k * (C / 8);
-  pixel_shuffle_kernel<T><<<GRID1D(n, 256), 0, st>>>(ycol, bias, out, B, H, W, C, k, 0);
+  S4G_CUDA(launch_dep(pixel_shuffle_kernel<T>, GRID1D(n, 256), 0, st, ycol, bias, out, B, H, W, C, k, 0));
   S4G_KERNEL_CHECK();
   return 0;
 }
 template <typename T> int k_pixel_unshuffle(const T* dout, T* dycol, int B, int H, int W, int C, int k, cudaStream_t st) {
   const long long n = (long long)B * H * k * W * k * (C / 8);
-  pixel_shuffle_kernel<T><<<GRID1D(n, 256), 0, st>>>(dycol, nullptr, const_cast<T*>(dout), B, H, W, C, k, 1);
+  S4G_CUDA(launch_dep(pixel_shuffle_kernel<T>, GRID1D(n, 256), 0, st, dycol, nullptr, const_cast<T*>(dout), B, H, W, C, k, 1));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -709,6 +712,8 @@ template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int
   return 0;
 }
 __global__ void bilinear2x_f32_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int B, int H, int W) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const long long n = (long long)B * Ho * Wo;
@@ -722,11 +727,13 @@ __global__ void bilinear2x_f32_fwd_kernel(const float* __restrict__ x, float* __
   }
 }
 int k_bilinear2x_f32_fwd(const float* x, float* y, int B, int H, int W, cudaStream_t st) {
-  bilinear2x_f32_fwd_kernel<<<GRID1D((long long)B * 4 * H * W, 256), 0, st>>>(x, y, B, H, W);
+  S4G_CUDA(launch_dep(bilinear2x_f32_fwd_kernel, GRID1D((long long)B * 4 * H * W, 256), 0, st, x, y, B, H, W));
   S4G_KERNEL_CHECK();
   return 0;
 }
 __global__ void bilinear2x_f32_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int B, int H, int W) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
   const long long n = (long long)B * H * W;
@@ -746,7 +753,7 @@ __global__ void bilinear2x_f32_bwd_kernel(const float* __restrict__ dy, float* _
   }
 }
 int k_bilinear2x_f32_bwd(const float* dy, float* dx, int B, int H, int W, cudaStream_t st) {
-  bilinear2x_f32_bwd_kernel<<<GRID1D((long long)B * H * W, 256), 0, st>>>(dy, dx, B, H, W);
+  S4G_CUDA(launch_dep(bilinear2x_f32_bwd_kernel, GRID1D((long long)B * H * W, 256), 0, st, dy, dx, B, H, W));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -760,6 +767,8 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const T* __restrict__ a,
                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
                                                         double* __restrict__ sums, int relu, long long M, int C,
                                                         long long rows_per_block) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   // FWD: a = x, sums = {sum x, sum x^2}.  BWD: a = dy, sums = {sum dy', sum dy' * xhat}
   extern __shared__ float sm[];  // [2][lanes][C]
   const int c8 = C / 8, lanes = 256 / c8;
@@ -821,6 +830,8 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_reduce_kernel(const T* __restri
                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                double* __restrict__ sums, int relu, long long M, int C,
                                                                long long rows_per_block) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   extern __shared__ float sm[];  // [2][lanes][C]
   const int c8 = C / 8, lanes = 256 / c8;
   const int g = threadIdx.x % c8, rl = threadIdx.x / c8;
@@ -872,7 +883,7 @@ static inline long long bn_rows_per_block(long long M) { return max((long long)3
 template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
   const long long rpb = bn_rows_per_block(M);
-  bn_reduce_kernel<T, false><<<cdiv(M, rpb), 256, 2 * 2048 * sizeof(float), st>>>(x, nullptr, nullptr, nullptr, nullptr, nullptr, stats, 0, M, C, rpb);
+  S4G_CUDA(launch_dep(bn_reduce_kernel<T, false>, dim3(cdiv(M, rpb)), dim3(256), 2 * 2048 * sizeof(float), st, x, nullptr, nullptr, nullptr, nullptr, nullptr, stats, 0, M, C, rpb));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -881,12 +892,14 @@ int k_bn_bwd_reduce(const T* dy, const T* x, const float* mean, const float* rst
                     const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
   const long long rpb = bn_rows_per_block(M);
-  bn_bwd_reduce_kernel<T><<<cdiv(M, rpb), 256, 2 * 2048 * sizeof(float), st>>>(dy, x, mean, rstd, gamma, beta, sums, relu, M, C, rpb);
+  S4G_CUDA(launch_dep(bn_bwd_reduce_kernel<T>, dim3(cdiv(M, rpb)), dim3(256), 2 * 2048 * sizeof(float), st, dy, x, mean, rstd, gamma, beta, sums, relu, M, C, rpb));
   S4G_KERNEL_CHECK();
   return 0;
 }
 __global__ void bn_finalize_kernel(const double* __restrict__ stats, double count, float* mean, float* rstd,
                                    float* running_mean, float* running_var, long long* nbt, float momentum, float eps, int C) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const double mu = stats[c] / count;
@@ -903,7 +916,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ stats, double coun
 }
 int k_bn_finalize(const double* stats, double count, float* mean, float* rstd, float* running_mean, float* running_var,
                   long long* nbt, float momentum, float eps, int C, cudaStream_t st) {
-  bn_finalize_kernel<<<cdiv(C, 256), 256, 0, st>>>(stats, count, mean, rstd, running_mean, running_var, nbt, momentum, eps, C);
+  S4G_CUDA(launch_dep(bn_finalize_kernel, dim3(cdiv(C, 256)), dim3(256), 0, st, stats, count, mean, rstd, running_mean, running_var, nbt, momentum, eps, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1082,6 +1095,8 @@ __global__ void __launch_bounds__(256, 2) seghead_fwd_kernel(const T* __restrict
                                                              const float* __restrict__ beta, const float* __restrict__ w,
                                                              const float* __restrict__ b, const uint8_t* __restrict__ mask,
                                                              float p, uint64_t seed, float* __restrict__ small, long long M) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   float sc[8], sh[8], wv[8];
 #pragma unroll
@@ -1117,7 +1132,7 @@ int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float*
                   const float* w, const float* b, const uint8_t* mask, float p, uint64_t seed, float* small,
                   long long M, int C, cudaStream_t st) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
-  seghead_fwd_kernel<T><<<(unsigned)min((long long)cdiv(M, 8), (long long)148 * 16), 256, 0, st>>>(x, mean, rstd, gamma, beta, w, b, mask, p, seed, small, M);
+  S4G_CUDA(launch_dep(seghead_fwd_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 16)), dim3(256), 0, st, x, mean, rstd, gamma, beta, w, b, mask, p, seed, small, M));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1130,6 +1145,8 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_reduce_kernel(const float*
                                                                     const float* __restrict__ w, const uint8_t* __restrict__ mask,
                                                                     float p, uint64_t seed, double* __restrict__ sums,
                                                                     float* __restrict__ dw, float* __restrict__ db, long long M) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   __shared__ float sm[3][8][256];
   __shared__ float sdb[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1189,7 +1206,7 @@ int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, con
                          const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
                          float* dw, float* db, long long M, int C, cudaStream_t st) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
-  seghead_bwd_reduce_kernel<T><<<(unsigned)min((long long)cdiv(M, 8), (long long)148 * 4), 256, 0, st>>>(dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, dw, db, M);
+  S4G_CUDA(launch_dep(seghead_bwd_reduce_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 4)), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, dw, db, M));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1201,7 +1218,8 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_apply_kernel(const float* 
                                                                    float p, uint64_t seed, const double* __restrict__ sums,
                                                                    double count, T* __restrict__ dx, float* dgamma, float* dbeta,
                                                                    long long M) {
-  pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   if (blockIdx.x == 0) {  // global sums / world under SyncBatchNorm, see bn_bwd_apply_kernel
     const double gs = (double)M / count;
@@ -1255,7 +1273,7 @@ int k_seghead_bwd_apply(const float* dsmall, const T* x, const float* mean, cons
                         const double* sums, double count, T* dx, float* dgamma, float* dbeta, long long M, int C,
                         cudaStream_t st) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
-  seghead_bwd_apply_kernel<T><<<(unsigned)min((long long)cdiv(M, 8), (long long)148 * 16), 256, 0, st>>>(dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, count, dx, dgamma, dbeta, M);
+  S4G_CUDA(launch_dep(seghead_bwd_apply_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 16)), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, count, dx, dgamma, dbeta, M));
   S4G_KERNEL_CHECK();
   return 0;
 }
