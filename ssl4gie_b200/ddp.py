@@ -48,7 +48,7 @@ class GradientAllReduce:
         self.engine.enable_direct_grads()
         self.group = process_group
         self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
-        self.n_buckets = n_buckets
+        self.n_buckets = int(os.environ.get("S4G_DDP_BUCKETS", n_buckets))
         self.overlap = os.environ.get("S4G_DDP_OVERLAP", "1") != "0"
         self.comm_stream = None
         self.slices = None
