@@ -20,3 +20,13 @@ def test_syncbn_peer_exchange_two_ranks():
            "--master-port", "29541", os.path.join(ROOT, "scripts", "check_syncbn_n2.py")]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "CHECK_SYNCBN_N2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_train_epoch_two_ranks():
+    """train_epoch with SyncBatchNorm + GradientAllReduce + FusedAdamW(grad_scale = 1/world): same epoch loss on every
+    rank, replicas bit-identical after 12 steps, loss falling (scripts/check_train_n2.py)."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29542", os.path.join(ROOT, "scripts", "check_train_n2.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CHECK_TRAIN_N2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
