@@ -90,8 +90,8 @@ typedef int (*s4g_allreduce_fn)(void* user, void* device_doubles, int count, voi
 int s4g_model_set_allreduce(S4GModel* m, s4g_allreduce_fn fn, void* user);
 /* The same cross-rank sum without the host callback: a one-CTA kernel that exchanges the statistic vector through
  * NVLink peer memory (P2P stores into every rank's mailbox + system-scope flags; csrc/peer.cu).  Replaces the NCCL
- * all_gather / all_reduce pair inside torch.nn.SyncBatchNorm (train_segmentation.py:199).  Every rank allocates one
- * mailbox per model handle (s4g_peer_alloc: zero-filled device memory + a 64-byte cudaIpc handle to send to the peers
+ * all_gather / all_reduce pair inside torch.nn.SyncBatchNorm (train_segmentation.py:199).  Every rank allocates ONE
+ * mailbox per process group, shared by all of its model handles (s4g_peer_alloc: zero-filled device memory + a 64-byte cudaIpc handle to send to the peers
  * by any host channel), opens the peers' (s4g_peer_open), and passes the `world` device pointers in rank order
  * (mailboxes[rank] = its own).  All ranks must have set the pointers (host barrier) before the first forward. */
 #define S4G_PEER_MAX_WORLD 8
@@ -102,10 +102,13 @@ int s4g_peer_open(const unsigned char handle[S4G_PEER_HANDLE_BYTES], void** dptr
 int s4g_peer_close(void* dptr);
 int s4g_peer_free(void* dptr);
 int s4g_model_set_peer_exchange(S4GModel* m, void* const* mailboxes, int rank, int world);
-/* Stand-alone exchange (tests): in-place sum over ranks of `count` <= 512 doubles; `seq` counts the exchanges made
- * through these mailboxes so far (0, 1, 2, ... identically on every rank). */
-int s4g_peer_sum_f64(double* data, int count, void* const* mailboxes, int rank, int world, unsigned long long seq,
-                     void* stream);
+/* Stand-alone exchange (tests): in-place sum over ranks of `count` <= 512 doubles.  The exchange counter lives in the
+ * rank's own mailbox (device memory), so every handle sharing the mailboxes stays in step and the launch is
+ * CUDA-graph replayable. */
+int s4g_peer_sum_f64(double* data, int count, void* const* mailboxes, int rank, int world, void* stream);
+/* Synchronises the device and reports a peer that did not answer within S4G_PEER_TIMEOUT_S (default 600 s):
+ * 0 = healthy, S4G_ERR_STATE + s4g_last_error() otherwise (the exchange kernel flags the time-out, it never traps). */
+int s4g_peer_check(void* own_mailbox);
 /* Gradient-bucket boundaries for overlapping the data-parallel all-reduce with backward (DDP reducer,
  * train_segmentation.py:203).  The library records events[i] (cudaEvent_t) on `stream` during backward once every
  * parameter gradient of bucket i is final: bucket 0 = DPT decoder, buckets 1..n-1 = encoder blocks from the last
@@ -156,11 +159,12 @@ int s4g_dice_fwd(const float* logits, const float* targets, void* scratch, float
                  void* stream);
 int s4g_dice_bwd(const float* logits, const float* targets, const void* scratch, const float* grad_out,
                  float* dlogits, int B, int HW, float smooth, void* stream);
-/* ScaleAndShiftInvariantLoss.forward (Depth_estimation/Metrics/losses.py:130-146), batch-based reduction.
- * ssi_out: optional [B,H,W] prediction_ssi (losses.py:138,148-151). */
+/* ScaleAndShiftInvariantLoss.forward (Depth_estimation/Metrics/losses.py:130-146); image_based = 0:
+ * reduction_batch_based (:28-37), else reduction_image_based (:40-48); scales <= 8.
+ * ssi_out: optional [B,H,W] prediction_ssi (losses.py:138,148-151).  All sums are two-stage, fixed-order (no atomics). */
 size_t s4g_ssi_scratch_bytes(int B);
 int s4g_ssi_fwd(const float* pred, const float* target, void* scratch, float* loss, float* ssi_out, int B, int H,
-                int W, float alpha, int scales, void* stream);
+                int W, float alpha, int scales, int image_based, void* stream);
 int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const float* grad_out, float* dpred, int B,
                 int H, int W, float alpha, int scales, void* stream);
 /* nn.CrossEntropyLoss(weight) of the classification fine-tune (Classification/train_classification.py:278):

@@ -183,6 +183,28 @@ def loss_kats():
     kat["ssi_rand_loss"] = loss.item()
     kat["ssi_rand_grad_norm"] = pp.grad.double().norm().item()
     kat["ssi_rand_grad_head"] = pp.grad.flatten()[:16].tolist()
+    # reduction="image-based" (losses.py:40-48) and more than four scales, same random case and a 64 x 64 one
+    for tag, pq, tq, kw in (("img", p, t, dict(alpha=0.1, reduction="image-based")),
+                            ("img_a0", p, t, dict(alpha=0.0, reduction="image-based"))):
+        pp = pq.clone().requires_grad_(True)
+        loss = depth_losses.ScaleAndShiftInvariantLoss(**kw)(pp, tq)
+        loss.backward()
+        kat[f"ssi_{tag}_loss"] = loss.item()
+        kat[f"ssi_{tag}_grad_norm"] = pp.grad.double().norm().item()
+        kat[f"ssi_{tag}_grad_head"] = pp.grad.flatten()[:16].tolist()
+    g = torch.Generator().manual_seed(4)
+    p6 = torch.rand(2, 1, 64, 64, generator=g)
+    t6 = torch.rand(2, 1, 64, 64, generator=g)
+    t6[torch.rand(2, 1, 64, 64, generator=g) < 0.15] = 0
+    for tag, kw in (("s6", dict(alpha=0.25, scales=6)), ("s5_img", dict(alpha=0.25, scales=5, reduction="image-based"))):
+        pp = p6.clone().requires_grad_(True)
+        loss = depth_losses.ScaleAndShiftInvariantLoss(**kw)(pp, t6)
+        loss.backward()
+        kat[f"ssi_{tag}_loss"] = loss.item()
+        kat[f"ssi_{tag}_grad_norm"] = pp.grad.double().norm().item()
+        kat[f"ssi_{tag}_grad_head"] = pp.grad.flatten()[:16].tolist()
+        l4 = ref_port.ssi_loss(p6, t6, kw["alpha"], kw["scales"], reduction=kw.get("reduction", "batch-based"))
+        assert abs(l4.item() - loss.item()) < 1e-7, (tag, l4.item(), loss.item())
     with open(os.path.join(OUT, "loss_kats.json"), "w") as f:
         json.dump(kat, f)
     # restatement agrees
@@ -225,6 +247,8 @@ if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(os.cpu_count())
     loss_kats()
+    if "--kats-only" in sys.argv:
+        sys.exit(0)
     if "--cls-only" not in sys.argv:
         run("seg")
         run("depth")

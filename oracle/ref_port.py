@@ -207,7 +207,15 @@ def _reduction_batch_based(image_loss, M):
     return torch.sum(image_loss) / divisor
 
 
-def _gradient_loss(prediction, target, mask):
+def _reduction_image_based(image_loss, M):
+    """Depth_estimation/Metrics/losses.py:40-48: mean over images of (image term / image mask count)."""
+    valid = M.nonzero()
+    image_loss = image_loss.clone()
+    image_loss[valid] = image_loss[valid] / M[valid]
+    return torch.mean(image_loss)
+
+
+def _gradient_loss(prediction, target, mask, reduction=_reduction_batch_based):
     """Depth_estimation/Metrics/losses.py:60-77."""
     M = torch.sum(mask, (1, 2))
     diff = torch.mul(mask, prediction - target)
@@ -216,11 +224,13 @@ def _gradient_loss(prediction, target, mask):
     grad_y = torch.abs(diff[:, 1:, :] - diff[:, :-1, :])
     grad_y = torch.mul(torch.mul(mask[:, 1:, :], mask[:, :-1, :]), grad_y)
     image_loss = torch.sum(grad_x, (1, 2)) + torch.sum(grad_y, (1, 2))
-    return _reduction_batch_based(image_loss, M)
+    return reduction(image_loss, M)
 
 
-def ssi_loss(prediction, target, alpha=0.5, scales=4, return_ssi=False):
-    """ScaleAndShiftInvariantLoss.forward, Depth_estimation/Metrics/losses.py:130-146."""
+def ssi_loss(prediction, target, alpha=0.5, scales=4, return_ssi=False, reduction="batch-based"):
+    """ScaleAndShiftInvariantLoss.forward, Depth_estimation/Metrics/losses.py:130-146; `reduction` selects the
+    reduction function the way MSELoss / GradientLoss do (:82-85, :99-102)."""
+    red = _reduction_batch_based if reduction == "batch-based" else _reduction_image_based
     prediction = prediction.squeeze(1)
     target = target.squeeze(1)
     mask = target > 0
@@ -228,12 +238,12 @@ def ssi_loss(prediction, target, alpha=0.5, scales=4, return_ssi=False):
     ssi = scale.view(-1, 1, 1) * prediction + shift.view(-1, 1, 1)
     M = torch.sum(mask, (1, 2))
     res = ssi - target
-    total = _reduction_batch_based(torch.sum(mask * res * res, (1, 2)), 2 * M)  # mse_loss :51-57
+    total = red(torch.sum(mask * res * res, (1, 2)), 2 * M)  # mse_loss :51-57
     if alpha > 0:
         reg = 0
         for s in range(scales):  # GradientLoss.forward :104-117
             step = 2 ** s
-            reg = reg + _gradient_loss(ssi[:, ::step, ::step], target[:, ::step, ::step], mask[:, ::step, ::step])
+            reg = reg + _gradient_loss(ssi[:, ::step, ::step], target[:, ::step, ::step], mask[:, ::step, ::step], red)
         total = total + alpha * reg
     return (total, ssi) if return_ssi else total
 

@@ -38,7 +38,7 @@ def main():
         v = torch.randn(n, dtype=torch.float64, device="cuda", generator=g)
         ref = v.clone()
         dist.all_reduce(ref)
-        _C.check(lib.s4g_peer_sum_f64(_C.ptr(v), n, boxes.ptrs, rank, world, seq, _C.stream_ptr()))
+        _C.check(lib.s4g_peer_sum_f64(_C.ptr(v), n, boxes.ptrs, rank, world, _C.stream_ptr()))
         worst = max(worst, (v - ref).abs().max().item())
         # bit-identical on every rank (fixed summation order)
         other = [torch.empty_like(v) for _ in range(world)]

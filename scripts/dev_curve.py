@@ -1,17 +1,19 @@
-"""Developer diagnostic: per-step deviation of the 200-step loss curve (bf16 product vs fp32 oracle), run twice."""
+"""Developer diagnostic: per-step deviation of the 200-step loss curve (bf16 product vs fp32 oracle).
+Usage: python scripts/dev_curve.py [seg|depth|cls ...]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from tests import test_gpu_train as T
 from oracle import ref_port
-sd = ref_port.make_state("seg", seed=42)
-x, t = T._data("seg", 4)
-ref = T._curve_oracle("seg", sd, x, t)
-a = T._curve_ours("seg", sd, x, t, "bf16")
-b = T._curve_ours("seg", sd, x, t, "bf16")
-da = ((a - ref).abs() / ref.abs())
-db = ((b - ref).abs() / ref.abs())
-print("max dev run1 %.4f at %d, run2 %.4f at %d, run1-vs-run2 %.4f" % (da.max(), da.argmax(), db.max(), db.argmax(), ((a - b).abs() / ref.abs()).max()))
-print("dev first 30:", [round(v, 4) for v in da[:30].tolist()])
-print("ref first 12:", [round(v, 4) for v in ref[:12].tolist()])
-print("ours first 12:", [round(v, 4) for v in a[:12].tolist()])
+for task in (sys.argv[1:] or ["seg"]):
+    sd = ref_port.make_state(None, seed=42, head_classes=23) if task == "cls" else ref_port.make_state(task, seed=42)
+    x, t = T._data(task, 4)
+    ref = T._curve_oracle(task, sd, x, t)
+    a = T._curve_ours(task, sd, x, t, "bf16")
+    b = T._curve_ours(task, sd, x, t, "bf16")
+    scale = torch.maximum(ref.abs(), 0.05 * ref[0].abs()) if task == "cls" else ref.abs()
+    da = (a - ref).abs() / scale
+    print("%s: max dev %.4f at %d (first 100: %.4f), run1 == run2: %s" % (task, da.max(), da.argmax(), da[:100].max(), torch.equal(a, b)))
+    print("  dev every 10:", [round(v, 4) for v in da[::10].tolist()])
+    print("  ref every 20:", [round(v, 5) for v in ref[::20].tolist()])
+    print("  ours every 20:", [round(v, 5) for v in a[::20].tolist()])

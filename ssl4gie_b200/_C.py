@@ -40,7 +40,8 @@ SIGNATURES = {
     "s4g_peer_close": (_i, [_vp]),
     "s4g_peer_free": (_i, [_vp]),
     "s4g_model_set_peer_exchange": (_i, [_vp, ctypes.POINTER(_vp), _i, _i]),
-    "s4g_peer_sum_f64": (_i, [_vp, _i, ctypes.POINTER(_vp), _i, _i, _u64, _vp]),
+    "s4g_peer_sum_f64": (_i, [_vp, _i, ctypes.POINTER(_vp), _i, _i, _vp]),
+    "s4g_peer_check": (_i, [_vp]),
     "s4g_model_set_bucket_events": (_i, [_vp, ctypes.POINTER(_vp), _i]),
     "s4g_model_bucket_params": (ctypes.c_char_p, [_vp, _i, _i]),
     "s4g_model_last_launches": (_i, [_vp]),
@@ -59,7 +60,7 @@ SIGNATURES = {
     "s4g_dice_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "s4g_dice_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "s4g_ssi_scratch_bytes": (_sz, [_i]),
-    "s4g_ssi_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp]),
+    "s4g_ssi_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _i, _vp]),
     "s4g_ssi_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _i, _vp]),
     "s4g_ce_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "s4g_ce_bwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),

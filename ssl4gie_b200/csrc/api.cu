@@ -35,6 +35,7 @@ int s4g_init(int device) {
     return S4G_ERR_ARCH;
   }
   S4G_CUDA(cudaSetDevice(device));
+  S4G_TRY(reduce_init());   // the only device allocation the library ever makes: 32 MB of reduction scratch per device
   return umma_init();
 }
 
@@ -90,8 +91,6 @@ int s4g_layernorm_fwd(const float* x, const float* gamma, const float* beta, voi
 }
 int s4g_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                       const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, int dtype, void* stream) {
-  S4G_CUDA(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, ST(stream)));
-  S4G_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, ST(stream)));
   DISPATCH(dtype, k_layernorm_bwd<T>((const T*)dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, C, ST(stream)),
            k_layernorm_bwd<T>((const T*)dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, C, ST(stream)));
 }
@@ -113,7 +112,7 @@ int s4g_bilinear2x_fwd(const void* x, void* y, int B, int H, int W, int C, int d
 int s4g_bilinear2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, int dtype, void* stream) {
   DISPATCH(dtype, k_bilinear2x_bwd<T>((const T*)dy, (T*)dx, B, H, W, C, ST(stream)), k_bilinear2x_bwd<T>((const T*)dy, (T*)dx, B, H, W, C, ST(stream)));
 }
-size_t s4g_dice_scratch_bytes(int B) { return sizeof(double) * 3 * (size_t)B; }
+size_t s4g_dice_scratch_bytes(int B) { return sizeof(double) * dice_scratch_doubles(B); }
 int s4g_dice_fwd(const float* logits, const float* targets, void* scratch, float* loss, int B, int HW, float smooth, void* stream) {
   return k_dice_fwd(logits, targets, (float*)scratch, loss, B, HW, smooth, ST(stream));
 }
@@ -123,8 +122,8 @@ int s4g_dice_bwd(const float* logits, const float* targets, const void* scratch,
 }
 size_t s4g_ssi_scratch_bytes(int B) { return sizeof(float) * ssi_scratch_floats(B); }
 int s4g_ssi_fwd(const float* pred, const float* target, void* scratch, float* loss, float* ssi_out, int B, int H, int W,
-                float alpha, int scales, void* stream) {
-  return k_ssi_fwd(pred, target, (float*)scratch, loss, ssi_out, B, H, W, alpha, scales, ST(stream));
+                float alpha, int scales, int image_based, void* stream) {
+  return k_ssi_fwd(pred, target, (float*)scratch, loss, ssi_out, B, H, W, alpha, scales, image_based, ST(stream));
 }
 int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const float* grad_out, float* dpred, int B, int H,
                 int W, float alpha, int scales, void* stream) {
@@ -164,9 +163,21 @@ int s4g_peer_open(const unsigned char handle[S4G_PEER_HANDLE_BYTES], void** dptr
 }
 int s4g_peer_close(void* dptr) { S4G_CUDA(cudaIpcCloseMemHandle(dptr)); return 0; }
 int s4g_peer_free(void* dptr) { S4G_CUDA(cudaFree(dptr)); return 0; }
-int s4g_peer_sum_f64(double* data, int count, void* const* mailboxes, int rank, int world, unsigned long long seq,
-                     void* stream) {
-  return k_peer_sum_f64(data, count, mailboxes, rank, world, seq, ST(stream));
+int s4g_peer_sum_f64(double* data, int count, void* const* mailboxes, int rank, int world, void* stream) {
+  return k_peer_sum_f64(data, count, mailboxes, rank, world, ST(stream));
+}
+int s4g_peer_check(void* own_mailbox) {
+  if (!own_mailbox) { s4g_set_error("peer_check: null mailbox"); return S4G_ERR_STATE; }
+  unsigned long long ctl[2] = {0, 0};
+  S4G_CUDA(cudaDeviceSynchronize());
+  S4G_CUDA(cudaMemcpy(ctl, reinterpret_cast<char*>(own_mailbox) + k_peer_ctl_offset(), sizeof(ctl), cudaMemcpyDeviceToHost));
+  if (ctl[1]) {
+    char buf[160];
+    snprintf(buf, sizeof(buf), "peer exchange %llu timed out waiting for rank %d (S4G_PEER_TIMEOUT_S)", ctl[1] >> 8, (int)(ctl[1] & 255) - 1);
+    s4g_set_error(buf);
+    return S4G_ERR_STATE;
+  }
+  return 0;
 }
 
 }  // extern "C"

@@ -138,22 +138,19 @@ int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y,
 // LayerNorm backward, one warp per token row: lane l owns columns 4l + 128i (i < C/128) of every row its warp visits, so
 // the three column accumulators (dgamma, dbeta, and the column sum of the produced dx = bias gradient of the Linear that
 // precedes this residual branch) stay in registers across rows, the two per-row reductions are warp shuffles, and there
-// is no block barrier inside the row loop.  At the end the warps of a block combine in shared memory and issue one
-// global atomic per column.
+// is no block barrier inside the row loop.  At the end the warps of a block combine in shared memory in warp order and
+// the block writes ONE partial row [3][C]; finalize (reduce.cu) sums the rows in a fixed order -- no atomics.
 template <typename T, int C>
 __global__ void __launch_bounds__(256, 1) layernorm_bwd_kernel(const T* __restrict__ dy, const float* __restrict__ x,
                                                                const float* __restrict__ gamma,
                                                                const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                const float* __restrict__ dres, float* __restrict__ dx,
-                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                               int rows, T* __restrict__ dx_cast, float* __restrict__ dxsum) {
+                                                               float* __restrict__ part, int rows, T* __restrict__ dx_cast) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   constexpr int V = C / 128;
   __shared__ float red[3][C];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int c = threadIdx.x; c < 3 * C; c += 256) (&red[0][0])[c] = 0.f;
-  __syncthreads();
   float4 gm[V], ag[V], ab[V], ac[V];
 #pragma unroll
   for (int i = 0; i < V; ++i) {
@@ -192,32 +189,54 @@ __global__ void __launch_bounds__(256, 1) layernorm_bwd_kernel(const T* __restri
       ac[i].x += r.x; ac[i].y += r.y; ac[i].z += r.z; ac[i].w += r.w;
     }
   }
+  // warps add their register sums into the block's row one after the other (warp 0 stores, 1..7 accumulate)
+  for (int w = 0; w < 8; ++w) {
+    if (warp == w) {
 #pragma unroll
-  for (int i = 0; i < V; ++i) {
-    const int c = (lane + 32 * i) * 4;
-    atomicAdd(&red[0][c], ag[i].x); atomicAdd(&red[0][c + 1], ag[i].y); atomicAdd(&red[0][c + 2], ag[i].z); atomicAdd(&red[0][c + 3], ag[i].w);
-    atomicAdd(&red[1][c], ab[i].x); atomicAdd(&red[1][c + 1], ab[i].y); atomicAdd(&red[1][c + 2], ab[i].z); atomicAdd(&red[1][c + 3], ab[i].w);
-    atomicAdd(&red[2][c], ac[i].x); atomicAdd(&red[2][c + 1], ac[i].y); atomicAdd(&red[2][c + 2], ac[i].z); atomicAdd(&red[2][c + 3], ac[i].w);
+      for (int i = 0; i < V; ++i) {
+        float4* r0 = reinterpret_cast<float4*>(&red[0][0]) + lane + 32 * i;
+        float4* r1 = reinterpret_cast<float4*>(&red[1][0]) + lane + 32 * i;
+        float4* r2 = reinterpret_cast<float4*>(&red[2][0]) + lane + 32 * i;
+        if (w == 0) { *r0 = ag[i]; *r1 = ab[i]; *r2 = ac[i]; }
+        else {
+          float4 t = *r0; t.x += ag[i].x; t.y += ag[i].y; t.z += ag[i].z; t.w += ag[i].w; *r0 = t;
+          t = *r1; t.x += ab[i].x; t.y += ab[i].y; t.z += ab[i].z; t.w += ab[i].w; *r1 = t;
+          t = *r2; t.x += ac[i].x; t.y += ac[i].y; t.z += ac[i].z; t.w += ac[i].w; *r2 = t;
+        }
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
-  for (int c = threadIdx.x; c < C; c += 256) {
-    atomicAdd(&dgamma[c], red[0][c]);
-    atomicAdd(&dbeta[c], red[1][c]);
-    if (dxsum) atomicAdd(&dxsum[c], red[2][c]);
-  }
+  float* prow = part + (size_t)blockIdx.x * 3 * C;
+  for (int c = threadIdx.x; c < 3 * C; c += 256) prow[c] = (&red[0][0])[c];
 }
 template <typename T>
 int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                     const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st, T* dx_cast,
-                    float* dxsum) {
+                    float* dxsum, const Reducer* red) {
   const int grid = std::min(cdiv(rows, 8), 148);
+  float* part = reinterpret_cast<float*>(reduce_scratch(red, ln_bwd_scratch_bytes(C)));
+  if (!part) return S4G_ERR_WORKSPACE;
   if (C == 768)
-    S4G_CUDA(launch_dep(layernorm_bwd_kernel<T, 768>, dim3(grid), dim3(256), 0, st, dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum));
+    S4G_CUDA(launch_dep(layernorm_bwd_kernel<T, 768>, dim3(grid), dim3(256), 0, st, dy, x, gamma, mean, rstd, dres, dx, part, rows, dx_cast));
   else if (C == 512)
-    S4G_CUDA(launch_dep(layernorm_bwd_kernel<T, 512>, dim3(grid), dim3(256), 0, st, dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, rows, dx_cast, dxsum));
+    S4G_CUDA(launch_dep(layernorm_bwd_kernel<T, 512>, dim3(grid), dim3(256), 0, st, dy, x, gamma, mean, rstd, dres, dx, part, rows, dx_cast));
   else { s4g_set_error("layernorm: C must be 768 or 512"); return S4G_ERR_SHAPE; }
   S4G_KERNEL_CHECK();
-  return 0;
+  // three outputs of one partial matrix [grid][3*C]; queued jobs of one producer stay together (library scratch: the
+  // three combines are launched one after the other before anything else touches the scratch)
+  if (red && red->scratch && red->defer) {
+    S4G_TRY(k_finalize(red, part, dgamma, grid, C, 3 * C, 0, 0, st));
+    S4G_TRY(k_finalize(red, part + C, dbeta, grid, C, 3 * C, 0, 0, st));
+    if (dxsum) S4G_TRY(k_finalize(red, part + 2 * C, dxsum, grid, C, 3 * C, 0, 0, st));
+    return 0;
+  }
+  FinalizeJobs q; q.n = 0; q.total_blocks = 0; q.launches = 0;
+  Reducer rq; rq.scratch = part; rq.scratch_bytes = ln_bwd_scratch_bytes(C); rq.defer = &q;
+  S4G_TRY(k_finalize(&rq, part, dgamma, grid, C, 3 * C, 0, 0, st));
+  S4G_TRY(k_finalize(&rq, part + C, dbeta, grid, C, 3 * C, 0, 0, st));
+  if (dxsum) S4G_TRY(k_finalize(&rq, part + 2 * C, dxsum, grid, C, 3 * C, 0, 0, st));
+  return k_finalize_flush(&q, st);
 }
 
 // ------------------------------------------------------------------------------------------ small elementwise
@@ -244,7 +263,7 @@ template <typename T> __global__ void __launch_bounds__(256) dgelu_mul_kernel(co
 // 77 MB tensor that a separate column-sum launch would make disappears.
 template <typename T>
 __global__ void __launch_bounds__(256, 3) dgelu_mul_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ u, T* __restrict__ out,
-                                                               float* __restrict__ colsum, long long M, int N, long long rows_per_block) {
+                                                               float* __restrict__ part, long long M, int N, long long rows_per_block) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   __shared__ float red[8][256 + 8];
@@ -284,16 +303,20 @@ __global__ void __launch_bounds__(256, 3) dgelu_mul_colsum_kernel(const T* __res
     float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
-    atomicAdd(&colsum[c], t);
+    part[(size_t)blockIdx.y * N + c] = t;   // one partial row per row block; finalize (reduce.cu) sums them in order
   }
 }
-// colsum (optional, zeroed by the caller): [N] column sums of the result for an [n / N, N] matrix
-template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum, int N) {
+// colsum (optional, overwritten): [N] column sums of the result for an [n / N, N] matrix
+template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum, int N, const Reducer* red) {
   if (colsum && N % 8 == 0 && n % N == 0) {
     const long long M = n / N;
     // 3 resident blocks per SM (launch bound above): one wave of 148 * 3 blocks
     const int rblocks = (int)std::max<long long>(1, std::min<long long>(cdiv(M, 64), (148 * 3) / cdiv(N, 256)));
-    S4G_CUDA(launch_dep(dgelu_mul_colsum_kernel<T>, dim3(dim3(cdiv(N, 256), rblocks)), dim3(256), 0, st, dy, u, out, colsum, M, N, cdiv(M, rblocks)));
+    float* part = reinterpret_cast<float*>(reduce_scratch(red, colsum_scratch_bytes(N)));
+    if (!part) return S4G_ERR_WORKSPACE;
+    S4G_CUDA(launch_dep(dgelu_mul_colsum_kernel<T>, dim3(dim3(cdiv(N, 256), rblocks)), dim3(256), 0, st, dy, u, out, part, M, N, cdiv(M, rblocks)));
+    S4G_KERNEL_CHECK();
+    return k_finalize(red, part, colsum, rblocks, N, N, 0, 0, st);
   } else {
     if (colsum) { s4g_set_error("dgelu_mul: bad column-sum shape"); return S4G_ERR_SHAPE; }
     dgelu_mul_kernel<T><<<GRID1D(n / 16, 256), 0, st>>>(dy, u, out, n / 8);
@@ -326,9 +349,9 @@ template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t s
   return 0;
 }
 
-// column sums of a [M, N] matrix (bias gradients); out must be zeroed.  Block = 32 column groups (8 columns, one
-// 16 B load each) x 8 row lanes, rows walked with a 4-deep unroll; one atomic per column per block.
-template <typename T> __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, float* __restrict__ out, long long M, int N, int ld, long long rows_per_block) {
+// column sums of a [M, N] matrix (bias gradients).  Block = 32 column groups (8 columns, one 16 B load each) x 8 row
+// lanes, rows walked with a 4-deep unroll; one partial row per row block, summed in order by finalize (reduce.cu).
+template <typename T> __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ dy, float* __restrict__ part, long long M, int N, int ld, long long rows_per_block) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   __shared__ float red[8][256 + 8];
@@ -364,18 +387,20 @@ template <typename T> __global__ void __launch_bounds__(256) colsum_kernel(const
     float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
-    atomicAdd(&out[c], t);
+    part[(size_t)blockIdx.y * N + c] = t;
   }
 }
-template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st) {
+template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st, const Reducer* red) {
   if (N % 8 || ld % 8) { s4g_set_error("colsum: N and ld must be multiples of 8"); return S4G_ERR_SHAPE; }
   const int gx = cdiv(N, 256);
   const long long want = std::max<long long>(1, (148 * 4) / gx);
   const long long rpb = std::max<long long>(64, (M + want - 1) / want);
   dim3 grid(gx, cdiv(M, rpb));
-  S4G_CUDA(launch_dep(colsum_kernel<T>, dim3(grid), dim3(256), 0, st, dy, out, M, N, ld, rpb));
+  float* part = reinterpret_cast<float*>(reduce_scratch(red, colsum_scratch_bytes(N)));
+  if (!part) return S4G_ERR_WORKSPACE;
+  S4G_CUDA(launch_dep(colsum_kernel<T>, dim3(grid), dim3(256), 0, st, dy, part, M, N, ld, rpb));
   S4G_KERNEL_CHECK();
-  return 0;
+  return k_finalize(red, part, out, (int)grid.y, N, N, 0, 0, st);
 }
 
 // Slice(1)+Transpose+Unflatten (Models/DPT_decoder.py:503-515): token rows 1..196 ARE the NHWC map
@@ -818,7 +843,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const T* __restrict__ a,
     const int which = c / C, ch = c % C;
     double s = 0.0;
     for (int l = 0; l < lanes; ++l) s += (double)sm[(size_t)(which * lanes + l) * C + ch];
-    atomicAdd(&sums[which * C + ch], s);
+    sums[(size_t)blockIdx.x * 2 * C + which * C + ch] = s;   // partial row of this block (finalize sums the rows in order)
   }
 }
 // backward sums {sum dy', sum dy' * xhat}: a thread accumulates sum dy' and sum dy' * x for its 8 channels (only the
@@ -875,26 +900,33 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_reduce_kernel(const T* __restri
   for (int c = threadIdx.x; c < C; c += 256) {
     double a = 0.0, b = 0.0;
     for (int l = 0; l < lanes; ++l) { a += (double)sm[(size_t)l * C + c]; b += (double)sm[(size_t)(lanes + l) * C + c]; }
-    atomicAdd(&sums[c], a);
-    atomicAdd(&sums[C + c], (b - (double)mean[c] * a) * (double)rstd[c]);
+    double* prow = sums + (size_t)blockIdx.x * 2 * C;   // partial row of this block
+    prow[c] = a;
+    prow[C + c] = (b - (double)mean[c] * a) * (double)rstd[c];
   }
 }
 static inline long long bn_rows_per_block(long long M) { return max((long long)32, (M + 148 * 4 - 1) / (148 * 4)); }
-template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st) {
+template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st, const Reducer* red) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
   const long long rpb = bn_rows_per_block(M);
-  S4G_CUDA(launch_dep(bn_reduce_kernel<T, false>, dim3(cdiv(M, rpb)), dim3(256), 2 * 2048 * sizeof(float), st, x, nullptr, nullptr, nullptr, nullptr, nullptr, stats, 0, M, C, rpb));
+  const int nb = cdiv(M, rpb);
+  double* part = reinterpret_cast<double*>(reduce_scratch(red, bn_scratch_bytes(C)));
+  if (!part) return S4G_ERR_WORKSPACE;
+  S4G_CUDA(launch_dep(bn_reduce_kernel<T, false>, dim3(nb), dim3(256), 2 * 2048 * sizeof(float), st, x, nullptr, nullptr, nullptr, nullptr, nullptr, part, 0, M, C, rpb));
   S4G_KERNEL_CHECK();
-  return 0;
+  return k_finalize(red, part, stats, nb, 2 * C, 2 * C, 1, 1, st);
 }
 template <typename T>
 int k_bn_bwd_reduce(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma,
-                    const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st) {
+                    const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st, const Reducer* red) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
   const long long rpb = bn_rows_per_block(M);
-  S4G_CUDA(launch_dep(bn_bwd_reduce_kernel<T>, dim3(cdiv(M, rpb)), dim3(256), 2 * 2048 * sizeof(float), st, dy, x, mean, rstd, gamma, beta, sums, relu, M, C, rpb));
+  const int nb = cdiv(M, rpb);
+  double* part = reinterpret_cast<double*>(reduce_scratch(red, bn_scratch_bytes(C)));
+  if (!part) return S4G_ERR_WORKSPACE;
+  S4G_CUDA(launch_dep(bn_bwd_reduce_kernel<T>, dim3(nb), dim3(256), 2 * 2048 * sizeof(float), st, dy, x, mean, rstd, gamma, beta, part, relu, M, C, rpb));
   S4G_KERNEL_CHECK();
-  return 0;
+  return k_finalize(red, part, sums, nb, 2 * C, 2 * C, 1, 1, st);
 }
 __global__ void bn_finalize_kernel(const double* __restrict__ stats, double count, float* mean, float* rstd,
                                    float* running_mean, float* running_var, long long* nbt, float momentum, float eps, int C) {
@@ -1143,8 +1175,7 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_reduce_kernel(const float*
                                                                     const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                     const float* __restrict__ w, const uint8_t* __restrict__ mask,
-                                                                    float p, uint64_t seed, double* __restrict__ sums,
-                                                                    float* __restrict__ dw, float* __restrict__ db, long long M) {
+                                                                    float p, uint64_t seed, double* __restrict__ sums, long long M) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   __shared__ float sm[3][8][256];
@@ -1196,19 +1227,30 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_reduce_kernel(const float*
   double a = 0.0, bq = 0.0; float cw = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) { a += sm[0][k][c]; bq += sm[1][k][c]; cw += sm[2][k][c]; }
-  atomicAdd(&sums[c], a);
-  atomicAdd(&sums[256 + c], (bq - (double)mean[c] * a) * (double)rstd[c]);
-  atomicAdd(&dw[c], cw);
-  if (c == 0) { float t = 0.f; for (int k = 0; k < 8; ++k) t += sdb[k]; atomicAdd(db, t); }
+  // partial row of this block: [0, 512) BN sums, [512, 768) dw, [768] db (doubles; finalize sums the rows in order)
+  double* prow = sums + (size_t)blockIdx.x * 776;
+  prow[c] = a;
+  prow[256 + c] = (bq - (double)mean[c] * a) * (double)rstd[c];
+  prow[512 + c] = (double)cw;
+  if (c == 0) { float t = 0.f; for (int k = 0; k < 8; ++k) t += sdb[k]; prow[768] = (double)t; }
 }
 template <typename T>
 int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                          const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
-                         float* dw, float* db, long long M, int C, cudaStream_t st) {
+                         float* dw, float* db, long long M, int C, cudaStream_t st, const Reducer* red) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
-  S4G_CUDA(launch_dep(seghead_bwd_reduce_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 4)), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, dw, db, M));
+  const int nb = (int)min((long long)cdiv(M, 8), (long long)148 * 4);
+  double* part = reinterpret_cast<double*>(reduce_scratch(red, seghead_scratch_bytes()));
+  if (!part) return S4G_ERR_WORKSPACE;
+  S4G_CUDA(launch_dep(seghead_bwd_reduce_kernel<T>, dim3(nb), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, part, M));
   S4G_KERNEL_CHECK();
-  return 0;
+  // one grouped combine for the three outputs (the BN sums are consumed by the very next kernel: never left queued)
+  FinalizeJobs q; q.n = 0; q.total_blocks = 0; q.launches = 0;
+  Reducer rq; rq.scratch = part; rq.scratch_bytes = seghead_scratch_bytes(); rq.defer = &q;
+  S4G_TRY(k_finalize(&rq, part, sums, nb, 512, 776, 1, 1, st));
+  S4G_TRY(k_finalize(&rq, part + 512, dw, nb, 256, 776, 1, 0, st));
+  S4G_TRY(k_finalize(&rq, part + 768, db, nb, 1, 776, 1, 0, st));
+  return k_finalize_flush(&q, st);
 }
 template <typename T>
 __global__ void __launch_bounds__(256, 2) seghead_bwd_apply_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
@@ -1303,13 +1345,8 @@ int k_depthhead_fwd(const T* h, const float* w, const float* b, float* out, long
 template <typename T>
 __global__ void __launch_bounds__(256) depthhead_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ out,
                                                             const T* __restrict__ h, const float* __restrict__ w,
-                                                            T* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db,
-                                                            long long M, int C) {
-  __shared__ float sdw[64];
-  __shared__ float sdb;
-  if (threadIdx.x < 64) sdw[threadIdx.x] = 0.f;
-  if (threadIdx.x == 0) sdb = 0.f;
-  __syncthreads();
+                                                            T* __restrict__ dh, float* __restrict__ part, long long M, int C) {
+  __shared__ float sdw[8][33];
   float lw[32], ldb = 0.f;
 #pragma unroll
   for (int i = 0; i < 32; ++i) lw[i] = 0.f;
@@ -1326,21 +1363,34 @@ __global__ void __launch_bounds__(256) depthhead_bwd_kernel(const float* __restr
       d.store(dh + row * 32 + c);
     }
   }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-  for (int i = 0; i < 32; ++i) { const float s = warp_sum(lw[i]); if ((threadIdx.x & 31) == 0) atomicAdd(&sdw[i], s); }
+  for (int i = 0; i < 32; ++i) { const float s = warp_sum(lw[i]); if (lane == 0) sdw[warp][i] = s; }
   ldb = warp_sum(ldb);
-  if ((threadIdx.x & 31) == 0) atomicAdd(&sdb, ldb);
+  if (lane == 0) sdw[warp][32] = ldb;
   __syncthreads();
-  if (threadIdx.x < C) atomicAdd(&dw[threadIdx.x], sdw[threadIdx.x]);
-  if (threadIdx.x == 0) atomicAdd(db, sdb);
+  // partial row of this block: [0, 32) dw, [32] db -- warps combined in warp order, rows summed in order by finalize
+  if (threadIdx.x < 33) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += sdw[k][threadIdx.x];
+    part[(size_t)blockIdx.x * 33 + threadIdx.x] = t;
+  }
 }
 template <typename T>
 int k_depthhead_bwd(const float* dout, const float* out, const T* h, const float* w, T* dh, float* dw, float* db,
-                    long long M, int C, cudaStream_t st) {
+                    long long M, int C, cudaStream_t st, const Reducer* red) {
   if (C != 32) { s4g_set_error("depthhead: C must be 32"); return S4G_ERR_SHAPE; }
-  depthhead_bwd_kernel<T><<<148 * 4, 256, 0, st>>>(dout, out, h, w, dh, dw, db, M, C);
+  const int nb = 148 * 4;
+  float* part = reinterpret_cast<float*>(reduce_scratch(red, depthhead_scratch_bytes()));
+  if (!part) return S4G_ERR_WORKSPACE;
+  depthhead_bwd_kernel<T><<<nb, 256, 0, st>>>(dout, out, h, w, dh, part, M, C);
   S4G_KERNEL_CHECK();
-  return 0;
+  FinalizeJobs q; q.n = 0; q.total_blocks = 0; q.launches = 0;
+  Reducer rq; rq.scratch = part; rq.scratch_bytes = depthhead_scratch_bytes(); rq.defer = &q;
+  S4G_TRY(k_finalize(&rq, part, dw, nb, 32, 33, 0, 0, st));
+  S4G_TRY(k_finalize(&rq, part + 32, db, nb, 1, 33, 0, 0, st));
+  return k_finalize_flush(&q, st);
 }
 
 // ------------------------------------------------------------------------------------------ weight packing
@@ -1514,10 +1564,10 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
   template int k_pack_linear_grouped<T>(const PackLinearJobs&, int, cudaStream_t);                                     \
   template int k_pack_conv3_grouped<T>(const PackLinearJobs&, int, cudaStream_t);                                      \
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
-  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*, float*); \
-  template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t, float*, int);                            \
+  template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*, float*, const Reducer*); \
+  template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t, float*, int, const Reducer*);                          \
   template int k_gelu<T>(const T*, T*, long long, cudaStream_t);                                                       \
-  template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t);                                       \
+  template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t, const Reducer*);                                       \
   template int k_tokens_to_nhwc<T>(const float*, T*, int, cudaStream_t);                                               \
   template int k_tap_grad<T>(const T*, float*, int, int, cudaStream_t, T*);                                                \
   template int k_cast_f32<T>(const float*, T*, long long, cudaStream_t);                                               \
@@ -1530,15 +1580,15 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
   template int k_col2im_s2<T>(const T*, T*, int, int, int, int, cudaStream_t);                                         \
   template int k_bilinear2x_fwd<T>(const T*, T*, int, int, int, int, cudaStream_t);                                    \
   template int k_bilinear2x_bwd<T>(const T*, T*, int, int, int, int, cudaStream_t);                                    \
-  template int k_bn_stats<T>(const T*, double*, long long, int, cudaStream_t);                                         \
+  template int k_bn_stats<T>(const T*, double*, long long, int, cudaStream_t, const Reducer*);                                         \
   template int k_bn_apply<T>(const T*, const float*, const float*, const float*, const float*, const T*, T*, int, long long, int, cudaStream_t); \
-  template int k_bn_bwd_reduce<T>(const T*, const T*, const float*, const float*, const float*, const float*, double*, int, long long, int, cudaStream_t); \
+  template int k_bn_bwd_reduce<T>(const T*, const T*, const float*, const float*, const float*, const float*, double*, int, long long, int, cudaStream_t, const Reducer*); \
   template int k_bn_bwd_apply<T>(const T*, const T*, const float*, const float*, const float*, const float*, const double*, double, T*, float*, float*, int, long long, int, cudaStream_t); \
   template int k_seghead_fwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, float*, long long, int, cudaStream_t); \
-  template int k_seghead_bwd_reduce<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, double*, float*, float*, long long, int, cudaStream_t); \
+  template int k_seghead_bwd_reduce<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, double*, float*, float*, long long, int, cudaStream_t, const Reducer*); \
   template int k_seghead_bwd_apply<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, const double*, double, T*, float*, float*, long long, int, cudaStream_t); \
   template int k_depthhead_fwd<T>(const T*, const float*, const float*, float*, long long, int, cudaStream_t);         \
-  template int k_depthhead_bwd<T>(const float*, const float*, const T*, const float*, T*, float*, float*, long long, int, cudaStream_t); \
+  template int k_depthhead_bwd<T>(const float*, const float*, const T*, const float*, T*, float*, float*, long long, int, cudaStream_t, const Reducer*); \
   template int k_pack_linear<T>(const float*, T*, T*, int, int, cudaStream_t);                                         \
   template int k_pack_conv<T>(const float*, T*, T*, int, int, int, cudaStream_t);                                      \
   template int k_pack_convT<T>(const float*, T*, T*, int, int, int, cudaStream_t);

@@ -50,18 +50,25 @@ struct S4GModel {
   void* allreduce_user = nullptr;
   void* peer_boxes[S4G_PEER_MAX_WORLD] = {};  // SyncBN exchange through NVLink peer memory (peer.cu) when peer_world > 1
   int peer_rank = 0, peer_world = 0;
-  unsigned long long peer_seq = 0;
   // BatchNorm accumulators of all layers live in two contiguous pools, zeroed by ONE memset at the top of forward
   // (sum / sumsq) and ONE at the top of backward (sum dy / sum dy*xhat) instead of one memset per layer
   size_t bn_stats_pool = 0, bn_sums_pool = 0;
   int bn_count = 0;
   // in-place sum over ranks of `count` doubles: the peer-memory kernel when mailboxes are set, else the host callback
   int exchange(double* v, int count, cudaStream_t st) {
-    if (peer_world > 1) { launches++; return k_peer_sum_f64(v, count, peer_boxes, peer_rank, peer_world, peer_seq++, st); }
+    if (peer_world > 1) { launches++; return k_peer_sum_f64(v, count, peer_boxes, peer_rank, peer_world, st); }
     if (!allreduce) { s4g_set_error("SyncBatchNorm needs s4g_model_set_peer_exchange or s4g_model_set_allreduce"); return S4G_ERR_STATE; }
     return allreduce(allreduce_user, v, count, st);
   }
   std::vector<cudaEvent_t> events;
+  // combine steps of the deterministic two-stage reductions (reduce.cu) queued by backward closures; run as one grouped
+  // launch at every gradient-bucket boundary and at the end of backward
+  FinalizeJobs pending{};
+  int flush_pending(cudaStream_t st) {
+    if (pending.n == 0) return 0;
+    launches++;
+    return k_finalize_flush(&pending, st);
+  }
   std::string bucket_str;
   int launches = 0;
   // per-call state read by closures
@@ -97,6 +104,16 @@ struct Builder {
     top = o + bytes;
     return o;
   }
+  // scratch of one two-stage reduction call site (partial rows, reduce.cu).  Deferred sites own their slot: the rows must
+  // survive until the grouped combine at the next bucket boundary.  Immediate sites share `shared_red`.
+  struct RedSlot { size_t off = 0, bytes = 0; };
+  RedSlot red_alloc(size_t bytes) { RedSlot r; r.off = alloc(bytes); r.bytes = bytes; return r; }
+  Reducer red(const RedSlot& sl, bool defer) const {
+    Reducer r;
+    r.scratch = m->ws + sl.off; r.scratch_bytes = sl.bytes; r.defer = defer ? &m->pending : nullptr;
+    return r;
+  }
+  RedSlot shared_red;
   int act(int Bn, int H, int W, int C, bool grad = true) {
     Act a;
     a.B = Bn; a.H = H; a.W = W; a.C = C;
@@ -145,11 +162,12 @@ struct Builder {
   }
 
   // ---- linear layers (nn.Linear and 1x1 Conv2d share the [N,K] weight layout) ------------------------------
-  struct Lin { Param* w; Param* b; size_t wf, wd; int N, K; };
+  struct Lin { Param* w; Param* b; size_t wf, wd; int N, K; RedSlot bias_red; };
   Lin linear(const std::string& name, int N, int K, bool dgrad = true) {
-    Lin l{P(name + ".weight"), Popt(name + ".bias"), 0, 0, N, K};
+    Lin l{P(name + ".weight"), Popt(name + ".bias"), 0, 0, N, K, RedSlot()};
     l.wf = alloc(sizeof(T) * (size_t)N * K);
     l.wd = dgrad ? alloc(sizeof(T) * (size_t)N * K) : 0;
+    if (l.b) l.bias_red = red_alloc(colsum_scratch_bytes(N));
     lin_jobs.push_back(l);   // packed by ONE grouped launch (finish())
     return l;
   }
@@ -158,17 +176,18 @@ struct Builder {
   int linear_param_grads(const Lin& l, const T* dY, const T* X, long long M, cudaStream_t st, bool bias_done = false) const {
     if (l.w->g) S4G_TRY(wgrad(linear_geom(M, l.N, l.K), dY, X, l.w->g, st));
     if (l.b && l.b->g && !bias_done) {
-      S4G_CUDA(cudaMemsetAsync(l.b->g, 0, sizeof(float) * l.N, st));
       m->launches++;
-      S4G_TRY(k_colsum<T>(dY, l.b->g, M, l.N, l.N, st));
+      const Reducer r = red(l.bias_red, true);
+      S4G_TRY(k_colsum<T>(dY, l.b->g, M, l.N, l.N, st, &r));
     }
     return 0;
   }
 
   // ---- 3x3 convolutions --------------------------------------------------------------------------------------
-  struct Conv { Param* w; Param* b; size_t wf, wd; int Co, Ci; };
+  struct Conv { Param* w; Param* b; size_t wf, wd; int Co, Ci; RedSlot bias_red; };
   Conv conv3(const std::string& name, int Co, int Ci) {
-    Conv c{P(name + ".weight"), Popt(name + ".bias"), 0, 0, Co, Ci};
+    Conv c{P(name + ".weight"), Popt(name + ".bias"), 0, 0, Co, Ci, RedSlot()};
+    if (c.b) c.bias_red = red_alloc(colsum_scratch_bytes(Co));
     c.wf = alloc(sizeof(T) * (size_t)Co * Ci * 9);
     c.wd = alloc(sizeof(T) * (size_t)Co * Ci * 9);
     dwp_bytes = std::max(dwp_bytes, sizeof(float) * (size_t)Co * Ci * 9);
@@ -205,9 +224,9 @@ struct Builder {
         }
       }
       if (c.b && c.b->g) {
-        S4G_CUDA(cudaMemsetAsync(c.b->g, 0, sizeof(float) * c.Co, st));
         mm->launches++;
-        S4G_TRY(k_colsum<T>(self->G(out), c.b->g, a.rows(), c.Co, c.Co, st));
+        const Reducer r = self->red(c.bias_red, true);
+        S4G_TRY(k_colsum<T>(self->G(out), c.b->g, a.rows(), c.Co, c.Co, st, &r));
       }
       return 0;
     });
@@ -244,6 +263,7 @@ struct Builder {
       m->bn_stats_pool = alloc(sizeof(double) * 512 * MAX_BN);
       m->bn_sums_pool = alloc(sizeof(double) * 512 * MAX_BN);
     }
+    need_shared_red(std::max(bn_scratch_bytes(256), seghead_scratch_bytes()));
     n.stats = m->bn_stats_pool + sizeof(double) * 512 * m->bn_count;
     n.sums = m->bn_sums_pool + sizeof(double) * 512 * m->bn_count;
     m->bn_count++;
@@ -251,14 +271,16 @@ struct Builder {
     n.rstd = alloc(sizeof(float) * 256);
     return n;
   }
+  void need_shared_red(size_t bytes) { if (shared_red.bytes < bytes) shared_red = red_alloc(bytes); }
   // statistics of x (forward): fills mean/rstd, updates running stats when training
   int bn_forward_stats(const BN& n, const T* x, long long M, cudaStream_t st) const {
     float* mean = m->template at<float>(n.mean);
     float* rstd = m->template at<float>(n.rstd);
     if (!m->training) { m->launches++; return k_bn_eval_prepare(n.rm->p, n.rv->p, mean, rstd, 1e-5f, 256, st); }
-    double* stats = m->template at<double>(n.stats);  // zeroed at the top of forward
-    m->launches += 2;
-    S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st));
+    double* stats = m->template at<double>(n.stats);
+    m->launches += 3;
+    const Reducer r = red(shared_red, false);
+    S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st, &r));
     if (m->d.world_size > 1) S4G_TRY(m->exchange(stats, 512, st));
     return k_bn_finalize(stats, (double)M * m->d.world_size, mean, rstd, n.rm->p, n.rv->p,
                          reinterpret_cast<long long*>(n.nbt->p), 0.1f, 1e-5f, 256, st);
@@ -267,8 +289,9 @@ struct Builder {
     double* sums = m->template at<double>(n.sums);
     const float* mean = m->template at<float>(n.mean);
     const float* rstd = m->template at<float>(n.rstd);
-    m->launches += 2;  // sums: zeroed at the top of backward
-    S4G_TRY(k_bn_bwd_reduce<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, relu, M, 256, st));
+    m->launches += 3;
+    const Reducer r = red(shared_red, false);
+    S4G_TRY(k_bn_bwd_reduce<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, relu, M, 256, st, &r));
     if (m->d.world_size > 1) S4G_TRY(m->exchange(sums, 512, st));
     return k_bn_bwd_apply<T>(dy, x, mean, rstd, n.w->p, n.b->p, sums, (double)M * m->d.world_size, dx, n.w->g, n.b->g,
                              relu, M, 256, st);
@@ -366,6 +389,7 @@ struct Builder {
     Param *n1w, *n1b, *n2w, *n2b;
     Lin qkv, proj, fc1, fc2;
     size_t h1, mean1, rstd1, qkvb, ao, lse, h2, mean2, rstd2, u, a;
+    RedSlot ln1_red, ln2_red, gelu_red;
   };
   std::vector<size_t> xs;  // residual stream snapshots: xs[2i] = block i input, xs[2i+1] = after attention
   std::vector<Block> blocks;
@@ -425,6 +449,10 @@ struct Builder {
       b.ao = alloc(sizeof(T) * Tk * 768);
       b.lse = alloc(sizeof(float) * (size_t)B * 12 * 197);
       b.u = alloc(sizeof(T) * Tk * 3072); b.a = alloc(sizeof(T) * Tk * 3072);
+      if (train_enc) {
+        b.ln1_red = red_alloc(ln_bwd_scratch_bytes(768)); b.ln2_red = red_alloc(ln_bwd_scratch_bytes(768));
+        b.gelu_red = red_alloc(colsum_scratch_bytes(3072));
+      }
       note_wgrad(linear_geom(Tk, 2304, 768)); note_wgrad(linear_geom(Tk, 768, 768));
       note_wgrad(linear_geom(Tk, 3072, 768)); note_wgrad(linear_geom(Tk, 768, 3072));
       blocks.push_back(b);
@@ -514,8 +542,8 @@ struct Builder {
           S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), epi(dub, 3072), st));
           mm->launches++;
           // fc1's bias gradient (column sums of du) comes out of the same pass
-          if (b.fc1.b->g) S4G_CUDA(cudaMemsetAsync(b.fc1.b->g, 0, sizeof(float) * 3072, st));
-          S4G_TRY(k_dgelu_mul<T>(dub, mm->template at<T>(b.u), dub, Tk * 3072, st, b.fc1.b->g, 3072));
+          const Reducer rg = self->red(b.gelu_red, true);
+          S4G_TRY(k_dgelu_mul<T>(dub, mm->template at<T>(b.u), dub, Tk * 3072, st, b.fc1.b->g, 3072, &rg));
         } else {
           EpiParams e = epi(dub, 3072, nullptr, EPI_DGELU);
           e.aux = mm->template at<T>(b.u);
@@ -524,21 +552,16 @@ struct Builder {
         S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st, fc2_bias_fused));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 3072), dub, mm->template at<T>(b.fc1.wd), epi(dhb, 768), st));
         S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st, self->umma_path()));
-        S4G_CUDA(cudaMemsetAsync(b.n2w->g, 0, sizeof(float) * 768, st));
-        S4G_CUDA(cudaMemsetAsync(b.n2b->g, 0, sizeof(float) * 768, st));
-        S4G_CUDA(cudaMemsetAsync(b.proj.b->g, 0, sizeof(float) * 768, st));
-        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st, dxt, b.proj.b->g));
+        const Reducer r2 = self->red(b.ln2_red, true), r1 = self->red(b.ln1_red, true);
+        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st, dxt, b.proj.b->g, &r2));
         // attention: x1 = x0 + proj(attn(qkv(ln1(x0))))
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), dxt, mm->template at<T>(b.proj.wd), epi(daob, 768), st));
         S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st, true));
         S4G_TRY(self->attn_bwd(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, st));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 2304), dqkvb, mm->template at<T>(b.qkv.wd), epi(dhb, 768), st));
         S4G_TRY(self->linear_param_grads(b.qkv, dqkvb, mm->template at<T>(b.h1), Tk, st));
-        S4G_CUDA(cudaMemsetAsync(b.n1w->g, 0, sizeof(float) * 768, st));
-        S4G_CUDA(cudaMemsetAsync(b.n1b->g, 0, sizeof(float) * 768, st));
-        if (prev_fc2_fused) S4G_CUDA(cudaMemsetAsync(prev_fc2_bias_g, 0, sizeof(float) * 768, st));
         return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st, i > 0 ? dxt : nullptr,
-                                  prev_fc2_fused ? prev_fc2_bias_g : nullptr);
+                                  prev_fc2_fused ? prev_fc2_bias_g : nullptr, &r1);
       });
     }
   }
@@ -604,12 +627,11 @@ struct Builder {
       bwd->push_back([=](cudaStream_t st) {
         float* ds = mm->template at<float>(self->head_dsmall);
         double* sums = mm->template at<double>(n.sums);
-        mm->launches += 3;
+        mm->launches += 4;
         S4G_TRY(k_bilinear2x_f32_bwd(mm->dout, ds, self->B, 112, 112, st));
-        S4G_CUDA(cudaMemsetAsync(w4->g, 0, sizeof(float) * 256, st));
-        S4G_CUDA(cudaMemsetAsync(b4->g, 0, sizeof(float), st));
+        const Reducer rs = self->red(self->shared_red, false);
         S4G_TRY(k_seghead_bwd_reduce<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
-                                        mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, w4->g, b4->g, M1, 256, st));
+                                        mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, w4->g, b4->g, M1, 256, st, &rs));
         if (mm->d.world_size > 1) S4G_TRY(mm->exchange(sums, 512, st));
         return k_seghead_bwd_apply<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
                                       mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, (double)M1 * mm->d.world_size, self->G(c),
@@ -628,11 +650,11 @@ struct Builder {
       const long long M2 = (long long)B * 224 * 224;
       m->fwd.push_back([=](cudaStream_t st) { mm->launches++; return k_depthhead_fwd<T>(self->V(h), w4->p, b4->p, mm->out, M2, 32, st); });
       // inserted BEFORE conv(…2)'s backward in run order because bwd runs reversed
+      need_shared_red(depthhead_scratch_bytes());
       bwd->push_back([=](cudaStream_t st) {
-        S4G_CUDA(cudaMemsetAsync(w4->g, 0, sizeof(float) * 32, st));
-        S4G_CUDA(cudaMemsetAsync(b4->g, 0, sizeof(float), st));
-        mm->launches += 2;
-        S4G_TRY(k_depthhead_bwd<T>(mm->dout, mm->out, self->V(h), w4->p, self->G(h), w4->g, b4->g, M2, 32, st));
+        mm->launches += 3;
+        const Reducer rd = self->red(self->shared_red, false);
+        S4G_TRY(k_depthhead_bwd<T>(mm->dout, mm->out, self->V(h), w4->p, self->G(h), w4->g, b4->g, M2, 32, st, &rd));
         return k_relu_bwd_add<T>(self->G(h), self->V(h), nullptr, self->G(h), M2 * 32, st);  // ReLU mask (h = relu(.))
       });
     }
@@ -653,6 +675,7 @@ struct Builder {
     const size_t ycol = alloc(sizeof(T) * M * kk * C), dycol = alloc(sizeof(T) * M * kk * C);
     const int out = act(a.B, a.H * k, a.W * k, C);
     note_wgrad(linear_geom(M, kk * C, C));
+    const RedSlot bias_red = red_alloc(colsum_scratch_bytes(C));
     m->fwd.push_back([=](cudaStream_t st) {
       S4G_TRY(self->fprop(linear_geom(M, kk * C, C), self->V(in), mm->template at<T>(wf), epi(mm->template at<T>(ycol), kk * C), st));
       mm->launches++;
@@ -666,8 +689,8 @@ struct Builder {
       float* dwp = mm->template at<float>(self->dwp_scratch);
       S4G_TRY(self->wgrad(linear_geom(M, kk * C, C), dy, self->V(in), dwp, st));
       S4G_TRY(k_unpack_convT_grad(dwp, w->g, C, C, k, st));
-      S4G_CUDA(cudaMemsetAsync(b->g, 0, sizeof(float) * C, st));
-      return k_colsum<T>(self->G(out), b->g, M * kk, C, C, st);
+      const Reducer r = self->red(bias_red, true);
+      return k_colsum<T>(self->G(out), b->g, M * kk, C, C, st, &r);
     });
     return out;
   }
@@ -693,6 +716,7 @@ struct Builder {
     });
     const int out = act(a.B, Ho, Wo, C);
     note_wgrad(linear_geom(M, C, 9 * C));
+    const RedSlot bias_red = red_alloc(colsum_scratch_bytes(C));
     m->fwd.push_back([=](cudaStream_t st) {
       mm->launches++;
       S4G_TRY(k_im2col_s2<T>(self->V(in), mm->template at<T>(col), a.B, a.H, a.W, C, st));
@@ -706,8 +730,8 @@ struct Builder {
       float* dwp = mm->template at<float>(self->dwp_scratch);
       S4G_TRY(self->wgrad(linear_geom(M, C, 9 * C), self->G(out), mm->template at<T>(col), dwp, st));
       S4G_TRY(k_unpack_conv_grad(dwp, w->g, C, C, 3, st));
-      S4G_CUDA(cudaMemsetAsync(b->g, 0, sizeof(float) * C, st));
-      return k_colsum<T>(self->G(out), b->g, M, C, C, st);
+      const Reducer r = self->red(bias_red, true);
+      return k_colsum<T>(self->G(out), b->g, M, C, C, st, &r);
     });
     return out;
   }
@@ -729,6 +753,7 @@ struct Builder {
     const size_t pooled = alloc(sizeof(float) * (size_t)B * 768);
     const size_t dhn = train_enc ? alloc(sizeof(T) * Tk * 768) : 0;
     const size_t xlast = xs[24];
+    const RedSlot ln_red = red_alloc(ln_bwd_scratch_bytes(768));
     m->fwd.push_back([=](cudaStream_t st) {
       mm->launches += 3;
       S4G_TRY(k_layernorm_fwd<T>(mm->template at<float>(xlast), nw->p, nb->p, mm->template at<T>(hn), mm->template at<float>(mean),
@@ -741,12 +766,11 @@ struct Builder {
       S4G_TRY(k_cls_head_bwd<T>(mm->dout, mm->template at<float>(pooled), hw ? hw->p : nullptr, hw ? hw->g : nullptr,
                                 hb ? hb->g : nullptr, train_enc ? mm->template at<T>(dhn) : nullptr, self->B, nc, 768, spatial, st));
       if (!train_enc) return 0;
-      if (nw->g) S4G_CUDA(cudaMemsetAsync(nw->g, 0, sizeof(float) * 768, st));
-      if (nb->g) S4G_CUDA(cudaMemsetAsync(nb->g, 0, sizeof(float) * 768, st));
       // gradient of the last block's output lands in dxa, where the encoder backward expects it
+      const Reducer r = self->red(ln_red, true);
       return k_layernorm_bwd<T>(mm->template at<T>(dhn), mm->template at<float>(xlast), nw->p, mm->template at<float>(mean),
                                 mm->template at<float>(rstd), nullptr, mm->template at<float>(self->dxa), nw->g, nb->g, (int)Tk, 768, st,
-                                nullptr, nullptr);
+                                nullptr, nullptr, &r);
     });
   }
 
@@ -880,7 +904,7 @@ int s4g_model_set_peer_exchange(S4GModel* m, void* const* mailboxes, int rank, i
     s4g_set_error("model_set_peer_exchange: bad argument (world <= 8)"); return S4G_ERR_STATE;
   }
   for (int r = 0; r < world; ++r) m->peer_boxes[r] = mailboxes[r];
-  m->peer_rank = rank; m->peer_world = world; m->peer_seq = 0;
+  m->peer_rank = rank; m->peer_world = world;
   return 0;
 }
 int s4g_model_set_allreduce(S4GModel* m, s4g_allreduce_fn fn, void* user) {
@@ -921,7 +945,6 @@ int s4g_model_forward(S4GModel* m, const float* images, float* out, int training
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   m->images = images; m->out = out; m->training = training; m->seed = seed; m->dropout_mask = dropout_mask;
   m->launches = 0;
-  if (m->bn_count && training) S4G_CUDA(cudaMemsetAsync(m->ws + m->bn_stats_pool, 0, sizeof(double) * 512 * m->bn_count, st));
   for (auto& op : m->pack) S4G_TRY(op(st));
   for (auto& op : m->fwd) S4G_TRY(op(st));
   return 0;
@@ -934,9 +957,10 @@ int s4g_model_backward(S4GModel* m, const float* dout, void* stream) {
   m->dout = dout;
   m->launches = 0;
   const int nb = (int)m->events.size();
-  if (m->bn_count) S4G_CUDA(cudaMemsetAsync(m->ws + m->bn_sums_pool, 0, sizeof(double) * 512 * m->bn_count, st));
+  m->pending.n = 0; m->pending.total_blocks = 0;
   for (size_t i = m->bwd_dec.size(); i-- > 0;) S4G_TRY(m->bwd_dec[i](st));
-  if (nb > 0) S4G_CUDA(cudaEventRecord(m->events[0], st));
+  // one bucket: it holds EVERY parameter (bucket_of_block() == 0), so its event is the end of backward, below
+  if (nb > 1) { S4G_TRY(m->flush_pending(st)); S4G_CUDA(cudaEventRecord(m->events[0], st)); }
   // bwd_enc[0] = patch-embed, bwd_enc[1 + i] = block i
   for (size_t i = m->bwd_enc.size(); i-- > 0;) {
     S4G_TRY(m->bwd_enc[i](st));
@@ -944,10 +968,11 @@ int s4g_model_backward(S4GModel* m, const float* dout, void* stream) {
       const int block = (int)i - 1;
       const int bkt = bucket_of_block(block, nb);
       const bool last_of_bucket = block == 0 ? false : bucket_of_block(block - 1, nb) != bkt;
-      if (last_of_bucket && bkt < nb - 1) S4G_CUDA(cudaEventRecord(m->events[bkt], st));
+      if (last_of_bucket && bkt < nb - 1) { S4G_TRY(m->flush_pending(st)); S4G_CUDA(cudaEventRecord(m->events[bkt], st)); }
     }
   }
-  if (nb > 1) S4G_CUDA(cudaEventRecord(m->events[nb - 1], st));
+  S4G_TRY(m->flush_pending(st));
+  if (nb > 0) S4G_CUDA(cudaEventRecord(m->events[nb - 1], st));
   return 0;
 }
 

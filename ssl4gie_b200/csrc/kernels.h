@@ -18,6 +18,28 @@ static inline ConvGeom conv3_geom(int B, int H, int W, int Cin, int Cout) {
   return g;
 }
 
+// ---- deterministic cross-block reductions: reduce.cu
+// A producer kernel writes one partial row per block into scratch; finalize sums the rows in a fixed order.
+struct FinalizeJob { const void* part; void* out; int nrows, ncols, ld, in_f64, out_f64, block0; };
+constexpr int MAX_FIN_JOBS = 64;
+struct FinalizeJobs { FinalizeJob job[MAX_FIN_JOBS]; int n, total_blocks, launches; };
+struct Reducer {
+  void* scratch = nullptr;        // where the partial rows go; null: the library's per-device scratch (s4g_init)
+  size_t scratch_bytes = 0;
+  FinalizeJobs* defer = nullptr;  // non-null (with own scratch): queue the combine step instead of launching it
+};
+int reduce_init();
+void* reduce_scratch(const Reducer* r, size_t bytes);  // null + error set when too small / not initialised
+// out[c] = sum_{row < nrows} part[row * ld + c], c < ncols (part: float or double rows; out: float or double)
+int k_finalize(const Reducer* r, const void* part, void* out, int nrows, int ncols, int ld, int in_f64, int out_f64, cudaStream_t st);
+int k_finalize_flush(FinalizeJobs* jobs, cudaStream_t st);
+// scratch a producer needs (upper bounds, bytes)
+static inline size_t ln_bwd_scratch_bytes(int C) { return (size_t)148 * 3 * C * sizeof(float); }
+static inline size_t colsum_scratch_bytes(int N) { return (size_t)((148 * 4) / ((N + 255) / 256) + 2) * N * sizeof(float); }   // k_colsum / k_dgelu_mul row blocks
+static inline size_t bn_scratch_bytes(int C) { return (size_t)(148 * 4 + 8) * 2 * C * sizeof(double); }
+static inline size_t seghead_scratch_bytes() { return (size_t)(148 * 4) * 776 * sizeof(double); }
+static inline size_t depthhead_scratch_bytes() { return (size_t)(148 * 4) * 33 * sizeof(float); }
+
 // ---- validation (SIMT) contractions: simt.cu
 template <typename T> int simt_conv_fprop(const ConvGeom& g, const T* X, const T* W, const EpiParams& e, cudaStream_t st);
 template <typename T> int simt_conv_wgrad(const ConvGeom& g, const T* dY, const T* X, float* dW, cudaStream_t st);
@@ -37,15 +59,15 @@ int k_assemble_tokens_bwd(const float* dx, float* dpe, float* dcls, float* dpos,
 template <typename T>
 int k_layernorm_fwd(const float* x, const float* gamma, const float* beta, T* y, float* mean, float* rstd, int rows,
                     int C, float eps, cudaStream_t st);
-// dx = (dres ? dres : 0) + LN-backward(dy); dgamma/dbeta accumulate atomically (must be zeroed by caller)
+// dx = (dres ? dres : 0) + LN-backward(dy); dgamma / dbeta are overwritten (deterministic two-stage reduction)
 template <typename T>
 int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                     const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, cudaStream_t st,
-                    T* dx_cast = nullptr, float* dxsum = nullptr);
-// dx_cast: optional T copy of dx (the next GEMM's operand); dxsum: optional [C] += column sums of dx (must be zeroed)
-template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum = nullptr, int N = 0);
+                    T* dx_cast = nullptr, float* dxsum = nullptr, const Reducer* red = nullptr);
+// dx_cast: optional T copy of dx (the next GEMM's operand); dxsum: optional [C] = column sums of dx
+template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum = nullptr, int N = 0, const Reducer* red = nullptr);
 template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st);
-template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st);  // out zeroed by caller
+template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st, const Reducer* red = nullptr);  // out overwritten
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out = nullptr);  // inverse of above (+ optional T copy of the result)
 // classification tail (cls_head.cu): token pooling + lin_head on fp32 master weights; W == nullptr: no head (out = pooled)
@@ -75,8 +97,8 @@ template <typename T> int k_col2im_s2(const T* dcol, T* dx, int B, int H, int W,
 template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st);
 template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int W, int C, cudaStream_t st);
 
-// BatchNorm2d(train): stats[0..C) = sum, [C..2C) = sumsq as double (zeroed by caller)
-template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st);
+// BatchNorm2d(train): stats[0..C) = sum, [C..2C) = sumsq as double (overwritten)
+template <typename T> int k_bn_stats(const T* x, double* stats, long long M, int C, cudaStream_t st, const Reducer* red = nullptr);
 // mean/rstd from (possibly all-reduced) sums over `count` rows; running stats update like torch
 int k_bn_finalize(const double* stats, double count, float* mean, float* rstd, float* running_mean, float* running_var,
                   long long* num_batches_tracked, float momentum, float eps, int C, cudaStream_t st);
@@ -86,10 +108,10 @@ int k_bn_eval_prepare(const float* running_mean, const float* running_var, float
 template <typename T>
 int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta, const T* skip,
                T* y, int relu, long long M, int C, cudaStream_t st);
-// sums[0..C) = sum(dy'), [C..2C) = sum(dy' * xhat) where dy' = relu ? dy*(bn(x)>0) : dy   (double, zeroed by caller)
+// sums[0..C) = sum(dy'), [C..2C) = sum(dy' * xhat) where dy' = relu ? dy*(bn(x)>0) : dy   (double, overwritten)
 template <typename T>
 int k_bn_bwd_reduce(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma,
-                    const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st);
+                    const float* beta, double* sums, int relu, long long M, int C, cudaStream_t st, const Reducer* red = nullptr);
 template <typename T>
 int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
                    const double* sums, double count, T* dx, float* dgamma, float* dbeta, int relu, long long M, int C,
@@ -104,7 +126,7 @@ int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float*
 template <typename T>
 int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                          const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
-                         float* dw, float* db, long long M, int C, cudaStream_t st);
+                         float* dw, float* db, long long M, int C, cudaStream_t st, const Reducer* red = nullptr);
 template <typename T>
 int k_seghead_bwd_apply(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                         const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed,
@@ -115,7 +137,7 @@ template <typename T>
 int k_depthhead_fwd(const T* h, const float* w, const float* b, float* out, long long M, int C, cudaStream_t st);
 template <typename T>
 int k_depthhead_bwd(const float* dout, const float* out, const T* h, const float* w, T* dh, float* dw, float* db,
-                    long long M, int C, cudaStream_t st);
+                    long long M, int C, cudaStream_t st, const Reducer* red = nullptr);
 // single-channel fp32 bilinear x2 (seg logits)
 int k_bilinear2x_f32_fwd(const float* x, float* y, int B, int H, int W, cudaStream_t st);
 int k_bilinear2x_f32_bwd(const float* dy, float* dx, int B, int H, int W, cudaStream_t st);
@@ -136,13 +158,14 @@ int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int Ntok, int H, c
 int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int Ntok, int H,
                  cudaStream_t st);
 
-// ---- losses: loss.cu   (sums are fp32 scratch, zeroed inside)
+// ---- losses: loss.cu   (scratch holds the per-block partial rows and the combined sums; nothing to zero)
+size_t dice_scratch_doubles(int B);
 int k_dice_fwd(const float* logits, const float* targets, float* sums, float* loss, int B, int HW, float smooth,
                cudaStream_t st);
 int k_dice_bwd(const float* logits, const float* targets, const float* sums, const float* gout, float* dlogits, int B,
                int HW, float smooth, cudaStream_t st);
 int k_ssi_fwd(const float* pred, const float* targ, float* scratch, float* loss, float* ssi_out, int B, int H, int W,
-              float alpha, int scales, cudaStream_t st);
+              float alpha, int scales, int image_based, cudaStream_t st);
 int k_ce_fwd(const float* logits, const long long* labels, const float* weight, float* loss, float* dlogits_unit, int B, int N,
              cudaStream_t st);
 int k_ce_bwd(const float* dlogits_unit, const float* gout, float* dlogits, int B, int N, cudaStream_t st);
@@ -156,4 +179,5 @@ int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr,
 
 // peer.cu: SyncBN statistic exchange over NVLink peer memory
 size_t k_peer_mailbox_bytes();
-int k_peer_sum_f64(double* data, int count, void* const* boxes, int rank, int world, unsigned long long seq, cudaStream_t st);
+size_t k_peer_ctl_offset();
+int k_peer_sum_f64(double* data, int count, void* const* boxes, int rank, int world, cudaStream_t st);

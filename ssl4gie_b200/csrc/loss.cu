@@ -18,9 +18,11 @@ __device__ __forceinline__ double block_sum_d(double v, double* red) {
 }
 
 // ---------------------------------------------------------------- Dice
-// sums (double) per image: [0] sum p*t, [1] sum p*p, [2] sum t*t
+// scratch (doubles): sums[B][3] = per image {sum p*t, sum p*p, sum t*t}, then the per-block partial rows part[B][LOSS_GX][3]
+// (block (x, b) writes row (b, x); the finalize kernel adds them in x order: no atomics, bit-reproducible)
+constexpr int LOSS_GX = 64;   // upper bound of the blocks per image
 __global__ void __launch_bounds__(256) dice_sums_kernel(const float* __restrict__ logits, const float* __restrict__ targets,
-                                                        double* __restrict__ sums, int HW) {
+                                                        double* __restrict__ part, int HW) {
   __shared__ double red[8];
   const int b = blockIdx.y;
   double s0 = 0, s1 = 0, s2 = 0;
@@ -30,16 +32,27 @@ __global__ void __launch_bounds__(256) dice_sums_kernel(const float* __restrict_
     s0 += p * t; s1 += p * p; s2 += t * t;
   }
   s0 = block_sum_d(s0, red); s1 = block_sum_d(s1, red); s2 = block_sum_d(s2, red);
-  if (threadIdx.x == 0) { atomicAdd(&sums[b * 3], s0); atomicAdd(&sums[b * 3 + 1], s1); atomicAdd(&sums[b * 3 + 2], s2); }
+  if (threadIdx.x == 0) { double* r = part + ((size_t)b * LOSS_GX + blockIdx.x) * 3; r[0] = s0; r[1] = s1; r[2] = s2; }
 }
-__global__ void dice_finalize_kernel(const double* __restrict__ sums, float* __restrict__ loss, int B, float smooth) {
-  if (threadIdx.x || blockIdx.x) return;
-  double acc = 0.0;
-  for (int b = 0; b < B; ++b) {
-    const float inter = (float)sums[b * 3], pp = (float)sums[b * 3 + 1], tt = (float)sums[b * 3 + 2];
-    acc += 2.0f * (inter + smooth) / (pp + tt + smooth);
+__global__ void __launch_bounds__(256) dice_finalize_kernel(double* __restrict__ sums, const double* __restrict__ part,
+                                                            float* __restrict__ loss, int B, int gx, float smooth) {
+  __shared__ double score[256];
+  double mine = 0.0;
+  for (int b = threadIdx.x; b < B; b += 256) {   // a thread owns whole images; images are added in index order below
+    double s0 = 0, s1 = 0, s2 = 0;
+    const double* r = part + (size_t)b * LOSS_GX * 3;
+    for (int x = 0; x < gx; ++x) { s0 += r[x * 3]; s1 += r[x * 3 + 1]; s2 += r[x * 3 + 2]; }
+    sums[b * 3] = s0; sums[b * 3 + 1] = s1; sums[b * 3 + 2] = s2;
+    const float inter = (float)s0, pp = (float)s1, tt = (float)s2;
+    mine += (double)(2.0f * (inter + smooth) / (pp + tt + smooth));
   }
-  *loss = 1.f - (float)(acc / B);
+  score[threadIdx.x] = mine;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double acc = 0.0;
+    for (int i = 0; i < 256 && i < B; ++i) acc += score[i];
+    *loss = 1.f - (float)(acc / B);
+  }
 }
 __global__ void dice_bwd_kernel(const float* __restrict__ logits, const float* __restrict__ targets,
                                 const double* __restrict__ sums, const float* __restrict__ gout,
@@ -57,13 +70,20 @@ __global__ void dice_bwd_kernel(const float* __restrict__ logits, const float* _
 
 // ---------------------------------------------------------------- SSI
 // scratch (doubles): per image b: S[b*8 + {0:a00,1:a01,2:a11,3:b0,4:b1,5:scale,6:shift,7:valid}],
-//   then global G[0]=mse_num, G[1]=Mtot, G[2+k]=grad_num_k, G[6+k]=M_k, then per image adjoint sums A[b*2+{0:G1,1:G0}]
+//   then global G[0]=mse_num, G[1]=Mtot, G[2+k]=grad_num_k, G[10+k]=M_k (k < 8), then per image adjoint sums
+//   A[b*2+{0:G1,1:G0}], the per-image backward weights Wt[b][9], then the per-block partial rows P[B][LOSS_GX][SSI_PW] every reducing kernel writes (block (x, b)
+//   -> row (b, x)) and the next small kernel adds in index order: no atomics, bit-reproducible
+constexpr int SSI_MAX_SCALES = 8;
+constexpr int SSI_PW = 1 + 2 * SSI_MAX_SCALES;   // widest partial row: mse + grad_num[8] + M[8]
 __device__ __forceinline__ double* ssi_S(double* s, int b) { return s + b * 8; }
 __device__ __forceinline__ double* ssi_G(double* s, int B) { return s + B * 8; }
-__device__ __forceinline__ double* ssi_A(double* s, int B, int b) { return s + B * 8 + 16 + b * 2; }
+__device__ __forceinline__ double* ssi_A(double* s, int B, int b) { return s + B * 8 + 24 + b * 2; }
+// per-image backward weights: Wt[b][0] = d total / d (sum m d^2 / 2) of image b, Wt[b][1+k] = d total / d (grad sum k)
+__device__ __forceinline__ double* ssi_Wt(double* s, int B, int b) { return s + B * 10 + 24 + b * (1 + SSI_MAX_SCALES); }
+__device__ __forceinline__ double* ssi_P(double* s, int B) { return s + B * (11 + SSI_MAX_SCALES) + 24; }
 
 __global__ void __launch_bounds__(256) ssi_sums_kernel(const float* __restrict__ pred, const float* __restrict__ targ,
-                                                       double* __restrict__ scratch, int HW) {
+                                                       double* __restrict__ scratch, int B, int HW) {
   __shared__ double red[8];
   const int b = blockIdx.y;
   double a00 = 0, a01 = 0, a11 = 0, b0 = 0, b1 = 0;
@@ -74,14 +94,21 @@ __global__ void __launch_bounds__(256) ssi_sums_kernel(const float* __restrict__
   a00 = block_sum_d(a00, red); a01 = block_sum_d(a01, red); a11 = block_sum_d(a11, red);
   b0 = block_sum_d(b0, red); b1 = block_sum_d(b1, red);
   if (threadIdx.x == 0) {
-    double* S = ssi_S(scratch, b);
-    atomicAdd(&S[0], a00); atomicAdd(&S[1], a01); atomicAdd(&S[2], a11); atomicAdd(&S[3], b0); atomicAdd(&S[4], b1);
+    double* r = ssi_P(scratch, B) + ((size_t)b * LOSS_GX + blockIdx.x) * SSI_PW;
+    r[0] = a00; r[1] = a01; r[2] = a11; r[3] = b0; r[4] = b1;
   }
 }
-__global__ void ssi_solve_kernel(double* __restrict__ scratch, int B) {
+__global__ void ssi_solve_kernel(double* __restrict__ scratch, int B, int gx) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   double* S = ssi_S(scratch, b);
+  {
+    double t[5] = {0, 0, 0, 0, 0};
+    const double* r = ssi_P(scratch, B) + (size_t)b * LOSS_GX * SSI_PW;
+    for (int x = 0; x < gx; ++x)
+      for (int k = 0; k < 5; ++k) t[k] += r[x * SSI_PW + k];
+    for (int k = 0; k < 5; ++k) S[k] = t[k];
+  }
   // the reference evaluates this in fp32 (losses.py:18-23); keep its `det != 0` selection on the fp32 value
   const float a00 = (float)S[0], a01 = (float)S[1], a11 = (float)S[2], b0 = (float)S[3], b1 = (float)S[4];
   const float det = a00 * a11 - a01 * a01;
@@ -105,14 +132,18 @@ __global__ void __launch_bounds__(256) ssi_terms_kernel(const float* __restrict_
   const float s = (float)ssi_S(scratch, b)[5], sh = (float)ssi_S(scratch, b)[6];
   const float* p = pred + (long long)b * HW;
   const float* t = targ + (long long)b * HW;
-  double mse = 0, gn[4] = {0, 0, 0, 0}, mk[4] = {0, 0, 0, 0};
+  double mse = 0, gn[SSI_MAX_SCALES], mk[SSI_MAX_SCALES];
+#pragma unroll
+  for (int k = 0; k < SSI_MAX_SCALES; ++k) { gn[k] = 0; mk[k] = 0; }
   for (int i = blockIdx.x * 256 + threadIdx.x; i < HW; i += gridDim.x * 256) {
     const int y = i / W, x = i % W;
     if (ssi_out) ssi_out[(long long)b * HW + i] = s * p[i] + sh;
     const bool m = t[i] > 0.f;
     const float d = ssi_diff(p, t, i, s, sh);
     mse += (double)(d * d);
-    for (int k = 0; k < scales; ++k) {
+#pragma unroll
+    for (int k = 0; k < SSI_MAX_SCALES; ++k) {
+      if (k >= scales) break;
       const int step = 1 << k;
       if ((y & (step - 1)) || (x & (step - 1))) break;
       if (m) mk[k] += 1.0;
@@ -120,24 +151,93 @@ __global__ void __launch_bounds__(256) ssi_terms_kernel(const float* __restrict_
       if (y + step < H && m && t[i + step * W] > 0.f) gn[k] += fabsf(ssi_diff(p, t, i + step * W, s, sh) - d);
     }
   }
-  double* G = ssi_G(scratch, B);
+  double* r = ssi_P(scratch, B) + ((size_t)b * LOSS_GX + blockIdx.x) * SSI_PW;
   mse = block_sum_d(mse, red);
-  if (threadIdx.x == 0) atomicAdd(&G[0], mse);
-  for (int k = 0; k < scales; ++k) {
+  if (threadIdx.x == 0) r[0] = mse;
+#pragma unroll
+  for (int k = 0; k < SSI_MAX_SCALES; ++k) {
+    if (k >= scales) break;
     const double a = block_sum_d(gn[k], red), c = block_sum_d(mk[k], red);
-    if (threadIdx.x == 0) { atomicAdd(&G[2 + k], a); atomicAdd(&G[6 + k], c); }
+    if (threadIdx.x == 0) { r[1 + k] = a; r[1 + SSI_MAX_SCALES + k] = c; }
   }
 }
-__global__ void ssi_finalize_kernel(double* __restrict__ scratch, float* __restrict__ loss, int B, float alpha, int scales) {
-  if (threadIdx.x || blockIdx.x) return;
+// Combines the per-block rows into per-image totals (a thread owns whole images), then one thread per component adds the
+// images in index order.  image_based != 0: reduction="image-based" (Depth_estimation/Metrics/losses.py:40-48, 82-85,
+// 99-102): every image's term is divided by its own mask count and the mean over images is taken; otherwise
+// reduction_batch_based (:28-37).  Also writes the per-image weights the backward pass multiplies with.
+__global__ void __launch_bounds__(256) ssi_finalize_kernel(double* __restrict__ scratch, float* __restrict__ loss, int B, int gx,
+                                                           float alpha, int scales, int image_based) {
+  __shared__ double tot[256][SSI_PW];
+  __shared__ double run[SSI_PW], img[SSI_PW];
+  __shared__ double s_mt;
   double* G = ssi_G(scratch, B);
-  double mt = 0.0;
-  for (int b = 0; b < B; ++b) mt += ssi_S(scratch, b)[2];
-  G[1] = mt;
-  double total = mt > 0.0 ? G[0] / (2.0 * mt) : 0.0;
-  if (alpha > 0.f)
-    for (int k = 0; k < scales; ++k) total += G[6 + k] > 0.0 ? alpha * G[2 + k] / G[6 + k] : 0.0;
-  *loss = (float)total;
+  if (threadIdx.x < SSI_PW) { run[threadIdx.x] = 0.0; img[threadIdx.x] = 0.0; }
+  if (threadIdx.x == 0) s_mt = 0.0;
+  __syncthreads();
+  for (int b0 = 0; b0 < B; b0 += 256) {
+    const int b = b0 + threadIdx.x;
+    if (b < B) {
+      const double* r = ssi_P(scratch, B) + (size_t)b * LOSS_GX * SSI_PW;
+      for (int c = 0; c < SSI_PW; ++c) {
+        const bool used = c == 0 || ((c - 1) % SSI_MAX_SCALES) < scales;
+        double t = 0.0;
+        if (used) for (int x = 0; x < gx; ++x) t += r[x * SSI_PW + c];
+        tot[threadIdx.x][c] = t;
+      }
+    }
+    __syncthreads();
+    const int nb = min(256, B - b0);
+    if (threadIdx.x < SSI_PW) {
+      const int c = threadIdx.x;
+      double a = run[c], ia = img[c];
+      for (int i = 0; i < nb; ++i) {
+        const double v = tot[i][c];
+        a += v;
+        if (c == 0) { const double m = ssi_S(scratch, b0 + i)[2]; ia += m > 0.0 ? v / (2.0 * m) : v; }
+        else if (c <= SSI_MAX_SCALES) { const double m = tot[i][c + SSI_MAX_SCALES]; ia += m > 0.0 ? v / m : v; }
+      }
+      run[c] = a; img[c] = ia;
+    } else if (threadIdx.x == 32) {
+      double mt = s_mt;
+      for (int i = 0; i < nb; ++i) mt += ssi_S(scratch, b0 + i)[2];
+      s_mt = mt;
+    }
+    __syncthreads();
+    if (b < B && image_based) {   // the weights of image-based reduction only need the image's own counts
+      double* w = ssi_Wt(scratch, B, b);
+      const double m = ssi_S(scratch, b)[2];
+      w[0] = (m > 0.0 ? 1.0 / m : 1.0) / B;
+      for (int k = 0; k < SSI_MAX_SCALES; ++k) {
+        const double mk = tot[threadIdx.x][1 + SSI_MAX_SCALES + k];
+        w[1 + k] = (k < scales && alpha > 0.f) ? (double)alpha * (mk > 0.0 ? 1.0 / mk : 1.0) / B : 0.0;
+      }
+    }
+    __syncthreads();
+  }
+  const double mt = s_mt;
+  if (threadIdx.x == 0) {
+    G[0] = run[0]; G[1] = mt;
+    for (int k = 0; k < SSI_MAX_SCALES; ++k) { G[2 + k] = run[1 + k]; G[10 + k] = run[1 + SSI_MAX_SCALES + k]; }
+    double total;
+    if (image_based) {
+      total = img[0] / B;
+      if (alpha > 0.f) for (int k = 0; k < scales; ++k) total += (double)alpha * img[1 + k] / B;
+    } else {
+      total = mt > 0.0 ? run[0] / (2.0 * mt) : 0.0;
+      if (alpha > 0.f) for (int k = 0; k < scales; ++k) total += run[1 + SSI_MAX_SCALES + k] > 0.0 ? (double)alpha * run[1 + k] / run[1 + SSI_MAX_SCALES + k] : 0.0;
+    }
+    *loss = (float)total;
+  }
+  if (!image_based) {
+    for (int b = threadIdx.x; b < B; b += 256) {
+      double* w = ssi_Wt(scratch, B, b);
+      w[0] = mt > 0.0 ? 1.0 / mt : 0.0;
+      for (int k = 0; k < SSI_MAX_SCALES; ++k) {
+        const double mk = run[1 + SSI_MAX_SCALES + k];
+        w[1 + k] = (k < scales && alpha > 0.f && mk > 0.0) ? (double)alpha / mk : 0.0;
+      }
+    }
+  }
 }
 // pass A of backward: q_i = d total / d ssi_i -> dpred (temporarily), and per-image G1 = sum q p, G0 = sum q
 __global__ void __launch_bounds__(256) ssi_bwd_q_kernel(const float* __restrict__ pred, const float* __restrict__ targ,
@@ -145,11 +245,13 @@ __global__ void __launch_bounds__(256) ssi_bwd_q_kernel(const float* __restrict_
                                                         int B, int H, int W, float alpha, int scales) {
   __shared__ double red[8];
   const int b = blockIdx.y, HW = H * W;
-  const double* G = ssi_G(scratch, B);
   const float s = (float)ssi_S(scratch, b)[5], sh = (float)ssi_S(scratch, b)[6];
-  const float inv_m = G[1] > 0.0 ? (float)(1.0 / G[1]) : 0.f;
-  float inv_k[4];
-  for (int k = 0; k < 4; ++k) inv_k[k] = (k < scales && alpha > 0.f && G[6 + k] > 0.0) ? (float)(alpha / G[6 + k]) : 0.f;
+  const double* wt = ssi_Wt(scratch, B, b);
+  const float inv_m = (float)wt[0];
+  float inv_k[SSI_MAX_SCALES];
+#pragma unroll
+  for (int k = 0; k < SSI_MAX_SCALES; ++k) inv_k[k] = (float)wt[1 + k];
+  (void)alpha;
   const float* p = pred + (long long)b * HW;
   const float* t = targ + (long long)b * HW;
   double g1 = 0, g0 = 0;
@@ -159,7 +261,9 @@ __global__ void __launch_bounds__(256) ssi_bwd_q_kernel(const float* __restrict_
     if (t[i] > 0.f) {
       const float d = ssi_diff(p, t, i, s, sh);
       q = d * inv_m;
-      for (int k = 0; k < scales; ++k) {
+#pragma unroll
+      for (int k = 0; k < SSI_MAX_SCALES; ++k) {
+        if (k >= scales) break;
         const int step = 1 << k;
         if ((y & (step - 1)) || (x & (step - 1))) break;
         float sg = 0.f;
@@ -177,7 +281,15 @@ __global__ void __launch_bounds__(256) ssi_bwd_q_kernel(const float* __restrict_
     g1 += (double)q * p[i]; g0 += (double)q;
   }
   g1 = block_sum_d(g1, red); g0 = block_sum_d(g0, red);
-  if (threadIdx.x == 0) { atomicAdd(&ssi_A(scratch, B, b)[0], g1); atomicAdd(&ssi_A(scratch, B, b)[1], g0); }
+  if (threadIdx.x == 0) { double* r = ssi_P(scratch, B) + ((size_t)b * LOSS_GX + blockIdx.x) * SSI_PW; r[0] = g1; r[1] = g0; }
+}
+__global__ void ssi_bwd_sum_kernel(double* __restrict__ scratch, int B, int gx) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const double* r = ssi_P(scratch, B) + (size_t)b * LOSS_GX * SSI_PW;
+  double g1 = 0.0, g0 = 0.0;
+  for (int x = 0; x < gx; ++x) { g1 += r[x * SSI_PW]; g0 += r[x * SSI_PW + 1]; }
+  ssi_A(scratch, B, b)[0] = g1; ssi_A(scratch, B, b)[1] = g0;
 }
 // pass B: dpred_i = gout * (q_i * s + m_i (2 p_i A00 + A01 + t_i B0)) — the terms through d(scale,shift)/d(pred)
 __global__ void ssi_bwd_final_kernel(const float* __restrict__ pred, const float* __restrict__ targ,
@@ -206,14 +318,17 @@ __global__ void ssi_bwd_final_kernel(const float* __restrict__ pred, const float
 }
 }  // namespace
 
-size_t ssi_scratch_floats(int B) { return 2 * ((size_t)B * 10 + 16); }  // doubles, expressed in floats
+size_t ssi_scratch_floats(int B) { return 2 * ((size_t)B * (11 + SSI_MAX_SCALES) + 24 + (size_t)B * LOSS_GX * SSI_PW); }  // doubles, expressed in floats
+size_t dice_scratch_doubles(int B) { return (size_t)B * 3 * (1 + LOSS_GX); }
+static inline int loss_gx(int HW) { return max(1, min(cdiv(HW, 2048), LOSS_GX)); }
 
 int k_dice_fwd(const float* logits, const float* targets, float* sums, float* loss, int B, int HW, float smooth, cudaStream_t st) {
   double* s = reinterpret_cast<double*>(sums);
-  S4G_CUDA(cudaMemsetAsync(s, 0, sizeof(double) * 3 * B, st));
-  dice_sums_kernel<<<dim3(max(1, min(cdiv(HW, 2048), 64)), B), 256, 0, st>>>(logits, targets, s, HW);
+  double* part = s + (size_t)B * 3;
+  const int gx = loss_gx(HW);
+  dice_sums_kernel<<<dim3(gx, B), 256, 0, st>>>(logits, targets, part, HW);
   S4G_KERNEL_CHECK();
-  dice_finalize_kernel<<<1, 32, 0, st>>>(s, loss, B, smooth);
+  dice_finalize_kernel<<<1, 256, 0, st>>>(s, part, loss, B, gx, smooth);
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -222,28 +337,31 @@ int k_dice_bwd(const float* logits, const float* targets, const float* sums, con
   S4G_KERNEL_CHECK();
   return 0;
 }
-int k_ssi_fwd(const float* pred, const float* targ, float* scratch, float* loss, float* ssi_out, int B, int H, int W, float alpha, int scales, cudaStream_t st) {
-  if (scales > 4) { s4g_set_error("ssi: scales must be <= 4"); return S4G_ERR_SHAPE; }
+int k_ssi_fwd(const float* pred, const float* targ, float* scratch, float* loss, float* ssi_out, int B, int H, int W, float alpha, int scales, int image_based, cudaStream_t st) {
+  if (scales > SSI_MAX_SCALES || scales < 0) { s4g_set_error("ssi: scales must be in [0, 8]"); return S4G_ERR_SHAPE; }
   double* s = reinterpret_cast<double*>(scratch);
-  S4G_CUDA(cudaMemsetAsync(s, 0, sizeof(float) * ssi_scratch_floats(B), st));
   const int HW = H * W;
-  dim3 grid(max(1, min(cdiv(HW, 2048), 64)), B);
-  ssi_sums_kernel<<<grid, 256, 0, st>>>(pred, targ, s, HW);
+  const int gx = loss_gx(HW);
+  dim3 grid(gx, B);
+  ssi_sums_kernel<<<grid, 256, 0, st>>>(pred, targ, s, B, HW);
   S4G_KERNEL_CHECK();
-  ssi_solve_kernel<<<cdiv(B, 128), 128, 0, st>>>(s, B);
+  ssi_solve_kernel<<<cdiv(B, 128), 128, 0, st>>>(s, B, gx);
   S4G_KERNEL_CHECK();
   ssi_terms_kernel<<<grid, 256, 0, st>>>(pred, targ, s, ssi_out, B, H, W, alpha > 0.f ? scales : 0);
   S4G_KERNEL_CHECK();
-  ssi_finalize_kernel<<<1, 32, 0, st>>>(s, loss, B, alpha, scales);
+  ssi_finalize_kernel<<<1, 256, 0, st>>>(s, loss, B, gx, alpha, alpha > 0.f ? scales : 0, image_based);
   S4G_KERNEL_CHECK();
   return 0;
 }
 int k_ssi_bwd(const float* pred, const float* targ, const float* scratch, const float* gout, float* dpred, int B, int H, int W, float alpha, int scales, cudaStream_t st) {
+  if (scales > SSI_MAX_SCALES || scales < 0) { s4g_set_error("ssi: scales must be in [0, 8]"); return S4G_ERR_SHAPE; }
   double* s = reinterpret_cast<double*>(const_cast<float*>(scratch));
   const int HW = H * W;
-  S4G_CUDA(cudaMemsetAsync(s + (size_t)B * 8 + 16, 0, sizeof(double) * 2 * B, st));
-  dim3 grid(max(1, min(cdiv(HW, 2048), 64)), B);
+  const int gx = loss_gx(HW);
+  dim3 grid(gx, B);
   ssi_bwd_q_kernel<<<grid, 256, 0, st>>>(pred, targ, s, dpred, B, H, W, alpha, alpha > 0.f ? scales : 0);
+  S4G_KERNEL_CHECK();
+  ssi_bwd_sum_kernel<<<cdiv(B, 128), 128, 0, st>>>(s, B, gx);
   S4G_KERNEL_CHECK();
   ssi_bwd_final_kernel<<<min(cdiv((long long)B * HW, 256), 148 * 16), 256, 0, st>>>(pred, targ, s, gout, dpred, B, HW);
   S4G_KERNEL_CHECK();

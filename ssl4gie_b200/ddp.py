@@ -54,6 +54,17 @@ class GradientAllReduce:
         self.slices = None
         self.events = None
         self.handles = []
+        if self.n_buckets < 1:
+            raise ValueError("GradientAllReduce: n_buckets must be >= 1")
+
+    def attach(self, optimizer):
+        """Fold the 1/world_size of DDP's gradient MEAN (train_segmentation.py:203) into the optimizer kernel: the
+        all-reduce here is a sum.  Called by train_epoch; call it yourself in a hand-written loop."""
+        if hasattr(optimizer, "grad_scale"):
+            optimizer.grad_scale = 1.0 / self.world_size
+        elif self.world_size > 1:
+            raise TypeError("GradientAllReduce sums gradients; use ssl4gie_b200.FusedAdamW (grad_scale) or divide "
+                            "engine.flat_grads by world_size before optimizer.step()")
 
     def _setup(self, handle):
         e = self.engine
@@ -70,7 +81,9 @@ class GradientAllReduce:
             e.bucket_events = self.events
 
     def prepare(self, batch):
-        """Call once before the first backward (needs the C model handle for the bucket plan)."""
+        """Before the first backward (needs the C model handle for the bucket plan): installs the per-bucket events so
+        that the exchange overlaps backward from the first step.  Optional: reduce() prepares itself otherwise, and
+        that first step's exchange simply runs after backward."""
         if self.slices is None:
             self._setup(self.engine.handle(batch))
 
@@ -81,6 +94,13 @@ class GradientAllReduce:
             return
         flat = self.engine.flat_grads
         cur = torch.cuda.current_stream()
+        if self.slices is None:
+            # not prepared: backward recorded no bucket events this step -> one exchange after backward, then install
+            # the plan (from any training handle of the model) for the following steps
+            dist.all_reduce(flat, group=self.group)
+            if self.engine.handles:  # the bucket plan depends on the parameter set only: any handle will do
+                self._setup(next(iter(self.engine.handles.values())))
+            return
         if not self.overlap:  # one all-reduce of the whole arena after backward (S4G_DDP_OVERLAP=0)
             dist.all_reduce(flat, group=self.group)
             return

@@ -149,7 +149,10 @@ class Engine:
         model = self.model_ref()
         self.materialize()
         prec, backend = self.config(model)
-        ws = self.world_size(model)
+        # Evaluation never exchanges BatchNorm statistics (running stats are used), so an eval-mode handle is a
+        # world-size-1 handle: building it involves no collective and the reference's "rank 0 evaluates while the
+        # others wait in a barrier" (train_segmentation.py:293-301) cannot deadlock on handle construction.
+        ws = self.world_size(model) if model.training else 1
         key = (batch, prec, backend, ws, bool(getattr(model, "frozen", False)))
         h = self.handles.get(key)
         if h is None:
@@ -194,14 +197,14 @@ class _Handle:
 
     def _install_allreduce(self):
         import torch.distributed as dist
-        from .peer import PeerMailboxes, use_peer_exchange
-        self.peer = None
+        from .peer import shared_mailboxes, use_peer_exchange
         if use_peer_exchange() and dist.get_world_size() <= 8 and dist.get_backend() == "nccl":
-            # one-CTA NVLink exchange kernel instead of an NCCL collective per statistic vector (csrc/peer.cu)
-            boxes = PeerMailboxes()
+            # one-CTA NVLink exchange kernel instead of an NCCL collective per statistic vector (csrc/peer.cu).  The
+            # mailboxes are created ONCE per process (collective: the first training forward, which every rank
+            # makes) and shared by every later handle, whose construction is then collective-free.
+            boxes = shared_mailboxes()
             if boxes.ok:
                 _C.check(_C.lib().s4g_model_set_peer_exchange(self.ptr, boxes.ptrs, boxes.rank, boxes.world))
-                self.peer = boxes
                 return
             print("ssl4gie_b200: peer mailboxes unavailable (%s); SyncBN statistics go through NCCL" % getattr(boxes, "error", "a peer failed"))
         ws_f64 = self.workspace[self.ws_off:self.ws_off + (self.workspace.numel() - 256) // 8 * 8].view(torch.float64)
@@ -220,9 +223,6 @@ class _Handle:
         _C.check(_C.lib().s4g_model_set_allreduce(self.ptr, self._cb, None))
 
     def destroy(self):
-        if getattr(self, "peer", None) is not None:
-            self.peer.close()
-            self.peer = None
         if self.ptr:
             _C.lib().s4g_model_destroy(self.ptr)
             self.ptr = None

@@ -46,7 +46,7 @@ class SoftDiceLoss(nn.Module):
 
 class _SSIFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, prediction, target, alpha, scales, holder):
+    def forward(ctx, prediction, target, alpha, scales, image_based, holder):
         _C.require_cuda(prediction, "prediction")
         p = prediction.detach().float().contiguous()
         t = target.detach().float().contiguous()
@@ -55,7 +55,7 @@ class _SSIFn(torch.autograd.Function):
         loss = torch.empty((), dtype=torch.float32, device=p.device)
         ssi = torch.empty((B, H, W), dtype=torch.float32, device=p.device)
         _C.check(_C.lib().s4g_ssi_fwd(_C.ptr(p), _C.ptr(t), _C.ptr(scratch), _C.ptr(loss), _C.ptr(ssi), B, H, W, alpha, scales,
-                                      _C.stream_ptr()))
+                                      int(image_based), _C.stream_ptr()))
         holder.append(ssi)
         ctx.save_for_backward(p, t, scratch)
         ctx.cfg = (alpha, scales, prediction.shape, prediction.dtype)
@@ -70,25 +70,26 @@ class _SSIFn(torch.autograd.Function):
         d = torch.empty_like(p)
         _C.check(_C.lib().s4g_ssi_bwd(_C.ptr(p), _C.ptr(t), _C.ptr(scratch), _C.ptr(g), _C.ptr(d), B, H, W, alpha, scales,
                                       _C.stream_ptr()))
-        return d.view(shape).to(dtype), None, None, None, None
+        return d.view(shape).to(dtype), None, None, None, None, None
 
 
 class ScaleAndShiftInvariantLoss(nn.Module):
-    """reference: Depth_estimation/Metrics/losses.py:120-151 (batch-based reduction only, as the reference uses)"""
+    """reference: Depth_estimation/Metrics/losses.py:120-151.  ``reduction``: "batch-based" (:28-37, what the training
+    scripts use) or anything else = image-based, exactly as the reference's constructors select it (:82-85, :99-102);
+    ``scales`` up to 8 (224 px: the reference's ``[::2**k]`` sub-sampling is meaningful up to 7)."""
 
     def __init__(self, alpha=0.5, scales=4, reduction="batch-based"):
         super().__init__()
-        if reduction != "batch-based":
-            raise NotImplementedError("the reference training scripts only use reduction='batch-based'")
-        if scales > 4:
-            raise NotImplementedError("scales <= 4")
+        if not 0 <= int(scales) <= 8:
+            raise ValueError("ScaleAndShiftInvariantLoss: 0 <= scales <= 8")
         self.__alpha = alpha
         self.__scales = scales
+        self.__image_based = reduction != "batch-based"
         self.__prediction_ssi = None
 
     def forward(self, prediction, target):
         holder = []
-        loss = _SSIFn.apply(prediction, target, float(self.__alpha), int(self.__scales), holder)
+        loss = _SSIFn.apply(prediction, target, float(self.__alpha), int(self.__scales), self.__image_based, holder)
         self.__prediction_ssi = holder[0]
         return loss
 

@@ -87,9 +87,6 @@ class VisionTransformer_from_Any(_Backbone):
                  ImageNet_weights=False):
         super().__init__()
         _check_supported(embed_dim, depth, num_heads, det)
-        if ImageNet_weights:
-            raise RuntimeError("ImageNet_weights=True downloads an .npz (Models/models.py:286-290); no network here — "
-                               "load a converted state_dict with load_state_dict instead")
         self.num_features = self.embed_dim = embed_dim
         self.patch_embed = _PatchEmbed(224, 16, 3, embed_dim)
         self.cls_token = nn.Parameter(torch.zeros(1, 1, embed_dim))
@@ -102,8 +99,76 @@ class VisionTransformer_from_Any(_Backbone):
             if isinstance(m, nn.Linear):
                 nn.init.trunc_normal_(m.weight, std=0.02)
                 nn.init.zeros_(m.bias)
+        if ImageNet_weights:
+            # reference Models/models.py:286-290: timm's download_cached_file + load_pretrained of the AugReg B/16 .npz.
+            # There is no network here, so the file must already be where timm would have cached it (or be named by
+            # ImageNet_weights=<path> / SSL4GIE_B200_IMAGENET_NPZ); the .npz -> state_dict key map is timm's.
+            self.load_pretrained(_find_imagenet_npz(ImageNet_weights))
         self.head = nn.Identity()
         self._finish(head, num_classes, frozen, dense, det, embed_dim, out_token)
+
+    @torch.no_grad()
+    def load_pretrained(self, checkpoint_path, prefix=""):
+        """timm 0.6.12 VisionTransformer.load_pretrained -> _load_weights for a Flax/JAX ViT ``.npz`` (the call at
+        reference Models/models.py:290).  Kernels are stored input-major (HWIO / [in, heads, head_dim]); the classifier
+        ("head/*", 1000 ImageNet classes) is dropped, as the reference replaces it with Identity right after loading."""
+        w = np.load(checkpoint_path)
+        sd = npz_to_state_dict(w, prefix, depth=len(self.blocks))
+        own = self.state_dict()
+        for k, v in sd.items():
+            if tuple(own[k].shape) != tuple(v.shape):
+                raise ValueError(f"{checkpoint_path}: {k} has shape {tuple(v.shape)}, expected {tuple(own[k].shape)}")
+            own[k].copy_(v)
+
+
+IMAGENET_NPZ = ("B_16-i21k-300ep-lr_0.001-aug_medium1-wd_0.1-do_0.0-sd_0.0--imagenet2012-steps_20k-lr_0.01-res_224.npz")
+
+
+def _find_imagenet_npz(arg):
+    import os
+    cands = []
+    if isinstance(arg, (str, os.PathLike)):
+        cands.append(os.fspath(arg))
+    if os.environ.get("SSL4GIE_B200_IMAGENET_NPZ"):
+        cands.append(os.environ["SSL4GIE_B200_IMAGENET_NPZ"])
+    cands.append(os.path.join(torch.hub.get_dir(), "checkpoints", IMAGENET_NPZ))  # timm download_cached_file's location
+    for c in cands:
+        if os.path.isfile(c):
+            return c
+    raise RuntimeError("ImageNet_weights=True needs the AugReg ViT-B/16 checkpoint " + IMAGENET_NPZ + " (reference "
+                       "Models/models.py:286-290 downloads it; this build never touches the network): place it at " +
+                       cands[-1] + ", or pass its path as ImageNet_weights / SSL4GIE_B200_IMAGENET_NPZ")
+
+
+def npz_to_state_dict(w, prefix="", depth=12):
+    """Flax ViT checkpoint arrays -> timm VisionTransformer state_dict entries (timm 0.6.12 _load_weights)."""
+    def t(a):
+        return torch.from_numpy(np.asarray(a, dtype=np.float32))
+
+    sd = {}
+    k = t(w[prefix + "embedding/kernel"])                       # [16, 16, 3, D] HWIO
+    sd["patch_embed.proj.weight"] = k.permute(3, 2, 0, 1).contiguous()
+    sd["patch_embed.proj.bias"] = t(w[prefix + "embedding/bias"])
+    sd["cls_token"] = t(w[prefix + "cls"]).reshape(1, 1, -1)
+    sd["pos_embed"] = t(w[prefix + "Transformer/posembed_input/pos_embedding"]).reshape(1, -1, k.shape[-1])
+    sd["norm.weight"] = t(w[prefix + "Transformer/encoder_norm/scale"])
+    sd["norm.bias"] = t(w[prefix + "Transformer/encoder_norm/bias"])
+    for i in range(depth):
+        b = f"{prefix}Transformer/encoderblock_{i}/"
+        mha = b + "MultiHeadDotProductAttention_1/"
+        o = f"blocks.{i}."
+        sd[o + "norm1.weight"] = t(w[b + "LayerNorm_0/scale"])
+        sd[o + "norm1.bias"] = t(w[b + "LayerNorm_0/bias"])
+        sd[o + "attn.qkv.weight"] = torch.cat([t(w[mha + n + "/kernel"]).flatten(1).T for n in ("query", "key", "value")])
+        sd[o + "attn.qkv.bias"] = torch.cat([t(w[mha + n + "/bias"]).reshape(-1) for n in ("query", "key", "value")])
+        sd[o + "attn.proj.weight"] = t(w[mha + "out/kernel"]).permute(2, 0, 1).flatten(1).contiguous()   # [H, hd, D] -> [D, H*hd]
+        sd[o + "attn.proj.bias"] = t(w[mha + "out/bias"])
+        for r in range(2):
+            sd[o + f"mlp.fc{r + 1}.weight"] = t(w[b + f"MlpBlock_3/Dense_{r}/kernel"]).T.contiguous()
+            sd[o + f"mlp.fc{r + 1}.bias"] = t(w[b + f"MlpBlock_3/Dense_{r}/bias"])
+        sd[o + "norm2.weight"] = t(w[b + "LayerNorm_2/scale"])
+        sd[o + "norm2.bias"] = t(w[b + "LayerNorm_2/bias"])
+    return sd
 
 
 def _sincos_1d(embed_dim, pos):

@@ -17,6 +17,9 @@ class FusedAdamW(torch.optim.Optimizer):
         core = model.module if hasattr(model, "module") else model
         self.engine = Engine.of(core)
         self.engine.materialize()
+        # p.grad aliases the flat gradient arena: backward writes it in place (no per-parameter clone, no accumulation
+        # into stale .grad tensors -- zero_grad() below is a no-op because every backward overwrites)
+        self.engine.enable_direct_grads()
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         # every parameter, in model.parameters() order, as the reference's torch.optim.AdamW(model.parameters()) holds
         # them: the indices in state_dict() are then the reference checkpoint's indices

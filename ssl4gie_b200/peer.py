@@ -1,6 +1,7 @@
 """Peer-memory mailboxes for the SyncBatchNorm statistic exchange (csrc/peer.cu; replaces the NCCL collectives inside
 torch.nn.SyncBatchNorm, reference Binary_segmentation/train_segmentation.py:199): every rank cudaMallocs one mailbox,
-the 64-byte cudaIpc handles travel through the process group, peers are opened with lazy peer access."""
+the 64-byte cudaIpc handles travel through the process group, peers are opened with lazy peer access.  One mailbox set
+per process serves every model handle (`shared_mailboxes`)."""
 import ctypes
 import os
 
@@ -52,6 +53,24 @@ class PeerMailboxes:
         if self.own:
             lib.s4g_peer_free(self.own)
             self.own = ctypes.c_void_p()
+
+
+    def check(self):
+        """Synchronises the device; raises if an exchange timed out waiting for a peer (S4G_PEER_TIMEOUT_S)."""
+        if self.own:
+            _C.check(_C.lib().s4g_peer_check(self.own))
+
+
+_shared = None
+
+
+def shared_mailboxes():
+    """The process-wide mailbox set of the default group (every model handle shares it: one exchange counter, kept in
+    the mailbox itself).  The FIRST call is collective; later calls are not."""
+    global _shared
+    if _shared is None:
+        _shared = PeerMailboxes()
+    return _shared
 
 
 def use_peer_exchange():

@@ -7,7 +7,17 @@ GPU: batches arrive through ``DevicePrefetcher`` (copy of batch i+1 under the co
 stays on the device (one all-reduce + one read-back per epoch instead of an all_reduce + ``.item()`` + ``barrier`` per
 step), progress lines print a loss that was read back asynchronously a few steps earlier, and autocast / GradScaler are
 not needed (bf16 operands with fp32 accumulation and fp32 master weights have fp32's exponent range).
+
+Precision: the reference runs these loops under ``torch.cuda.amp.autocast`` (train_segmentation.py:45).  Here the loops
+select the bf16 tcgen05 schedule themselves: a model whose ``precision`` attribute is still ``"auto"`` runs as
+``"bf16"`` inside ``train_epoch`` / ``test`` (outside them ``"auto"`` means bf16 under ``torch.autocast`` and the fp32
+FFMA validation kernels otherwise).  Set ``model.precision = "fp32"`` (or SSL4GIE_B200_PRECISION=fp32) to run the loops
+in the validation mode.
+
+Multi-GPU: pass ``grad_sync=ssl4gie_b200.ddp.GradientAllReduce(model)``; it prepares itself on the first ``reduce()``
+and folds the 1/world_size mean into ``FusedAdamW`` (``grad_sync.attach(optimizer)`` is called here).
 """
+import contextlib
 import random
 import time
 
@@ -20,6 +30,20 @@ from .prefetch import DevicePrefetcher
 def _is_dist():
     import torch.distributed as dist
     return dist.is_available() and dist.is_initialized()
+
+
+@contextlib.contextmanager
+def _bf16_by_default(model):
+    """Resolve precision "auto" to the bf16 tensor-core schedule for the duration of an epoch loop."""
+    core = model.module if hasattr(model, "module") else model
+    was = getattr(core, "precision", None)
+    if was == "auto":
+        core.precision = "bf16"
+    try:
+        yield
+    finally:
+        if was == "auto":
+            core.precision = was
 
 
 class _LaggedScalar:
@@ -51,10 +75,19 @@ def train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer,
 
     ``scaler`` is accepted for signature compatibility and ignored.  ``grad_sync`` is the
     ``ssl4gie_b200.ddp.GradientAllReduce`` of the model when world_size > 1 (the reference wraps the model in DDP)."""
+    with _bf16_by_default(model):
+        return _train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer, epoch, loss_fn, log_path,
+                            grad_sync, log_every)
+
+
+def _train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer, epoch, loss_fn, log_path, grad_sync,
+                 log_every):
     t = time.time()
     model.train()
     if train_sampler is not None:
         train_sampler.set_epoch(epoch - 1)
+    if grad_sync is not None and hasattr(grad_sync, "attach"):
+        grad_sync.attach(optimizer)
     n_batches = len(train_loader)
     n_data = len(train_loader.dataset) if hasattr(train_loader, "dataset") else None
     losses = None
@@ -97,6 +130,11 @@ def train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer,
 @torch.no_grad()
 def test(model, rank, test_loader, epoch, perf_fn, log_path):
     """Sample-weighted mean of ``perf_fn(output, target)`` over the loader (reference train_segmentation.py:84-126)."""
+    with _bf16_by_default(model):
+        return _test(model, rank, test_loader, epoch, perf_fn, log_path)
+
+
+def _test(model, rank, test_loader, epoch, perf_fn, log_path):
     t = time.time()
     model.eval()
     acc = None
@@ -119,6 +157,12 @@ def test(model, rank, test_loader, epoch, perf_fn, log_path):
     return result
 
 
+def _default_scaler_state():
+    """State of a fresh, enabled GradScaler: the reference's build() loads "scaler_state_dict" into one unconditionally
+    (train_segmentation.py:205-207) and torch refuses an empty dict there."""
+    return {"scale": 65536.0, "growth_factor": 2.0, "backoff_factor": 0.5, "growth_interval": 2000, "_growth_tracker": 0}
+
+
 def save_checkpoint(ckpt_path, epoch, model, optimizer, scaler, loss, val_perf, test_perf):
     """The reference's checkpoint dict, key for key (train_segmentation.py:328-342): loadable by the reference's
     build() (:185-206) and by eval_segmentation.py.  ``model`` may be wrapped (``.module``)."""
@@ -127,7 +171,7 @@ def save_checkpoint(ckpt_path, epoch, model, optimizer, scaler, loss, val_perf, 
         "epoch": epoch,
         "model_state_dict": core.state_dict(),
         "optimizer_state_dict": optimizer.state_dict(),
-        "scaler_state_dict": scaler.state_dict() if scaler is not None else {},
+        "scaler_state_dict": scaler.state_dict() if scaler is not None else _default_scaler_state(),
         "loss": loss,
         "val_perf": val_perf,
         "test_perf": test_perf,

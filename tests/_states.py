@@ -1,0 +1,70 @@
+"""Test helpers (checker side): synthetic targets that look like the real tasks' and a *well-conditioned* model state.
+
+At random init the decoder's BatchNorm statistics are untrained, the seg logits sit on the flat part of the Dice loss and
+the depth loss's 2x2 scale/shift solve is nearly singular: the reference's own fp32 gradients are then only 1e-1..1e-3
+accurate (measured against fp64) and say nothing about a bf16 implementation.  A few dozen reference AdamW steps on a
+fixed batch with blob-like targets move the model off that plateau; gradients there are well defined and the plain
+north-star criterion (2e-2 relative, cosine 0.999) can be applied to every tensor.
+"""
+import torch
+
+from oracle import ref_port  # checker only
+
+
+def blob_masks(B, seed=0, size=224):
+    """Union of 1-3 random discs per image (SURVEY.md §8d config 1 "blob variant", Kvasir-like masks)."""
+    g = torch.Generator().manual_seed(seed)
+    yy, xx = torch.meshgrid(torch.arange(size, dtype=torch.float32), torch.arange(size, dtype=torch.float32), indexing="ij")
+    out = torch.zeros(B, 1, size, size)
+    for b in range(B):
+        for _ in range(int(torch.randint(1, 4, (1,), generator=g))):
+            cx, cy = (torch.rand(2, generator=g) * 0.6 + 0.2) * size
+            r = (torch.rand(1, generator=g) * 0.2 + 0.08) * size
+            out[b, 0] = torch.maximum(out[b, 0], ((xx - cx) ** 2 + (yy - cy) ** 2 <= r * r).float())
+    return out
+
+
+def smooth_depth(B, seed=0, size=224):
+    """Low-frequency depth maps in (0.05, 1] with a zero (invalid) border and ~3 % invalid specks, C3VD-like
+    (Depth_estimation/Data/dataset.py:9-16 pads to a square with zeros)."""
+    g = torch.Generator().manual_seed(seed)
+    coarse = torch.rand(B, 1, 7, 7, generator=g)
+    d = torch.nn.functional.interpolate(coarse, size=(size, size), mode="bicubic", align_corners=True).clamp(0.05, 1.0)
+    d[torch.rand(B, 1, size, size, generator=g) < 0.03] = 0.0
+    d[:, :, :12, :] = 0.0
+    d[:, :, -12:, :] = 0.0
+    return d
+
+
+def structured_images(B, seed=0, size=224):
+    """Images correlated with nothing in particular but not white noise: smooth colour fields plus noise."""
+    g = torch.Generator().manual_seed(seed + 1000)
+    low = torch.nn.functional.interpolate(torch.randn(B, 3, 14, 14, generator=g), size=(size, size), mode="bilinear", align_corners=False)
+    return low + 0.3 * torch.randn(B, 3, size, size, generator=g)
+
+
+def warm_state(dense, sd, x, t, steps=50, lr=1e-4, alpha=0.1):
+    """`steps` reference AdamW steps (fp32 oracle + torch.optim.AdamW, train_segmentation.py:204) on the fixed batch.
+    Returns the state_dict (incl. BatchNorm running statistics) on x's device."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    full = {k: v.to(x.device).clone() for k, v in sd.items()}
+    params = {k: v.requires_grad_(True) for k, v in ref_port.trainable(full).items()}
+    full.update(params)
+    opt = torch.optim.AdamW(list(params.values()), lr=lr)
+    bn_names = [k[:-len("running_mean")] for k in full if k.endswith("running_mean")]
+    for _ in range(steps):
+        opt.zero_grad(set_to_none=True)
+        stats = {}
+        out = ref_port.forward(full, x, dense, True, None, stats)
+        loss = ref_port.soft_dice_loss(out, t) if dense == "seg" else ref_port.ssi_loss(out, t, alpha)
+        loss.backward()
+        opt.step()
+        with torch.no_grad():
+            for p in bn_names:  # nn.BatchNorm2d momentum 0.1 running statistics, as the module would keep them
+                if p in stats:
+                    mean, var = stats[p]
+                    full[p + "running_mean"].mul_(0.9).add_(0.1 * mean)
+                    full[p + "running_var"].mul_(0.9).add_(0.1 * var)
+                    full[p + "num_batches_tracked"] += 1
+    return {k: v.detach().clone() for k, v in full.items()}

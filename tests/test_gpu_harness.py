@@ -104,6 +104,10 @@ def test_train_epoch_checkpoint_and_resume(tmp_path, golden_dir, capsys):
     assert sorted(d["model_state_dict"]) == sorted(manifest)
     m_b = _model(seed=3)
     torch.optim.AdamW(m_b.parameters(), lr=1e-4).load_state_dict(d["optimizer_state_dict"])  # train_segmentation.py:206
+    # the reference's build() loads "scaler_state_dict" into an ENABLED GradScaler unconditionally (:205-207)
+    sc = torch.amp.GradScaler("cuda")
+    sc.load_state_dict(d["scaler_state_dict"])
+    assert sc.get_scale() == 65536.0
 
     # resume in a fresh process state: same second epoch
     opt_b = FusedAdamW(m_b, lr=1e-4)
@@ -120,3 +124,20 @@ def test_train_epoch_checkpoint_and_resume(tmp_path, golden_dir, capsys):
     mean_diff = sum((p.detach() - q.detach()).abs().sum().item() for p, q in zip(m_a.parameters(), m_b.parameters())) / \
         sum(p.numel() for p in m_a.parameters())
     assert mean_diff < 2e-6 and _max_param_diff(m_a, m_b) < 4e-4, (mean_diff, _max_param_diff(m_a, m_b))
+
+
+def test_epoch_loops_select_the_bf16_schedule_by_default():
+    """precision "auto" outside autocast means the fp32 validation kernels for a bare model(x) call, but the drop-in
+    epoch loops (the reference runs them under autocast, train_segmentation.py:45) pick the bf16 tcgen05 schedule."""
+    from ssl4gie_b200 import FusedAdamW, SoftDiceLoss, train
+    from ssl4gie_b200.engine import Engine
+    m = _model(precision="auto")
+    opt = FusedAdamW(m, lr=1e-4)
+    train.train_epoch(m, 0, 1, _batches(2), None, opt, 1, SoftDiceLoss(), None)
+    train.test(m, 0, _batches(1), 1, lambda o, t: ((o > 0).float() == t).float().mean(), None)
+    keys = list(Engine.of(m).handles)
+    assert keys and all(k[1] == "bf16" and k[2] == "tensor" for k in keys), keys
+    assert m.precision == "auto"
+    m.precision = "fp32"   # explicit choice is respected
+    train.test(m, 0, _batches(1), 1, lambda o, t: ((o > 0).float() == t).float().mean(), None)
+    assert any(k[1] == "fp32" for k in Engine.of(m).handles)

@@ -177,14 +177,19 @@ def test_bf16_step_matches_oracle(dense, backend):
     # gradients: 2e-2 relative L2 / cosine 0.999 against the exact result where bf16 allows it; where the
     # reference's own bf16-autocast run cannot reach that (it does not at B=4 with random init: measured cosine
     # ~0.985 for seg and negative for depth), we must be at least as close to the truth as that run.
-    bad = []
+    # The plain criterion on a well-conditioned state is tests/test_gpu_wellcond.py; here the count is printed.
+    bad, strict, strict_ref, total = [], 0, 0, 0
     for n, p in m.named_parameters():
         if g64.get(n) is None:
             continue
         e, e_ref = _l2(p.grad, g64[n]), _l2(params[n].grad, g64[n])
         c, c_ref = _cos(p.grad, g64[n]), _cos(params[n].grad, g64[n])
+        total += 1
+        strict += e <= 2e-2 and c >= 0.999
+        strict_ref += e_ref <= 2e-2 and c_ref >= 0.999
         if e > max(2e-2, 1.25 * e_ref) or c < min(0.999, c_ref - 0.01):
             bad.append((n, e, e_ref, c, c_ref))
+    print(f"[{dense}/{backend} random init B=4] strict_pass ours {strict}/{total}, reference bf16 autocast {strict_ref}/{total}")
     assert not bad, (len(bad), bad[:10])
 
 

@@ -83,6 +83,38 @@ def test_ssi_random_and_empty_mask(C, golden_dir):
     assert z.item() == 0.0
 
 
+@pytest.mark.parametrize("tag", ["img", "img_a0", "s6", "s5_img"])
+def test_ssi_image_based_and_more_scales(C, golden_dir, tag):
+    """reduction="image-based" and scales > 4 against known answers from the reference's own loss code."""
+    from ssl4gie_b200 import ScaleAndShiftInvariantLoss
+    from tests.test_oracle import _ssi_ext_cases
+    kat = json.load(open(os.path.join(golden_dir, "loss_kats.json")))
+    p, t, kw = _ssi_ext_cases()[tag]
+    pp = p.cuda().requires_grad_(True)
+    loss = ScaleAndShiftInvariantLoss(**kw)(pp, t.cuda())
+    loss.backward()
+    assert abs(loss.item() - kat[f"ssi_{tag}_loss"]) < 2e-6
+    assert abs(pp.grad.double().norm().item() - kat[f"ssi_{tag}_grad_norm"]) < 2e-4 * kat[f"ssi_{tag}_grad_norm"]
+    assert _rel(pp.grad.flatten()[:16].cpu(), torch.tensor(kat[f"ssi_{tag}_grad_head"])) < 5e-4
+
+
+def test_losses_are_bit_reproducible(C):
+    """Two-stage fixed-order reductions: the same inputs give bit-identical loss and gradient, run after run."""
+    from ssl4gie_b200 import ScaleAndShiftInvariantLoss, SoftDiceLoss
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(16, 1, 224, 224, generator=g).cuda()
+    t = torch.rand(16, 1, 224, 224, generator=g).cuda()
+    t[t < 0.1] = 0
+    for fn, a, b in ((SoftDiceLoss(), x, (t > 0.5).float()), (ScaleAndShiftInvariantLoss(alpha=0.1), torch.sigmoid(x), t)):
+        outs = []
+        for _ in range(3):
+            p = a.clone().requires_grad_(True)
+            loss = fn(p, b)
+            loss.backward()
+            outs.append((loss.detach().clone(), p.grad.clone()))
+        assert all(torch.equal(outs[0][0], o[0]) and torch.equal(outs[0][1], o[1]) for o in outs[1:])
+
+
 def test_losses_full_size_vs_oracle(C):
     from ssl4gie_b200 import ScaleAndShiftInvariantLoss, SoftDiceLoss
     g = torch.Generator().manual_seed(5)

@@ -45,6 +45,65 @@ def test_variant_manifests_and_frozen_flags(golden_dir):
     assert _manifest(cls) == ref["any_cls23"]
 
 
+def test_imagenet_npz_loader(tmp_path, monkeypatch):
+    """ImageNet_weights=True (reference Models/models.py:286-290 -> timm load_pretrained of a Flax .npz): the key map
+    and layout transposes, on a synthetic checkpoint written in the Flax layout; the classifier arrays are ignored."""
+    import numpy as np
+    from ssl4gie_b200 import utils
+    g = torch.Generator().manual_seed(5)
+    want = {}
+    arrays = {"head/kernel": np.zeros((768, 1000), np.float32), "head/bias": np.zeros(1000, np.float32)}
+
+    def rnd(*shape):
+        return torch.randn(*shape, generator=g) * 0.05
+
+    want["patch_embed.proj.weight"] = rnd(768, 3, 16, 16)
+    arrays["embedding/kernel"] = want["patch_embed.proj.weight"].permute(2, 3, 1, 0).numpy()          # HWIO
+    want["patch_embed.proj.bias"] = rnd(768); arrays["embedding/bias"] = want["patch_embed.proj.bias"].numpy()
+    want["cls_token"] = rnd(1, 1, 768); arrays["cls"] = want["cls_token"].numpy()
+    want["pos_embed"] = rnd(1, 197, 768); arrays["Transformer/posembed_input/pos_embedding"] = want["pos_embed"].numpy()
+    want["norm.weight"] = rnd(768); arrays["Transformer/encoder_norm/scale"] = want["norm.weight"].numpy()
+    want["norm.bias"] = rnd(768); arrays["Transformer/encoder_norm/bias"] = want["norm.bias"].numpy()
+    for i in range(12):
+        b, o = f"Transformer/encoderblock_{i}/", f"blocks.{i}."
+        for ln, fl in (("norm1", "LayerNorm_0"), ("norm2", "LayerNorm_2")):
+            want[o + ln + ".weight"] = rnd(768); arrays[b + fl + "/scale"] = want[o + ln + ".weight"].numpy()
+            want[o + ln + ".bias"] = rnd(768); arrays[b + fl + "/bias"] = want[o + ln + ".bias"].numpy()
+        qkv_w, qkv_b = rnd(2304, 768), rnd(2304)
+        want[o + "attn.qkv.weight"], want[o + "attn.qkv.bias"] = qkv_w, qkv_b
+        for j, n in enumerate(("query", "key", "value")):
+            # Flax: y[h, d] = sum_in x[in] * kernel[in, h, d]
+            arrays[b + f"MultiHeadDotProductAttention_1/{n}/kernel"] = qkv_w[j * 768:(j + 1) * 768].T.reshape(768, 12, 64).numpy()
+            arrays[b + f"MultiHeadDotProductAttention_1/{n}/bias"] = qkv_b[j * 768:(j + 1) * 768].reshape(12, 64).numpy()
+        want[o + "attn.proj.weight"] = rnd(768, 768)
+        arrays[b + "MultiHeadDotProductAttention_1/out/kernel"] = want[o + "attn.proj.weight"].T.reshape(12, 64, 768).numpy()
+        want[o + "attn.proj.bias"] = rnd(768); arrays[b + "MultiHeadDotProductAttention_1/out/bias"] = want[o + "attn.proj.bias"].numpy()
+        for r, (n_out, n_in) in enumerate(((3072, 768), (768, 3072))):
+            want[o + f"mlp.fc{r + 1}.weight"] = rnd(n_out, n_in)
+            arrays[b + f"MlpBlock_3/Dense_{r}/kernel"] = want[o + f"mlp.fc{r + 1}.weight"].T.numpy()
+            want[o + f"mlp.fc{r + 1}.bias"] = rnd(n_out); arrays[b + f"MlpBlock_3/Dense_{r}/bias"] = want[o + f"mlp.fc{r + 1}.bias"].numpy()
+    path = str(tmp_path / "vit_b16.npz")
+    np.savez(path, **arrays)
+    m = utils.get_ImageNet_or_random_ViT(False, 1, False, "seg", False, path)
+    sd = m.state_dict()
+    for k, v in want.items():
+        assert torch.equal(sd[k], v), k
+    # the attention layout means what timm's Attention computes: q of head h = x @ kernel[:, h, :] + bias[h]
+    x = torch.randn(3, 768, generator=g)
+    q_flax = torch.einsum("ni,ihd->nhd", x, torch.from_numpy(arrays["Transformer/encoderblock_3/MultiHeadDotProductAttention_1/query/kernel"])) + \
+        torch.from_numpy(arrays["Transformer/encoderblock_3/MultiHeadDotProductAttention_1/query/bias"])
+    q_timm = torch.nn.functional.linear(x, sd["blocks.3.attn.qkv.weight"], sd["blocks.3.attn.qkv.bias"])[:, :768].reshape(3, 12, 64)
+    assert torch.allclose(q_flax, q_timm, atol=1e-5)
+    # ImageNet_weights=True with no file anywhere: a clear error, never a download
+    monkeypatch.setenv("TORCH_HOME", str(tmp_path / "empty_hub"))
+    monkeypatch.delenv("SSL4GIE_B200_IMAGENET_NPZ", raising=False)
+    with pytest.raises(RuntimeError, match="never touches the network"):
+        utils.get_ImageNet_or_random_ViT(False, 1, False, "seg", False, True)
+    monkeypatch.setenv("SSL4GIE_B200_IMAGENET_NPZ", path)
+    m2 = utils.get_ImageNet_or_random_ViT(True, 23, False, None, False, True)
+    assert torch.equal(m2.state_dict()["blocks.11.mlp.fc2.weight"], want["blocks.11.mlp.fc2.weight"])
+
+
 def test_factory_signatures_match_reference():
     """reference utils.py:8-23, :26-50, :59-82 (callers pass positionally)."""
     from ssl4gie_b200 import utils
@@ -107,6 +166,13 @@ def test_arena_layout_and_bucket_plan():
     assert "blocks.11.mlp.fc2.weight" in plan[1] and "blocks.0.attn.qkv.weight" in plan[-1] and "patch_embed.proj.weight" in plan[-1]
     sl = bucket_slices(plan, offsets)
     assert all(s is not None and 0 <= s[0] < s[1] <= n_active for s in sl)
+    # one bucket = the whole gradient arena (its event is recorded at the END of backward, csrc/engine.cu)
+    plan1, _, _ = _bucket_plan(m, 1)
+    assert sorted(plan1[0]) == sorted(with_grad)
+    assert bucket_slices(plan1, offsets)[0][0] == 0
+    # two buckets: decoder | whole encoder
+    plan2, _, _ = _bucket_plan(m, 2)
+    assert all(n.startswith("decoder.") for n in plan2[0]) and sorted(plan2[0] + plan2[1]) == sorted(with_grad)
 
 
 def _gloo_worker(rank, world, port, plan, offsets, n_active, out):

@@ -87,6 +87,33 @@ def test_ssi_random_with_empty_mask_image(kats):
     assert ref_port.ssi_loss(p, torch.zeros_like(t), 0.0) == 0
 
 
+def _ssi_ext_cases():
+    g = torch.Generator().manual_seed(3)
+    p = torch.rand(3, 1, 32, 32, generator=g)
+    t = torch.rand(3, 1, 32, 32, generator=g)
+    t[torch.rand(3, 1, 32, 32, generator=g) < 0.2] = 0
+    t[2] = 0
+    g = torch.Generator().manual_seed(4)
+    p6 = torch.rand(2, 1, 64, 64, generator=g)
+    t6 = torch.rand(2, 1, 64, 64, generator=g)
+    t6[torch.rand(2, 1, 64, 64, generator=g) < 0.15] = 0
+    return {"img": (p, t, dict(alpha=0.1, reduction="image-based")), "img_a0": (p, t, dict(alpha=0.0, reduction="image-based")),
+            "s6": (p6, t6, dict(alpha=0.25, scales=6)), "s5_img": (p6, t6, dict(alpha=0.25, scales=5, reduction="image-based"))}
+
+
+@pytest.mark.parametrize("tag", ["img", "img_a0", "s6", "s5_img"])
+def test_ssi_image_based_and_more_scales(kats, tag):
+    """reduction="image-based" (Depth_estimation/Metrics/losses.py:40-48) and scales > 4 (:104-117): known answers from
+    the reference's own loss code (oracle/make_golden.py)."""
+    p, t, kw = _ssi_ext_cases()[tag]
+    pp = p.clone().requires_grad_(True)
+    loss = ref_port.ssi_loss(pp, t, **kw)
+    loss.backward()
+    assert abs(loss.item() - kats[f"ssi_{tag}_loss"]) < 1e-7
+    assert abs(pp.grad.double().norm().item() - kats[f"ssi_{tag}_grad_norm"]) < 1e-5 * kats[f"ssi_{tag}_grad_norm"]
+    assert torch.allclose(pp.grad.flatten()[:16], torch.tensor(kats[f"ssi_{tag}_grad_head"]), rtol=1e-4, atol=1e-10)
+
+
 @pytest.mark.parametrize("dense", ["seg", "depth"])
 def test_step_matches_reference_fixture(dense, golden_dir):
     """One fwd + loss + bwd at B=2 fp32 (BASELINE.json configs[0]) reproduces the reference's logits, loss, gradient
