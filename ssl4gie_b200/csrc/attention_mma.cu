@@ -385,7 +385,14 @@ static int attn_grid(int total) {
   return total < g_attn_sms ? total : g_attn_sms;
 }
 
+// S4G_ATTN=mma keeps this mma.sync kernel (A/B measurements); the default tensor-core attention is attention_umma.cu
+static bool use_umma_attention() {
+  static const bool v = [] { const char* e = getenv("S4G_ATTN"); return !(e && std::string(e) == "mma"); }();
+  return v;
+}
+
 int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int N, int H, cudaStream_t st) {
+  if (use_umma_attention()) return attn_fwd_umma(qkv, o, lse, B, N, H, st);
   if (N > NP || N < 1) { s4g_set_error("attn_fwd_mma: specialised for sequences of at most 208 tokens"); return S4G_ERR_SHAPE; }
   const size_t smem = 2 * 3 * TILE_BYTES;
   static bool attr = false;
@@ -396,6 +403,7 @@ int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int N, int H, cuda
 }
 int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int N, int H,
                  cudaStream_t st) {
+  if (use_umma_attention()) return attn_bwd_umma(qkv, o, dout, lse, dqkv, B, N, H, st);
   if (N > NP || N < 1) { s4g_set_error("attn_bwd_mma: specialised for sequences of at most 208 tokens"); return S4G_ERR_SHAPE; }
   const size_t smem = 2 * BWD_STAGE_BYTES;
   static bool attr = false;

@@ -51,6 +51,8 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
                     cudaStream_t st, int torch_layout = 0);
 size_t umma_wgrad_scratch_bytes(const ConvGeom& g);
 int umma_init();
+int umma_make_map_bf16(void* cu_tensor_map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box);
+int umma_num_sms();
 
 // ---- elementwise / normalisation / resampling: elementwise.cu
 template <typename T> int k_patchify(const float* img, T* out, int B, cudaStream_t st);
@@ -153,6 +155,10 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
 template <typename T> int attn_fwd_simt(const T* qkv, T* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
 template <typename T>
 int attn_bwd_simt(const T* qkv, const T* o, const T* dout, const float* lse, T* dqkv, int B, int Ntok, int H,
+                  cudaStream_t st);
+// tcgen05 attention (attention_umma.cu): S and P in tensor memory, Q/K/V by TMA; head dim 64, Ntok <= 208
+int attn_fwd_umma(const bf16* qkv, bf16* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
+int attn_bwd_umma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int Ntok, int H,
                   cudaStream_t st);
 int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
 int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int Ntok, int H,

@@ -43,17 +43,36 @@ def structured_images(B, seed=0, size=224):
     return low + 0.3 * torch.randn(B, 3, size, size, generator=g)
 
 
-def warm_state(dense, sd, x, t, steps=50, lr=1e-4, alpha=0.1):
-    """`steps` reference AdamW steps (fp32 oracle + torch.optim.AdamW, train_segmentation.py:204) on the fixed batch.
-    Returns the state_dict (incl. BatchNorm running statistics) on x's device."""
+def task_batch(dense, B, seed=0, size=224):
+    """A learnable synthetic sample of the task: the target (blob mask / smooth depth) is visible in the image through
+    a brightness cue under structured noise, so training has something to find and a fresh batch per step never gets
+    memorised (the loss settles at a mid-range value with substantial gradients)."""
+    x = structured_images(B, seed, size)
+    if dense == "seg":
+        t = blob_masks(B, seed, size)
+        x = x + 1.2 * (t - 0.5)
+    else:
+        t = smooth_depth(B, seed, size)
+        x = x + 1.5 * (t - 0.5) * (t > 0)
+    return x, t
+
+
+def warm_state(dense, sd, x, t, steps=50, lr=1e-4, alpha=0.1, fresh=None, device=None):
+    """`steps` reference AdamW steps (fp32 oracle + torch.optim.AdamW, train_segmentation.py:204) on the fixed batch
+    (x, t), or -- fresh = batch size -- on a new task_batch(dense, fresh, seed = 1000 + step) every step.
+    Returns the state_dict (incl. BatchNorm running statistics) on the device."""
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
-    full = {k: v.to(x.device).clone() for k, v in sd.items()}
+    if device is None:
+        device = x.device
+    full = {k: v.to(device).clone() for k, v in sd.items()}
     params = {k: v.requires_grad_(True) for k, v in ref_port.trainable(full).items()}
     full.update(params)
     opt = torch.optim.AdamW(list(params.values()), lr=lr)
     bn_names = [k[:-len("running_mean")] for k in full if k.endswith("running_mean")]
-    for _ in range(steps):
+    for k in range(steps):
+        if fresh:
+            x, t = (v.to(device) for v in task_batch(dense, fresh, 1000 + k))
         opt.zero_grad(set_to_none=True)
         stats = {}
         out = ref_port.forward(full, x, dense, True, None, stats)
