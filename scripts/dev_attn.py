@@ -9,6 +9,8 @@ L = C.lib()
 
 
 def rel(a, b):
+    if a.numel() == 0:
+        return 0.0
     return ((a.double() - b.double()).abs().max() / (b.double().abs().max() + 1e-30)).item()
 
 

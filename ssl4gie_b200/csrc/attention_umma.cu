@@ -14,7 +14,7 @@
 //               one query row (= one TMEM lane): row max, exp2, row sum, bf16 P written over the first half of S,
 //               later O / sum -> global.  The two tiles run half a phase apart, so the MMAs of one overlap the exponentials
 //               of the other.
-// backward, one persistent CTA per SM, 10 warps, keys on the TMEM lanes (S^T = K Q^T, dP^T = V dO^T), so that P^T and
+// backward, one persistent CTA per SM, same warp roles, keys on the TMEM lanes (S^T = K Q^T, dP^T = V dO^T), so that P^T and
 // dS^T are A operands in tensor memory for dV = P^T dO and dK = dS^T Q; dS^T additionally goes through a 32 KB shared
 // memory tile as the MN-major A operand of dQ = dS K.  Four steps per head (2 key tiles x 2 query halves), accumulators
 // of dV, dK (per key tile) and dQ (both query tiles) stay in tensor memory: 512 columns exactly.  No atomics anywhere:
@@ -35,7 +35,8 @@ constexpr int NP = 208;                  // tokens padded to 13 x 16
 constexpr int TILE_BYTES = NP * 128;     // one of Q / K / V / dO in shared memory: rows of 128 B, SWIZZLE_128B
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float SCALE = 0.125f;          // 64^-0.5
-constexpr int THREADS = 320;
+constexpr int THREADS = 320;             // forward: warp 0 TMA, warp 1 MMA, warps 2-9 compute (ptxas allocates for 384: 168 registers)
+constexpr int BWD_THREADS = 384;         // backward: + warps 10-11, the per-query statistics of the next head
 
 __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
   return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~(uintptr_t)1023);
@@ -45,23 +46,72 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// 64 fp32 accumulator columns of this thread's TMEM lane -> bf16 -> 128 contiguous bytes; 32 columns at a time (the
+// packed half is kept, so only 32 + 16 registers are live); `pk` is filled for the caller to store after it has released
+// the accumulator
+__device__ __forceinline__ void read_row64(uint32_t taddr, uint4 (&pk)[8], float scale) {
+#pragma unroll
+  for (int hf = 0; hf < 2; ++hf) {
+    uint32_t a[32];
+    tmem_ld32(taddr + hf * 32, a);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+      pk[hf * 4 + g] = make_uint4(pack_bf16(__uint_as_float(a[g * 8]) * scale, __uint_as_float(a[g * 8 + 1]) * scale),
+                                  pack_bf16(__uint_as_float(a[g * 8 + 2]) * scale, __uint_as_float(a[g * 8 + 3]) * scale),
+                                  pack_bf16(__uint_as_float(a[g * 8 + 4]) * scale, __uint_as_float(a[g * 8 + 5]) * scale),
+                                  pack_bf16(__uint_as_float(a[g * 8 + 6]) * scale, __uint_as_float(a[g * 8 + 7]) * scale));
+  }
+}
+// 32 rows x 128 B of one warp -> global, rows `ld` elements apart: every lane holds one row (8 x 16 B) but a warp store
+// that writes 32 different rows touches 32 cache lines; through the warp's 4 KB staging tile (16 B chunks XOR-swizzled by
+// the row: conflict-free both ways) each store instruction instead covers 4 rows x 128 contiguous bytes.
+__device__ __forceinline__ void store_rows_staged(uint8_t* wstage, bf16* base, long long ld, int row0, int nrows, const uint4 (&pk)[8], int lane) {
+  __syncwarp();   // the previous use of the staging tile has been read
+#pragma unroll
+  for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(wstage + lane * 128 + ((g ^ (lane & 7)) << 4)) = pk[g];
+  __syncwarp();
+  const int sub = lane >> 3, ch = lane & 7;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int r = j * 4 + sub;
+    const uint4 v = *reinterpret_cast<const uint4*>(wstage + r * 128 + ((ch ^ (r & 7)) << 4));
+    if (row0 + r < nrows) *reinterpret_cast<uint4*>(base + (long long)(row0 + r) * ld + ch * 8) = v;
+  }
+}
+constexpr int WSTAGE_BYTES = 32 * 128;   // per compute warp
+
 // =========================================================================================== forward
 constexpr int FWD_HALF_ROWS = 104;                       // TMA box rows: two boxes per tensor
 constexpr int FWD_STAGE_BYTES = 3 * TILE_BYTES;
 constexpr int FWD_STAGES = 2;
-constexpr int SLOT_COLS = 256;                           // TMEM columns per query tile: S [0,208), P [0,104), O [128,192)
+constexpr int SLOT_COLS = 256;                           // TMEM columns per query tile: S [0,208), P [0,104), O [128,208)
 constexpr int O_COL = 128;
+constexpr int O_N = D + 16;                              // O = P [V | 1 0 ... 0]: column 64 of the product is the row sum of P
 
 struct FwdCtl {
   uint64_t full[FWD_STAGES], empty[FWD_STAGES], s_full[2], p_full[2], o_full[2], slot_free[2];
   uint32_t tmem_base;
 };
 
+// 32 scores -> 16 packed bf16 pairs of p = 2^(s * sl2 + nb); `valid` = number of real key columns in this chunk
+template <bool MASKED>
+__device__ __forceinline__ void softmax_chunk32(const uint32_t (&v)[32], uint32_t (&pk)[16], float sl2, float nb, int valid) {
+#pragma unroll
+  for (int k = 0; k < 32; k += 2) {
+    float p0 = ex2_approx(fmaf(__uint_as_float(v[k]), sl2, nb)), p1 = ex2_approx(fmaf(__uint_as_float(v[k + 1]), sl2, nb));
+    if (MASKED) { if (k >= valid) p0 = 0.f; if (k + 1 >= valid) p1 = 0.f; }
+    pk[k >> 1] = pack_bf16(p0, p1);
+  }
+}
+
 __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o,
-                                                                   float* __restrict__ lse, int N, int H, int total) {
+                                                                   float* __restrict__ lse, int N, int H, int total, int dbg) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
-  FwdCtl* ctl = reinterpret_cast<FwdCtl*>(smem + FWD_STAGES * FWD_STAGE_BYTES);
+  uint8_t* ones = smem + FWD_STAGES * FWD_STAGE_BYTES;   // [208 keys][64]: column 0 = 1 (second 64-column group of B = [V | 1])
+  uint8_t* wstages = ones + TILE_BYTES;                  // 8 x 4 KB: output staging of the softmax warps
+  FwdCtl* ctl = reinterpret_cast<FwdCtl*>(wstages + 8 * WSTAGE_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int C = H * D;
 
@@ -74,6 +124,14 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
+  // the ones tile (SWIZZLE_128B: the 16 B chunk holding columns 0..7 of row r sits at chunk index r & 7)
+  for (int i = threadIdx.x; i < TILE_BYTES / 16; i += THREADS) {
+    const int r = i >> 3, ch = i & 7;
+    uint4 z = make_uint4(0, 0, 0, 0);
+    if (ch == (r & 7) && r < N) z.x = 0x3F80u;   // bf16 1.0 in element 0; rows past the sequence contribute nothing
+    reinterpret_cast<uint4*>(ones)[i] = z;
+  }
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -88,6 +146,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
       for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
         const int stage = i & 1;
         mbar_wait(&ctl->empty[stage], ((i >> 1) & 1) ^ 1);
+        if (dbg & 8) { mbar_arrive(&ctl->full[stage]); continue; }
         mbar_expect_tx(&ctl->full[stage], FWD_STAGE_BYTES);
         const int b = w / H, h = w % H;
         uint8_t* s = smem + stage * FWD_STAGE_BYTES;
@@ -99,7 +158,8 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     const uint32_t idesc_s = make_idesc(128, NP, 0, 0);     // S = Q K^T: both operands K-major
-    const uint32_t idesc_o = make_idesc(128, D, 0, 1);      // O = P V: A in TMEM, V MN-major (rows = keys)
+    const uint32_t idesc_o = make_idesc(128, O_N, 0, 1);    // O = P [V | 1]: A in TMEM, B MN-major (rows = keys)
+    const uint32_t u_ones = smem_u32(ones);
     // O_t of head ip: needs P_t complete; the last reader of the head's shared memory stage
     auto issue_pv = [&](int ip, int t) {
       mbar_wait(&ctl->p_full[t], ip & 1);
@@ -109,7 +169,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
         const uint32_t slot = tmem_base + t * SLOT_COLS;
 #pragma unroll
         for (int kk = 0; kk < NP / 16; ++kk)
-          umma_bf16_ts(slot + O_COL, slot + kk * 8, make_desc(sv + kk * 2048, TILE_BYTES, 1024), idesc_o, kk != 0);
+          if (!(dbg & 1)) umma_bf16_ts(slot + O_COL, slot + kk * 8, make_desc(sv + kk * 2048, u_ones - sv, 1024), idesc_o, kk != 0);
         umma_commit(&ctl->o_full[t]);
         if (t == 1) umma_commit(&ctl->empty[ip & 1]);
       }
@@ -128,7 +188,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
           const uint32_t sk = smem_u32(smem + stage * FWD_STAGE_BYTES + TILE_BYTES);
 #pragma unroll
           for (int kk = 0; kk < D / 16; ++kk)
-            umma_bf16(tmem_base + t * SLOT_COLS, make_desc(sq + kk * 32, 16, 1024), make_desc(sk + kk * 32, 16, 1024), idesc_s, kk != 0);
+            if (!(dbg & 2)) umma_bf16(tmem_base + t * SLOT_COLS, make_desc(sq + kk * 32, 16, 1024), make_desc(sk + kk * 32, 16, 1024), idesc_s, kk != 0);
           umma_commit(&ctl->s_full[t]);
         }
         __syncwarp();
@@ -145,99 +205,94 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
     const bool warp_active = t * 128 + q * 32 < N;
     const uint32_t taddr = tmem_base + t * SLOT_COLS + ((uint32_t)(q * 32) << 16);
     const float sl2 = SCALE * LOG2E;
+    const int full_chunks = N >> 5;            // 32-column chunks without padding (6 for N = 197)
     int i = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
       const int b = w / H, h = w % H;
       mbar_wait(&ctl->s_full[t], i & 1);
       tc_fence_after();
-      float mx = -INFINITY, sum = 0.f;
-      if (warp_active) {
-        // pass 1: row maximum over the valid keys
+      float mx = -INFINITY;
+      if (warp_active && !(dbg & 4)) {
+        // pass 1: row maximum over the valid keys; the load of chunk c + 1 is in flight while chunk c is reduced
+        uint32_t va[32], vb[32];
+        tmem_ld32(taddr, va);
 #pragma unroll 1
-        for (int c0 = 0; c0 < NP; c0 += 32) {
-          if (c0 + 32 <= NP) {
-            uint32_t v[32];
-            tmem_ld32(taddr + c0, v);
-            tmem_ld_wait();
-            if (c0 + 32 <= N) {
+        for (int c = 0; c < 6; c += 2) {
+          tmem_ld_wait();
+          tmem_ld32(taddr + (c + 1) * 32, vb);
+          if (c < full_chunks) {
 #pragma unroll
-              for (int k = 0; k < 32; ++k) mx = fmaxf(mx, __uint_as_float(v[k]));
-            } else {
-#pragma unroll
-              for (int k = 0; k < 32; ++k) if (c0 + k < N) mx = fmaxf(mx, __uint_as_float(v[k]));
-            }
+            for (int k = 0; k < 32; ++k) mx = fmaxf(mx, __uint_as_float(va[k]));
           } else {
-            uint32_t v[16];
-            tmem_ld16(taddr + c0, v);
-            tmem_ld_wait();
 #pragma unroll
-            for (int k = 0; k < 16; ++k) if (c0 + k < N) mx = fmaxf(mx, __uint_as_float(v[k]));
+            for (int k = 0; k < 32; ++k) if (c * 32 + k < N) mx = fmaxf(mx, __uint_as_float(va[k]));
+          }
+          tmem_ld_wait();
+          if (c + 2 < 6) tmem_ld32(taddr + (c + 2) * 32, va);
+          else tmem_ld16(taddr + 192, reinterpret_cast<uint32_t(&)[16]>(va));
+          if (c + 1 < full_chunks) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) mx = fmaxf(mx, __uint_as_float(vb[k]));
+          } else {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) if ((c + 1) * 32 + k < N) mx = fmaxf(mx, __uint_as_float(vb[k]));
           }
         }
+        tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) if (192 + k < N) mx = fmaxf(mx, __uint_as_float(va[k]));
         const float nb = -mx * sl2;
-        // pass 2: p = exp2((s - max) * scale * log2 e) -> bf16 pairs written over the first half of S (a thread only ever
-        // touches its own lane, and P chunk c lands on columns this thread has already read)
+        // pass 2: p = 2^((s - max) * scale * log2 e) -> bf16 pairs written over the first half of S (a thread only ever
+        // touches its own lane, and P chunk c lands on columns this thread has already read); same load pipelining
+        uint32_t pk[16];
+        tmem_ld32(taddr, va);
 #pragma unroll 1
-        for (int c0 = 0; c0 < NP; c0 += 32) {
-          if (c0 + 32 <= NP) {
-            uint32_t v[32], pk[16];
-            tmem_ld32(taddr + c0, v);
-            tmem_ld_wait();
+        for (int c = 0; c < 6; c += 2) {
+          tmem_ld_wait();
+          tmem_ld32(taddr + (c + 1) * 32, vb);
+          if (c < full_chunks) softmax_chunk32<false>(va, pk, sl2, nb, 32); else softmax_chunk32<true>(va, pk, sl2, nb, N - c * 32);
+          tmem_ld_wait();   // chunk c + 1 has left tensor memory: its columns [16(c+1) .. ) may be overwritten below and later
+          if (c + 2 < 6) tmem_ld32(taddr + (c + 2) * 32, va);
+          else tmem_ld16(taddr + 192, reinterpret_cast<uint32_t(&)[16]>(va));
+          tmem_st16(taddr + c * 16, pk);
+          if (c + 1 < full_chunks) softmax_chunk32<false>(vb, pk, sl2, nb, 32); else softmax_chunk32<true>(vb, pk, sl2, nb, N - (c + 1) * 32);
+          tmem_st16(taddr + (c + 1) * 16, pk);
+        }
+        tmem_ld_wait();
+        {
+          uint32_t p8[8];
 #pragma unroll
-            for (int k = 0; k < 32; k += 2) {
-              float p0 = ex2_approx(fmaf(__uint_as_float(v[k]), sl2, nb)), p1 = ex2_approx(fmaf(__uint_as_float(v[k + 1]), sl2, nb));
-              if (c0 + k >= N) p0 = 0.f;
-              if (c0 + k + 1 >= N) p1 = 0.f;
-              sum += p0 + p1;
-              pk[k >> 1] = pack_bf16(p0, p1);
-            }
-            tmem_st16(taddr + (c0 >> 1), pk);
-          } else {
-            uint32_t v[16], pk[8];
-            tmem_ld16(taddr + c0, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int k = 0; k < 16; k += 2) {
-              float p0 = ex2_approx(fmaf(__uint_as_float(v[k]), sl2, nb)), p1 = ex2_approx(fmaf(__uint_as_float(v[k + 1]), sl2, nb));
-              if (c0 + k >= N) p0 = 0.f;
-              if (c0 + k + 1 >= N) p1 = 0.f;
-              sum += p0 + p1;
-              pk[k >> 1] = pack_bf16(p0, p1);
-            }
-            tmem_st8(taddr + (c0 >> 1), pk);
+          for (int k = 0; k < 16; k += 2) {
+            float p0 = ex2_approx(fmaf(__uint_as_float(va[k]), sl2, nb)), p1 = ex2_approx(fmaf(__uint_as_float(va[k + 1]), sl2, nb));
+            if (192 + k >= N) p0 = 0.f;
+            if (192 + k + 1 >= N) p1 = 0.f;
+            p8[k >> 1] = pack_bf16(p0, p1);
           }
+          tmem_st8(taddr + 96, p8);
         }
         tmem_st_wait();
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl->p_full[t]);
-      // epilogue: O / sum -> bf16 -> global
+      // epilogue: O / sum -> bf16 -> global; the row sum is column 64 of the product (the sum of the bf16 P the MMA used)
       mbar_wait(&ctl->o_full[t], i & 1);
       tc_fence_after();
-      uint32_t acc[2][32];
+      uint4 acc[8];
+      float sum = 1.f;
       if (warp_active) {
-        tmem_ld32(taddr + O_COL, acc[0]);
-        tmem_ld32(taddr + O_COL + 32, acc[1]);
+        uint32_t rs[8];
+        tmem_ld8(taddr + O_COL + 64, rs);
         tmem_ld_wait();
+        sum = __uint_as_float(rs[0]);
+        read_row64(taddr + O_COL, acc, 1.f / sum);
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl->slot_free[t]);   // the slot may take the next head's S while the stores drain
-      if (warp_active && row < N) {
-        const float inv = 1.f / sum;
-        bf16* dst = o + ((long long)b * N + row) * C + h * D;
-#pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          const uint32_t* a = acc[g >> 2] + (g & 3) * 8;
-          uint4 pk;
-          pk.x = pack_bf16(__uint_as_float(a[0]) * inv, __uint_as_float(a[1]) * inv);
-          pk.y = pack_bf16(__uint_as_float(a[2]) * inv, __uint_as_float(a[3]) * inv);
-          pk.z = pack_bf16(__uint_as_float(a[4]) * inv, __uint_as_float(a[5]) * inv);
-          pk.w = pack_bf16(__uint_as_float(a[6]) * inv, __uint_as_float(a[7]) * inv);
-          *reinterpret_cast<uint4*>(dst + g * 8) = pk;
-        }
-        lse[((long long)b * H + h) * N + row] = mx * SCALE + logf(sum);
+      if (warp_active && !(dbg & 16)) {
+        store_rows_staged(wstages + (warp - 2) * WSTAGE_BYTES, o + (long long)b * N * C + h * D, C, t * 128 + q * 32, N, acc, lane);
+        if (row < N) lse[((long long)b * H + h) * N + row] = mx * SCALE + logf(sum);
       }
     }
   }
@@ -247,45 +302,89 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
 }
 
 // =========================================================================================== backward
-// shared memory: Q | K | V | dO (each [lo 128 rows | hi 80 rows] x 128 B), dS^T staging (2 query groups x 128 keys x 128 B),
-// lse * log2(e) and delta of the 208 (padded) queries, barriers
+// Keys on the TMEM lanes.  Per head: 2 key tiles (keys 0..127, 128..207) x 4 query chunks (64, 64, 64, 16 queries) = 8 steps.
+// Step: S^T = K_t Q_c^T and dP^T = V_t dO_c^T (M = 128 keys, N = chunk) into one of two TMEM buffers; eight compute warps
+// (thread = key row, 32 columns each) turn them into bf16 P^T and dS^T = P^T o (dP^T - delta) * scale, written back over
+// the same columns (A operands of dV += P^T dO_c and dK += dS^T Q_c) and, dS^T only, into a shared-memory tile that is the
+// MN-major A operand of dQ_pair += dS_pair K_t (issued once per pair of chunks = 128 queries).  The MMA warp issues the
+// S / dP product of step s + 1 before it waits for the compute warps of step s, so the tensor core and the exponentials
+// overlap.  shared memory: Q | K | V | dO ([lo 128 rows | hi 80 rows] x 128 B each), two dS^T staging tiles (2 query groups x
+// 128 keys x 128 B), per-query statistics of two heads, barriers.
 constexpr int LO_ROWS = 128, HI_ROWS = NP - LO_ROWS;    // 128 + 80
-constexpr int STG_BYTES = 2 * 128 * 128;                 // 32 KB
+constexpr int STG_BYTES = 2 * 128 * 128;                 // one staging tile: 32 KB
 constexpr int BWD_SMEM_TENSORS = 4 * TILE_BYTES;
-// TMEM columns
-constexpr int COL_S = 0, COL_DP = 128, COL_DV = 256, COL_DK = 320, COL_DQ = 384;
+// TMEM columns: buffer b at 128 b: S^T [0,64) dP^T [64,128); accumulators behind
+constexpr int COL_DP = 64, COL_DV = 256, COL_DK = 320, COL_DQ = 384;
 
 struct BwdCtl {
   uint64_t full[3], empty[3];       // input groups: 0 = {K_lo, V_lo}, 1 = {Q_lo, dO_lo}, 2 = {K_hi, V_hi, Q_hi, dO_hi}
-  uint64_t sdp_full, p_ready, stg_free, dvdk_full, dvdk_free, dq_full, dq_free;
+  uint64_t sdp_full[2], p_ready[2], stg_free[2], dvdk_full, dvdk_free, dq_full, dq_free;
+  uint64_t stats_full[2], stats_empty[2];
   uint32_t tmem_base;
 };
 
-__global__ void __launch_bounds__(THREADS, 1) attn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmQKVlo,
+__device__ __forceinline__ float4 lds_v4(const float* p) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+// NC columns (32 or 16) of one key row: p = 2^(s * sl2 + nl_q), ds = p * (dp * scale - delta_q * scale)
+template <int NC>
+__device__ __forceinline__ void bwd_chunk(uint32_t tS, uint32_t tDP, uint32_t tP, uint32_t tDS, const float* nl, const float* dsc, uint8_t* srow,
+                                          int ch0, int krow) {
+  uint32_t sv[NC], dv[NC], pp[NC / 2], dd[NC / 2];
+  if (NC == 32) { tmem_ld32(tS, reinterpret_cast<uint32_t(&)[32]>(sv)); tmem_ld32(tDP, reinterpret_cast<uint32_t(&)[32]>(dv)); }
+  else { tmem_ld16(tS, reinterpret_cast<uint32_t(&)[16]>(sv)); tmem_ld16(tDP, reinterpret_cast<uint32_t(&)[16]>(dv)); }
+  tmem_ld_wait();
+  const float sl2 = SCALE * LOG2E;
+#pragma unroll
+  for (int k = 0; k < NC; k += 4) {
+    // volatile shared loads: issued after the TMEM loads have landed and in program order, so the 2 x NC per-query values
+    // are not all hoisted above the chunk (which spills)
+    const float4 l4 = lds_v4(nl + k);
+    const float4 d4 = lds_v4(dsc + k);
+    const float p0 = ex2_approx(fmaf(__uint_as_float(sv[k]), sl2, l4.x)), p1 = ex2_approx(fmaf(__uint_as_float(sv[k + 1]), sl2, l4.y));
+    const float p2 = ex2_approx(fmaf(__uint_as_float(sv[k + 2]), sl2, l4.z)), p3 = ex2_approx(fmaf(__uint_as_float(sv[k + 3]), sl2, l4.w));
+    pp[k >> 1] = pack_bf16(p0, p1);
+    pp[(k >> 1) + 1] = pack_bf16(p2, p3);
+    dd[k >> 1] = pack_bf16(p0 * fmaf(__uint_as_float(dv[k]), SCALE, -d4.x), p1 * fmaf(__uint_as_float(dv[k + 1]), SCALE, -d4.y));
+    dd[(k >> 1) + 1] = pack_bf16(p2 * fmaf(__uint_as_float(dv[k + 2]), SCALE, -d4.z), p3 * fmaf(__uint_as_float(dv[k + 3]), SCALE, -d4.w));
+  }
+  // packed columns over the first half of what this thread has just read
+  if (NC == 32) { tmem_st16(tP, reinterpret_cast<uint32_t(&)[16]>(pp)); tmem_st16(tDS, reinterpret_cast<uint32_t(&)[16]>(dd)); }
+  else { tmem_st8(tP, reinterpret_cast<uint32_t(&)[8]>(pp)); tmem_st8(tDS, reinterpret_cast<uint32_t(&)[8]>(dd)); }
+  // dS^T staging: row = key, 16 B chunks (8 queries) XOR-swizzled by the row (SWIZZLE_128B)
+#pragma unroll
+  for (int j = 0; j < NC / 8; ++j)
+    *reinterpret_cast<uint4*>(srow + (((ch0 + j) ^ (krow & 7)) << 4)) = make_uint4(dd[4 * j], dd[4 * j + 1], dd[4 * j + 2], dd[4 * j + 3]);
+}
+
+__global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __grid_constant__ CUtensorMap tmQKVlo,
                                                                    const __grid_constant__ CUtensorMap tmQKVhi,
                                                                    const __grid_constant__ CUtensorMap tmDOlo,
                                                                    const __grid_constant__ CUtensorMap tmDOhi,
                                                                    const bf16* __restrict__ o, const bf16* __restrict__ dout,
                                                                    const float* __restrict__ lse, bf16* __restrict__ dqkv,
-                                                                   int N, int H, int total) {
+                                                                   int N, int H, int total, int dbg) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
   uint8_t* sQ = smem;
   uint8_t* sK = smem + TILE_BYTES;
   uint8_t* sV = smem + 2 * TILE_BYTES;
   uint8_t* sDO = smem + 3 * TILE_BYTES;
-  uint8_t* stg = smem + BWD_SMEM_TENSORS;
-  float* s_lse = reinterpret_cast<float*>(stg + STG_BYTES);   // lse * log2(e); padded queries: +big  (=> P = 0)
-  float* s_delta = s_lse + NP;
-  BwdCtl* ctl = reinterpret_cast<BwdCtl*>(s_delta + NP);
+  uint8_t* stg = smem + BWD_SMEM_TENSORS;                               // [2][STG_BYTES]
+  float* stats = reinterpret_cast<float*>(stg + 2 * STG_BYTES);         // [2 heads][2][NP]: -lse * log2(e) | delta * scale
+  uint8_t* wstages = reinterpret_cast<uint8_t*>(stats + 4 * NP);        // 8 x 4 KB: output staging of the compute warps
+  BwdCtl* ctl = reinterpret_cast<BwdCtl*>(wstages + 8 * WSTAGE_BYTES);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int C = H * D, C3 = 3 * C;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKVlo); tma_prefetch_desc(&tmQKVhi); tma_prefetch_desc(&tmDOlo); tma_prefetch_desc(&tmDOhi);
     for (int i = 0; i < 3; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
-    mbar_init(&ctl->sdp_full, 1); mbar_init(&ctl->p_ready, 8); mbar_init(&ctl->stg_free, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->sdp_full[i], 1); mbar_init(&ctl->p_ready[i], 8); mbar_init(&ctl->stg_free[i], 1); }
     mbar_init(&ctl->dvdk_full, 1); mbar_init(&ctl->dvdk_free, 8); mbar_init(&ctl->dq_full, 1); mbar_init(&ctl->dq_free, 8);
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->stats_full[i], 2); mbar_init(&ctl->stats_empty[i], 8); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
@@ -303,6 +402,10 @@ __global__ void __launch_bounds__(THREADS, 1) attn_bwd_umma_kernel(const __grid_
       for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
         const int b = w / H, h = w % H;
         const uint32_t ph = (i & 1) ^ 1;
+        if (dbg & 16) {
+          for (int g = 0; g < 3; ++g) { mbar_wait(&ctl->empty[g], ph); mbar_arrive(&ctl->full[g]); }
+          continue;
+        }
         mbar_wait(&ctl->empty[0], ph);
         mbar_expect_tx(&ctl->full[0], 2 * LO_ROWS * 128);
         tma_load_3d(&tmQKVlo, &ctl->full[0], sK, C + h * D, 0, b);
@@ -313,201 +416,201 @@ __global__ void __launch_bounds__(THREADS, 1) attn_bwd_umma_kernel(const __grid_
         tma_load_3d(&tmDOlo, &ctl->full[1], sDO, h * D, 0, b);
         mbar_wait(&ctl->empty[2], ph);
         mbar_expect_tx(&ctl->full[2], 4 * HI_ROWS * 128);
-        tma_load_3d(&tmQKVhi, &ctl->full[2], sK + LO_ROWS * 128, C + h * D, LO_ROWS, b);
-        tma_load_3d(&tmQKVhi, &ctl->full[2], sV + LO_ROWS * 128, 2 * C + h * D, LO_ROWS, b);
         tma_load_3d(&tmQKVhi, &ctl->full[2], sQ + LO_ROWS * 128, h * D, LO_ROWS, b);
         tma_load_3d(&tmDOhi, &ctl->full[2], sDO + LO_ROWS * 128, h * D, LO_ROWS, b);
+        tma_load_3d(&tmQKVhi, &ctl->full[2], sK + LO_ROWS * 128, C + h * D, LO_ROWS, b);
+        tma_load_3d(&tmQKVhi, &ctl->full[2], sV + LO_ROWS * 128, 2 * C + h * D, LO_ROWS, b);
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     const uint32_t uQ = smem_u32(sQ), uK = smem_u32(sK), uV = smem_u32(sV), uDO = smem_u32(sDO), uStg = smem_u32(stg);
-    int i = 0, step = 0;
-    for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
+    int nheads = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x) ++nheads;
+    const int nsteps = nheads * 8;
+    // S^T / dP^T of step s (head s >> 3, key tile (s >> 2) & 1, chunk s & 3) into TMEM buffer s & 1
+    auto issue_sdp = [&](int s) {
+      const int i = s >> 3, t = (s >> 2) & 1, c = s & 3;
       const uint32_t ph = i & 1;
-      for (int t = 0; t < 2; ++t) {
-        for (int qh = 0; qh < 2; ++qh, ++step) {
-          const int nq = qh ? HI_ROWS : LO_ROWS;       // query columns of this step
-          const int nk = t ? HI_ROWS : LO_ROWS;        // keys that take part in the dQ contraction
-          if (t == 0 && qh == 0) { mbar_wait(&ctl->full[0], ph); mbar_wait(&ctl->full[1], ph); }
-          if (t == 0 && qh == 1) mbar_wait(&ctl->full[2], ph);
-          tc_fence_after();
-          if (elect_one()) {
-            // S^T = K_t Q_qh^T and dP^T = V_t dO_qh^T (M = 128 keys, N = nq queries, K = 64)
-            const uint32_t idesc = make_idesc(128, nq, 0, 0);
-            const uint32_t ak = uK + t * 128 * 128, av = uV + t * 128 * 128, bq = uQ + qh * 128 * 128, bdo = uDO + qh * 128 * 128;
+      if (t == 0 && c == 0) { mbar_wait(&ctl->full[0], ph); mbar_wait(&ctl->full[1], ph); }
+      if (t == 0 && c == 2) mbar_wait(&ctl->full[2], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        const int nq = c == 3 ? 16 : 64;
+        const uint32_t idesc = make_idesc(128, nq, 0, 0);
+        const uint32_t ak = uK + t * 128 * 128, av = uV + t * 128 * 128, bq = uQ + c * 64 * 128, bdo = uDO + c * 64 * 128;
+        const uint32_t tb = tmem_base + (s & 1) * 128;
 #pragma unroll
-            for (int kk = 0; kk < D / 16; ++kk)
-              umma_bf16(tmem_base + COL_S, make_desc(ak + kk * 32, 16, 1024), make_desc(bq + kk * 32, 16, 1024), idesc, kk != 0);
+        for (int kk = 0; kk < D / 16; ++kk)
+          if (!(dbg & 1)) umma_bf16(tb, make_desc(ak + kk * 32, 16, 1024), make_desc(bq + kk * 32, 16, 1024), idesc, kk != 0);
 #pragma unroll
-            for (int kk = 0; kk < D / 16; ++kk)
-              umma_bf16(tmem_base + COL_DP, make_desc(av + kk * 32, 16, 1024), make_desc(bdo + kk * 32, 16, 1024), idesc, kk != 0);
-            umma_commit(&ctl->sdp_full);
-          }
-          __syncwarp();
-          // P^T, dS^T (tensor memory) and dS^T (staging) of this step are complete
-          mbar_wait(&ctl->p_ready, step & 1);
-          if (qh == 0 && (t == 1 || i > 0)) mbar_wait(&ctl->dvdk_free, (2 * i + t - 1) & 1);   // previous key tile's dV / dK read out
-          if (t == 0 && qh == 0 && i > 0) mbar_wait(&ctl->dq_free, (i - 1) & 1);               // previous head's dQ read out
-          tc_fence_after();
-          if (elect_one()) {
-            const uint32_t idesc_kv = make_idesc(128, D, 0, 1);    // A in TMEM (K-major), B = dO / Q rows, MN-major
-            const uint32_t idesc_q = make_idesc(128, D, 1, 1);     // A = dS^T staging (MN-major), B = K rows (MN-major)
-            const int n0 = nq == LO_ROWS ? 64 : 48;                // columns owned by the first compute warp group
-            for (int kk = 0; kk < nq / 16; ++kk) {
-              const int qc = kk * 16;                               // query offset inside this half
-              const uint32_t acol = qc < n0 ? (qc >> 1) : n0 + ((qc - n0) >> 1);   // where that group put its packed columns
-              umma_bf16_ts(tmem_base + COL_DV, tmem_base + COL_S + acol, make_desc(uDO + (qh * 128 + qc) * 128, TILE_BYTES, 1024), idesc_kv,
-                           (qh | kk) != 0);
+        for (int kk = 0; kk < D / 16; ++kk)
+          if (!(dbg & 1)) umma_bf16(tb + COL_DP, make_desc(av + kk * 32, 16, 1024), make_desc(bdo + kk * 32, 16, 1024), idesc, kk != 0);
+        umma_commit(&ctl->sdp_full[s & 1]);
+      }
+      __syncwarp();
+    };
+    if (nsteps > 0) issue_sdp(0);
+    for (int s = 0; s < nsteps; ++s) {
+      if (s + 1 < nsteps) issue_sdp(s + 1);      // runs on the tensor core while the compute warps work on step s
+      const int i = s >> 3, t = (s >> 2) & 1, c = s & 3;
+      mbar_wait(&ctl->p_ready[s & 1], (s >> 1) & 1);
+      if (c == 0 && (2 * i + t) > 0) mbar_wait(&ctl->dvdk_free, (2 * i + t - 1) & 1);   // previous key tile's dV / dK read out
+      if (t == 0 && c == 1 && i > 0) mbar_wait(&ctl->dq_free, (i - 1) & 1);             // previous head's dQ read out
+      tc_fence_after();
+      if (elect_one()) {
+        const int nq = c == 3 ? 16 : 64;
+        const uint32_t idesc_kv = make_idesc(128, D, 0, 1);    // A in TMEM (K-major), B = dO / Q rows, MN-major
+        const uint32_t tb = tmem_base + (s & 1) * 128;
+        for (int kk = 0; kk < nq / 16 && !(dbg & 2); ++kk) {
+          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;   // warp group kk >> 1 packed its 32 columns into 16
+          umma_bf16_ts(tmem_base + COL_DV, tb + acol, make_desc(uDO + (c * 64 + kk * 16) * 128, TILE_BYTES, 1024), idesc_kv, (c | kk) != 0);
+        }
+        for (int kk = 0; kk < nq / 16 && !(dbg & 2); ++kk) {
+          const uint32_t acol = (kk >> 1) * 32 + (kk & 1) * 8;
+          umma_bf16_ts(tmem_base + COL_DK, tb + COL_DP + acol, make_desc(uQ + (c * 64 + kk * 16) * 128, TILE_BYTES, 1024), idesc_kv, (c | kk) != 0);
+        }
+        if (c & 1) {
+          // dQ of this pair of chunks (128 queries): A = dS^T staging tile (MN-major), B = K rows of the key tile (MN-major)
+          const uint32_t idesc_q = make_idesc(128, D, 1, 1);
+          const int pair = c >> 1, nk = t ? HI_ROWS : LO_ROWS;
+          const int sb = (4 * i + 2 * t + pair) & 1;
+          for (int kk = 0; kk < nk / 16 && !(dbg & 4); ++kk)
+            umma_bf16(tmem_base + COL_DQ + pair * 64, make_desc(uStg + sb * STG_BYTES + kk * 2048, 128 * 128, 1024),
+                      make_desc(uK + (t * 128 + kk * 16) * 128, TILE_BYTES, 1024), idesc_q, (t | kk) != 0);
+          umma_commit(&ctl->stg_free[sb]);
+        }
+        if (c == 3) umma_commit(&ctl->dvdk_full);
+        if (t == 1 && c == 3) umma_commit(&ctl->dq_full);
+        // input groups whose last reader has been issued
+        if (t == 0 && c == 3) umma_commit(&ctl->empty[0]);
+        if (t == 1 && c == 1) umma_commit(&ctl->empty[1]);
+        if (t == 1 && c == 3) umma_commit(&ctl->empty[2]);
+      }
+      __syncwarp();
+    }
+  } else if (warp >= 10) {
+    // ------------------------------------------------------------------ statistics warps: one head ahead of the compute warps
+    // per query: delta_i = sum_d dO[i,d] O[i,d] (8 lanes per row, coalesced 16 B loads) and lse_i, pre-scaled
+    const int stid = threadIdx.x - 320;    // 0..63
+    const int sub = stid & 7;
+    int i = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
+      const int slot = i & 1;
+      mbar_wait(&ctl->stats_empty[slot], ((i >> 1) & 1) ^ 1);
+      const int b = w / H, h = w % H;
+      const bf16* dob = dout + (long long)b * N * C + h * D;
+      const bf16* ob = o + (long long)b * N * C + h * D;
+      float* nl = stats + slot * 2 * NP;
+      float* dsc = nl + NP;
+      if (!(dbg & 32)) {
+        // two batches of 13 rows per 8-lane group: all 26 16 B loads of a batch are in flight together
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          uint4 xr[13], yr[13];
+#pragma unroll
+          for (int it = 0; it < 13; ++it) {
+            const int r = (half * 13 + it) * 8 + (stid >> 3);
+            xr[it] = yr[it] = make_uint4(0, 0, 0, 0);
+            if (r < N) {
+              xr[it] = *reinterpret_cast<const uint4*>(dob + (long long)r * C + sub * 8);
+              yr[it] = *reinterpret_cast<const uint4*>(ob + (long long)r * C + sub * 8);
             }
-            for (int kk = 0; kk < nq / 16; ++kk) {
-              const int qc = kk * 16;
-              const uint32_t acol = qc < n0 ? (qc >> 1) : n0 + ((qc - n0) >> 1);
-              umma_bf16_ts(tmem_base + COL_DK, tmem_base + COL_DP + acol, make_desc(uQ + (qh * 128 + qc) * 128, TILE_BYTES, 1024), idesc_kv,
-                           (qh | kk) != 0);
-            }
-            for (int kk = 0; kk < nk / 16; ++kk)
-              umma_bf16(tmem_base + COL_DQ + qh * 64, make_desc(uStg + kk * 2048, 128 * 128, 1024),
-                        make_desc(uK + (t * 128 + kk * 16) * 128, TILE_BYTES, 1024), idesc_q, (t | kk) != 0);
-            umma_commit(&ctl->stg_free);
-            if (qh == 1) umma_commit(&ctl->dvdk_full);
-            if (t == 1 && qh == 1) umma_commit(&ctl->dq_full);
-            // input groups whose last reader has been issued
-            if (t == 0 && qh == 1) umma_commit(&ctl->empty[0]);
-            if (t == 1 && qh == 0) umma_commit(&ctl->empty[1]);
-            if (t == 1 && qh == 1) umma_commit(&ctl->empty[2]);
           }
-          __syncwarp();
+#pragma unroll
+          for (int it = 0; it < 13; ++it) {
+            const int r = (half * 13 + it) * 8 + (stid >> 3);
+            const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xr[it]);
+            const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&yr[it]);
+            float acc = 0.f;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 a = __bfloat1622float2(xh[e]), c2 = __bfloat1622float2(yh[e]);
+              acc = fmaf(a.x, c2.x, acc);
+              acc = fmaf(a.y, c2.y, acc);
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if (sub == 0) {
+              dsc[r] = acc * SCALE;
+              nl[r] = r < N ? -lse[((long long)b * H + h) * N + r] * LOG2E : -1e30f;   // padded queries: P = 0
+            }
+          }
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->stats_full[slot]);
     }
   } else {
     // ------------------------------------------------------------------ compute warps: thread = key row (TMEM lane)
     const int wg = (warp - 2) >> 2;
     const int q = warp & 3;
-    const int ctid = threadIdx.x - 64;     // 0..255
+    const int krow = q * 32 + lane;        // key row inside the tile
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    const float sl2 = SCALE * LOG2E;
-    int i = 0, step = 0;
+    uint8_t* wstage = wstages + (warp - 2) * WSTAGE_BYTES;
+    int i = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
       const int b = w / H, h = w % H;
-      // per-query statistics of this head: delta_i = sum_d dO[i,d] O[i,d] (straight from global memory), lse_i * log2(e)
-      asm volatile("bar.sync 1, 256;" ::: "memory");   // every compute warp is done with the previous head's statistics
-      {
-        const bf16* dob = dout + (long long)b * N * C + h * D;
-        const bf16* ob = o + (long long)b * N * C + h * D;
-        for (int r = ctid; r < NP; r += 256) {
-          float acc = 0.f;
-          if (r < N) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              Vec8<bf16> x, y;
-              x.load(dob + (long long)r * C + k * 8);
-              y.load(ob + (long long)r * C + k * 8);
-#pragma unroll
-              for (int e = 0; e < 8; ++e) acc += x.v[e] * y.v[e];
-            }
-          }
-          s_delta[r] = acc;
-          s_lse[r] = r < N ? lse[((long long)b * H + h) * N + r] * LOG2E : 1e30f;
-        }
-      }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(&ctl->stats_full[i & 1], (i >> 1) & 1);   // this head's statistics (written by warps 10-11 during the previous head)
+      const float* nl = stats + (i & 1) * 2 * NP;
+      const float* dsc = nl + NP;
       for (int t = 0; t < 2; ++t) {
         const bool warp_active = t * 128 + q * 32 < NP;    // key rows of this warp exist in shared memory (incl. zero padding)
-        const int krow = q * 32 + lane;                     // key row inside the tile
-        for (int qh = 0; qh < 2; ++qh, ++step) {
-          const int nq = qh ? HI_ROWS : LO_ROWS;
-          const int n0 = nq == LO_ROWS ? 64 : 48;
-          const int c_begin = wg ? n0 : 0, c_end = wg ? nq : n0;
-          mbar_wait(&ctl->sdp_full, step & 1);
-          if (step > 0) mbar_wait(&ctl->stg_free, (step - 1) & 1);   // the previous step's dQ MMAs have read the staging tile
+        for (int c = 0; c < 4; ++c) {
+          const int s = i * 8 + t * 4 + c;
+          const int pair = 4 * i + 2 * t + (c >> 1), sb = pair & 1;
+          mbar_wait(&ctl->sdp_full[s & 1], (s >> 1) & 1);
+          if (!(c & 1) && pair >= 2) mbar_wait(&ctl->stg_free[sb], ((pair >> 1) - 1) & 1);   // the dQ MMAs that read this staging tile are done
           tc_fence_after();
-          if (warp_active) {
+          if (warp_active && !(dbg & 8)) {
+            const uint32_t tb = tmem_base + lane_off + (s & 1) * 128 + wg * 32;
+            uint8_t* srow = stg + sb * STG_BYTES + (c & 1) * (128 * 128) + krow * 128;
+            const int q0 = c * 64 + wg * 32;
+            // 16 columns at a time (keeps the live register set small): half h reads columns [16 h, +16) of this warp's 32 and
+            // packs them into columns [8 h, +8) -- already read
+            if (c < 3) {
 #pragma unroll 1
-            for (int c0 = c_begin; c0 < c_end; c0 += 16) {
-              uint32_t sv[16], dv[16], pp[8], ds[8];
-              tmem_ld16(tmem_base + lane_off + COL_S + c0, sv);
-              tmem_ld16(tmem_base + lane_off + COL_DP + c0, dv);
-              tmem_ld_wait();
-              const int qi = qh * 128 + c0;   // global query index of column c0
-#pragma unroll
-              for (int k = 0; k < 16; k += 4) {
-                const float4 l4 = *reinterpret_cast<const float4*>(s_lse + qi + k);
-                const float4 d4 = *reinterpret_cast<const float4*>(s_delta + qi + k);
-                const float p0 = ex2_approx(fmaf(__uint_as_float(sv[k]), sl2, -l4.x)), p1 = ex2_approx(fmaf(__uint_as_float(sv[k + 1]), sl2, -l4.y));
-                const float p2 = ex2_approx(fmaf(__uint_as_float(sv[k + 2]), sl2, -l4.z)), p3 = ex2_approx(fmaf(__uint_as_float(sv[k + 3]), sl2, -l4.w));
-                pp[k >> 1] = pack_bf16(p0, p1);
-                pp[(k >> 1) + 1] = pack_bf16(p2, p3);
-                ds[k >> 1] = pack_bf16(p0 * (__uint_as_float(dv[k]) - d4.x) * SCALE, p1 * (__uint_as_float(dv[k + 1]) - d4.y) * SCALE);
-                ds[(k >> 1) + 1] = pack_bf16(p2 * (__uint_as_float(dv[k + 2]) - d4.z) * SCALE, p3 * (__uint_as_float(dv[k + 3]) - d4.w) * SCALE);
-              }
-              // packed columns go to this warp group's own part of the S / dP regions (already read by this thread)
-              const uint32_t pc = c_begin + ((c0 - c_begin) >> 1);
-              tmem_st8(tmem_base + lane_off + COL_S + pc, pp);
-              tmem_st8(tmem_base + lane_off + COL_DP + pc, ds);
-              // dS^T staging: row = key, 64-query groups 16 KB apart, 16 B chunks XOR-swizzled by the row (SWIZZLE_128B)
-              uint8_t* srow = stg + (c0 >> 6) * (128 * 128) + krow * 128;
-              const int ch = (c0 & 63) >> 3;
-              *reinterpret_cast<uint4*>(srow + (((ch) ^ (krow & 7)) << 4)) = make_uint4(ds[0], ds[1], ds[2], ds[3]);
-              *reinterpret_cast<uint4*>(srow + (((ch + 1) ^ (krow & 7)) << 4)) = make_uint4(ds[4], ds[5], ds[6], ds[7]);
+              for (int hf = 0; hf < 2; ++hf)
+                bwd_chunk<16>(tb + hf * 16, tb + COL_DP + hf * 16, tb + hf * 8, tb + COL_DP + hf * 8, nl + q0 + hf * 16, dsc + q0 + hf * 16, srow,
+                              wg * 4 + hf * 2, krow);
+            } else if (wg == 0) {
+              bwd_chunk<16>(tb, tb + COL_DP, tb, tb + COL_DP, nl + q0, dsc + q0, srow, 0, krow);
             }
             tmem_st_wait();
           }
           fence_proxy_async();   // the staging stores must be visible to the tensor core's (async proxy) reads
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&ctl->p_ready);
-          if (qh == 1) {
+          if (lane == 0) mbar_arrive(&ctl->p_ready[s & 1]);
+          if (t == 1 && c == 3 && lane == 0) mbar_arrive(&ctl->stats_empty[i & 1]);   // last reader of this head's statistics
+          if (c == 3) {
             // dV (warp group 0) / dK (warp group 1) of key tile t
             mbar_wait(&ctl->dvdk_full, (2 * i + t) & 1);
             tc_fence_after();
-            uint32_t acc[2][32];
-            if (warp_active) {
-              tmem_ld32(tmem_base + lane_off + (wg ? COL_DK : COL_DV), acc[0]);
-              tmem_ld32(tmem_base + lane_off + (wg ? COL_DK : COL_DV) + 32, acc[1]);
-              tmem_ld_wait();
-            }
+            uint4 acc[8];
+            if (warp_active) read_row64(tmem_base + lane_off + (wg ? COL_DK : COL_DV), acc, 1.f);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl->dvdk_free);
             const int key = t * 128 + krow;
-            if (warp_active && key < N) {
-              bf16* dst = dqkv + ((long long)b * N + key) * C3 + (wg ? C : 2 * C) + h * D;
-#pragma unroll
-              for (int g = 0; g < 8; ++g) {
-                const uint32_t* a = acc[g >> 2] + (g & 3) * 8;
-                *reinterpret_cast<uint4*>(dst + g * 8) =
-                    make_uint4(pack_bf16(__uint_as_float(a[0]), __uint_as_float(a[1])), pack_bf16(__uint_as_float(a[2]), __uint_as_float(a[3])),
-                               pack_bf16(__uint_as_float(a[4]), __uint_as_float(a[5])), pack_bf16(__uint_as_float(a[6]), __uint_as_float(a[7])));
-              }
-            }
+            (void)key;
+            if (warp_active && !(dbg & 64))
+              store_rows_staged(wstage, dqkv + (long long)b * N * C3 + (wg ? C : 2 * C) + h * D, C3, t * 128 + q * 32, N, acc, lane);
           }
-          if (t == 1 && qh == 1) {
+          if (t == 1 && c == 3) {
             // dQ: warp group g reads query tile g
             mbar_wait(&ctl->dq_full, i & 1);
             tc_fence_after();
             const bool rows_here = wg * 128 + q * 32 < N;
-            uint32_t acc[2][32];
-            if (rows_here) {
-              tmem_ld32(tmem_base + lane_off + COL_DQ + wg * 64, acc[0]);
-              tmem_ld32(tmem_base + lane_off + COL_DQ + wg * 64 + 32, acc[1]);
-              tmem_ld_wait();
-            }
+            uint4 acc[8];
+            if (rows_here) read_row64(tmem_base + lane_off + COL_DQ + wg * 64, acc, 1.f);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl->dq_free);
-            const int qrow = wg * 128 + q * 32 + lane;
-            if (rows_here && qrow < N) {
-              bf16* dst = dqkv + ((long long)b * N + qrow) * C3 + h * D;
-#pragma unroll
-              for (int g = 0; g < 8; ++g) {
-                const uint32_t* a = acc[g >> 2] + (g & 3) * 8;
-                *reinterpret_cast<uint4*>(dst + g * 8) =
-                    make_uint4(pack_bf16(__uint_as_float(a[0]), __uint_as_float(a[1])), pack_bf16(__uint_as_float(a[2]), __uint_as_float(a[3])),
-                               pack_bf16(__uint_as_float(a[4]), __uint_as_float(a[5])), pack_bf16(__uint_as_float(a[6]), __uint_as_float(a[7])));
-              }
-            }
+            const int qrow = wg * 128 + krow;
+            (void)qrow;
+            if (rows_here && !(dbg & 64)) store_rows_staged(wstage, dqkv + (long long)b * N * C3 + h * D, C3, wg * 128 + q * 32, N, acc, lane);
           }
         }
       }
@@ -528,6 +631,12 @@ int make_rows_map(CUtensorMap* map, const bf16* base, int cols, int N, int B, in
 
 }  // namespace
 
+// S4G_ATTN_DBG (timing experiments only; results are wrong): forward 1 = no P V MMAs, 2 = no S MMAs, 4 = no softmax;
+// backward 1 = no S / dP MMAs, 2 = no dV / dK MMAs, 4 = no dQ MMAs, 8 = no elementwise pass
+static int attn_dbg() {
+  static const int v = getenv("S4G_ATTN_DBG") ? atoi(getenv("S4G_ATTN_DBG")) : 0;
+  return v;
+}
 static int attn_umma_grid(int total) {
   const int sms = umma_num_sms();
   return total < sms ? total : sms;
@@ -537,10 +646,10 @@ int attn_fwd_umma(const bf16* qkv, bf16* o, float* lse, int B, int N, int H, cud
   if (N > NP || N < 1) { s4g_set_error("attn_fwd_umma: specialised for sequences of at most 208 tokens"); return S4G_ERR_SHAPE; }
   CUtensorMap tm;
   S4G_TRY(make_rows_map(&tm, qkv, 3 * H * D, N, B, FWD_HALF_ROWS));
-  const size_t smem = 1024 + FWD_STAGES * FWD_STAGE_BYTES + sizeof(FwdCtl);
+  const size_t smem = 1024 + FWD_STAGES * FWD_STAGE_BYTES + TILE_BYTES + 8 * WSTAGE_BYTES + sizeof(FwdCtl);
   static bool attr = false;
   if (!attr) { S4G_CUDA(cudaFuncSetAttribute(attn_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  S4G_CUDA(launch_dep(attn_fwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(THREADS), smem, st, tm, o, lse, N, H, B * H));
+  S4G_CUDA(launch_dep(attn_fwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(THREADS), smem, st, tm, o, lse, N, H, B * H, attn_dbg()));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -553,11 +662,11 @@ int attn_bwd_umma(const bf16* qkv, const bf16* o, const bf16* dout, const float*
   S4G_TRY(make_rows_map(&qhi, qkv, 3 * H * D, N, B, HI_ROWS));
   S4G_TRY(make_rows_map(&dlo, dout, H * D, N, B, LO_ROWS));
   S4G_TRY(make_rows_map(&dhi, dout, H * D, N, B, HI_ROWS));
-  const size_t smem = 1024 + BWD_SMEM_TENSORS + STG_BYTES + 2 * NP * sizeof(float) + sizeof(BwdCtl);
+  const size_t smem = 1024 + BWD_SMEM_TENSORS + 2 * STG_BYTES + 4 * NP * sizeof(float) + 8 * WSTAGE_BYTES + sizeof(BwdCtl);
   static bool attr = false;
   if (!attr) { S4G_CUDA(cudaFuncSetAttribute(attn_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  S4G_CUDA(launch_dep(attn_bwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(THREADS), smem, st, qlo, qhi, dlo, dhi, o, dout, lse, dqkv, N, H,
-                      B * H));
+  S4G_CUDA(launch_dep(attn_bwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(BWD_THREADS), smem, st, qlo, qhi, dlo, dhi, o, dout, lse, dqkv, N, H,
+                      B * H, attn_dbg()));
   S4G_KERNEL_CHECK();
   return 0;
 }
