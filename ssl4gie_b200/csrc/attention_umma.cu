@@ -5,15 +5,14 @@
 // The whole key range of a head fits one MMA (N = 208 = 197 padded to 13 x 16), so the softmax is single pass: no running
 // maximum, no rescaling of the output accumulator.
 //
-// forward, one persistent CTA per SM, 10 warps:
+// forward, one persistent CTA per SM, 12 warps (warp 3 idle):
 //   warp 0      TMA producer: Q, K, V of the next (image, head) into a 2-stage ring (3-D tensor map over qkv, the rows
 //               197..207 of every box are out of bounds and arrive as zeros)
-//   warp 1      MMA issuer: S_t = Q_t K^T (M = 128 query rows, N = 208, K = 64) into TMEM slot t, then O_t = P_t V with
+//   warps 1-2   MMA issuers, one per query tile t: S_t = Q_t K^T (M = 128 query rows, N = 208, K = 64) into TMEM slot t, then O_t = P_t V with
 //               P_t read straight from tensor memory (A operand in TMEM) and V as an MN-major B operand
-//   warps 2-5   softmax + epilogue of query tile 0 (rows 0..127), warps 6-9 of query tile 1 (rows 128..196): a thread owns
+//   warps 4-11  softmax + epilogue: 4-7 query tile 0 (rows 0..127), 8-11 query tile 1 (rows 128..196): a thread owns
 //               one query row (= one TMEM lane): row max, exp2, row sum, bf16 P written over the first half of S,
-//               later O / sum -> global.  The two tiles run half a phase apart, so the MMAs of one overlap the exponentials
-//               of the other.
+//               later O / sum -> global.
 // backward, one persistent CTA per SM, same warp roles, keys on the TMEM lanes (S^T = K Q^T, dP^T = V dO^T), so that P^T and
 // dS^T are A operands in tensor memory for dV = P^T dO and dK = dS^T Q; dS^T additionally goes through a 32 KB shared
 // memory tile as the MN-major A operand of dQ = dS K.  Four steps per head (2 key tiles x 2 query halves), accumulators
@@ -35,8 +34,14 @@ constexpr int NP = 208;                  // tokens padded to 13 x 16
 constexpr int TILE_BYTES = NP * 128;     // one of Q / K / V / dO in shared memory: rows of 128 B, SWIZZLE_128B
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float SCALE = 0.125f;          // 64^-0.5
-constexpr int THREADS = 320;             // forward: warp 0 TMA, warp 1 MMA, warps 2-9 compute (ptxas allocates for 384: 168 registers)
+constexpr int THREADS = 384;             // forward: warp 0 TMA, warps 1-2 MMA (one per query tile), warp 3 idle, warps 4-11 softmax
 constexpr int BWD_THREADS = 384;         // backward: + warps 10-11, the per-query statistics of the next head
+
+// Named barriers carry the compute-warp -> issuing-warp signals (a hardware barrier resolves in tens of cycles; an mbarrier
+// round trip costs several hundred): the producers arrive without waiting, the consumer warp syncs.  Signals from the
+// tensor core / TMA (tcgen05.commit, complete_tx) can only be mbarriers.
+__device__ __forceinline__ void nbar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void nbar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 
 __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
   return reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(p) + 1023) & ~(uintptr_t)1023);
@@ -90,9 +95,11 @@ constexpr int O_COL = 128;
 constexpr int O_N = D + 16;                              // O = P [V | 1 0 ... 0]: column 64 of the product is the row sum of P
 
 struct FwdCtl {
-  uint64_t full[FWD_STAGES], empty[FWD_STAGES], s_full[2], p_full[2], o_full[2], slot_free[2];
+  uint64_t full[FWD_STAGES], empty[FWD_STAGES], s_full[2], o_full[2];
   uint32_t tmem_base;
 };
+// named barriers: P of tile t written (softmax warps of the tile -> its MMA warp), O of tile t read out
+constexpr int FWD_BAR_P = 2, FWD_BAR_FREE = 4, FWD_BAR_COUNT = 128 + 32;
 
 // 32 scores -> 16 packed bf16 pairs of p = 2^(s * sl2 + nb); `valid` = number of real key columns in this chunk
 template <bool MASKED>
@@ -117,10 +124,8 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
-    for (int i = 0; i < FWD_STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(&ctl->s_full[i], 1); mbar_init(&ctl->p_full[i], 4); mbar_init(&ctl->o_full[i], 1); mbar_init(&ctl->slot_free[i], 4);
-    }
+    for (int i = 0; i < FWD_STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 2); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->s_full[i], 1); mbar_init(&ctl->o_full[i], 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
@@ -155,51 +160,47 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
             tma_load_3d(&tmQKV, &ctl->full[stage], s + t * TILE_BYTES + half * FWD_HALF_ROWS * 128, t * C + h * D, half * FWD_HALF_ROWS, b);
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
+  } else if (warp == 1 || warp == 2) {
+    // ------------------------------------------------------------------ MMA issuer of query tile t = warp - 1
+    // (one issuing warp per tile: neither tile's hand-shakes wait behind the other's.  Measured alternatives: one warp
+    // serving both tiles in a fixed order -- same speed; issuing S_t only when the other tile's softmax is done, so that the
+    // two groups alternate on the exponential unit -- 30 % slower: one softmax warp per scheduler cannot hide its own
+    // TMEM-load latency, two can.)
+    const int t = warp - 1;
     const uint32_t idesc_s = make_idesc(128, NP, 0, 0);     // S = Q K^T: both operands K-major
     const uint32_t idesc_o = make_idesc(128, O_N, 0, 1);    // O = P [V | 1]: A in TMEM, B MN-major (rows = keys)
     const uint32_t u_ones = smem_u32(ones);
-    // O_t of head ip: needs P_t complete; the last reader of the head's shared memory stage
-    auto issue_pv = [&](int ip, int t) {
-      mbar_wait(&ctl->p_full[t], ip & 1);
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t sv = smem_u32(smem + (ip & 1) * FWD_STAGE_BYTES + 2 * TILE_BYTES);
-        const uint32_t slot = tmem_base + t * SLOT_COLS;
-#pragma unroll
-        for (int kk = 0; kk < NP / 16; ++kk)
-          if (!(dbg & 1)) umma_bf16_ts(slot + O_COL, slot + kk * 8, make_desc(sv + kk * 2048, u_ones - sv, 1024), idesc_o, kk != 0);
-        umma_commit(&ctl->o_full[t]);
-        if (t == 1) umma_commit(&ctl->empty[ip & 1]);
-      }
-      __syncwarp();
-    };
+    const uint32_t slot = tmem_base + t * SLOT_COLS;
     int i = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
       const int stage = i & 1;
       mbar_wait(&ctl->full[stage], (i >> 1) & 1);
       tc_fence_after();
-      for (int t = 0; t < 2; ++t) {
-        mbar_wait(&ctl->slot_free[t], (i & 1) ^ 1);   // the epilogue of the previous head has read O_t out of this slot
-        tc_fence_after();
-        if (elect_one()) {
-          const uint32_t sq = smem_u32(smem + stage * FWD_STAGE_BYTES) + t * 128 * 128;
-          const uint32_t sk = smem_u32(smem + stage * FWD_STAGE_BYTES + TILE_BYTES);
+      if (elect_one()) {
+        const uint32_t sq = smem_u32(smem + stage * FWD_STAGE_BYTES) + t * 128 * 128;
+        const uint32_t sk = smem_u32(smem + stage * FWD_STAGE_BYTES + TILE_BYTES);
 #pragma unroll
-          for (int kk = 0; kk < D / 16; ++kk)
-            if (!(dbg & 2)) umma_bf16(tmem_base + t * SLOT_COLS, make_desc(sq + kk * 32, 16, 1024), make_desc(sk + kk * 32, 16, 1024), idesc_s, kk != 0);
-          umma_commit(&ctl->s_full[t]);
-        }
-        __syncwarp();
-        // the P V product of the job issued before this one (tile 1 of the previous head, or tile 0 of this head)
-        if (t == 0) { if (i > 0) issue_pv(i - 1, 1); } else issue_pv(i, 0);
+        for (int kk = 0; kk < D / 16; ++kk)
+          if (!(dbg & 2)) umma_bf16(slot, make_desc(sq + kk * 32, 16, 1024), make_desc(sk + kk * 32, 16, 1024), idesc_s, kk != 0);
+        umma_commit(&ctl->s_full[t]);
       }
+      __syncwarp();
+      nbar_sync(FWD_BAR_P + t, FWD_BAR_COUNT);      // P_t is in tensor memory
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sv = smem_u32(smem + stage * FWD_STAGE_BYTES + 2 * TILE_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < NP / 16; ++kk)
+          if (!(dbg & 1)) umma_bf16_ts(slot + O_COL, slot + kk * 8, make_desc(sv + kk * 2048, u_ones - sv, 1024), idesc_o, kk != 0);
+        umma_commit(&ctl->o_full[t]);
+        umma_commit(&ctl->empty[stage]);            // both tiles' products release the stage
+      }
+      __syncwarp();
+      nbar_sync(FWD_BAR_FREE + t, FWD_BAR_COUNT);   // O_t has been read out: the slot may take the next head's S
     }
-    if (i > 0) issue_pv(i - 1, 1);
-  } else {
-    // ------------------------------------------------------------------ softmax + epilogue: warps 2-5 tile 0, 6-9 tile 1
-    const int t = (warp - 2) >> 2;
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ softmax + epilogue: warps 4-7 tile 0, 8-11 tile 1
+    const int t = (warp - 4) >> 2;
     const int q = warp & 3;                    // TMEM lane quarter this warp may touch
     const int row = t * 128 + q * 32 + lane;   // query row of this thread
     const bool warp_active = t * 128 + q * 32 < N;
@@ -273,8 +274,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
         tmem_st_wait();
       }
       tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->p_full[t]);
+      nbar_arrive(FWD_BAR_P + t, FWD_BAR_COUNT);
       // epilogue: O / sum -> bf16 -> global; the row sum is column 64 of the product (the sum of the bf16 P the MMA used)
       mbar_wait(&ctl->o_full[t], i & 1);
       tc_fence_after();
@@ -288,10 +288,9 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
         read_row64(taddr + O_COL, acc, 1.f / sum);
       }
       tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->slot_free[t]);   // the slot may take the next head's S while the stores drain
+      nbar_arrive(FWD_BAR_FREE + t, FWD_BAR_COUNT);   // the slot may take the next head's S while the stores drain
       if (warp_active && !(dbg & 16)) {
-        store_rows_staged(wstages + (warp - 2) * WSTAGE_BYTES, o + (long long)b * N * C + h * D, C, t * 128 + q * 32, N, acc, lane);
+        store_rows_staged(wstages + (warp - 4) * WSTAGE_BYTES, o + (long long)b * N * C + h * D, C, t * 128 + q * 32, N, acc, lane);
         if (row < N) lse[((long long)b * H + h) * N + row] = mx * SCALE + logf(sum);
       }
     }
@@ -318,10 +317,14 @@ constexpr int COL_DP = 64, COL_DV = 256, COL_DK = 320, COL_DQ = 384;
 
 struct BwdCtl {
   uint64_t full[3], empty[3];       // input groups: 0 = {K_lo, V_lo}, 1 = {Q_lo, dO_lo}, 2 = {K_hi, V_hi, Q_hi, dO_hi}
-  uint64_t sdp_full[2], p_ready[2], stg_free[2], dvdk_full, dvdk_free, dq_full, dq_free;
-  uint64_t stats_full[2], stats_empty[2];
+  uint64_t sdp_full[2], stg_free[2], dvdk_full, dq_full;   // tensor-core completions
+  uint64_t stats_full[2];
   uint32_t tmem_base;
 };
+// named barriers (compute warps arrive, the consumer warp syncs): P^T / dS^T of TMEM buffer b complete, dV / dK read out,
+// dQ read out (-> MMA warp); statistics slot released (-> statistics warps)
+constexpr int BWD_BAR_P = 2, BWD_BAR_DVDK = 4, BWD_BAR_DQ = 5, BWD_BAR_STATS = 6;
+constexpr int BWD_COUNT_MMA = 256 + 32, BWD_COUNT_STATS = 256 + 64;
 
 __device__ __forceinline__ float4 lds_v4(const float* p) {
   float4 v;
@@ -382,9 +385,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKVlo); tma_prefetch_desc(&tmQKVhi); tma_prefetch_desc(&tmDOlo); tma_prefetch_desc(&tmDOhi);
     for (int i = 0; i < 3; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->sdp_full[i], 1); mbar_init(&ctl->p_ready[i], 8); mbar_init(&ctl->stg_free[i], 1); }
-    mbar_init(&ctl->dvdk_full, 1); mbar_init(&ctl->dvdk_free, 8); mbar_init(&ctl->dq_full, 1); mbar_init(&ctl->dq_free, 8);
-    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->stats_full[i], 2); mbar_init(&ctl->stats_empty[i], 8); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->sdp_full[i], 1); mbar_init(&ctl->stg_free[i], 1); mbar_init(&ctl->stats_full[i], 2); }
+    mbar_init(&ctl->dvdk_full, 1); mbar_init(&ctl->dq_full, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&ctl->tmem_base, 512);
@@ -454,9 +456,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
     for (int s = 0; s < nsteps; ++s) {
       if (s + 1 < nsteps) issue_sdp(s + 1);      // runs on the tensor core while the compute warps work on step s
       const int i = s >> 3, t = (s >> 2) & 1, c = s & 3;
-      mbar_wait(&ctl->p_ready[s & 1], (s >> 1) & 1);
-      if (c == 0 && (2 * i + t) > 0) mbar_wait(&ctl->dvdk_free, (2 * i + t - 1) & 1);   // previous key tile's dV / dK read out
-      if (t == 0 && c == 1 && i > 0) mbar_wait(&ctl->dq_free, (i - 1) & 1);             // previous head's dQ read out
+      nbar_sync(BWD_BAR_P + (s & 1), BWD_COUNT_MMA);
+      if (c == 0 && (2 * i + t) > 0) nbar_sync(BWD_BAR_DVDK, BWD_COUNT_MMA);   // previous key tile's dV / dK read out
+      if (t == 0 && c == 1 && i > 0) nbar_sync(BWD_BAR_DQ, BWD_COUNT_MMA);     // previous head's dQ read out
       tc_fence_after();
       if (elect_one()) {
         const int nq = c == 3 ? 16 : 64;
@@ -489,6 +491,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
       }
       __syncwarp();
     }
+    if (nsteps > 0) { nbar_sync(BWD_BAR_DVDK, BWD_COUNT_MMA); nbar_sync(BWD_BAR_DQ, BWD_COUNT_MMA); }   // the last read-outs' arrivals
   } else if (warp >= 10) {
     // ------------------------------------------------------------------ statistics warps: one head ahead of the compute warps
     // per query: delta_i = sum_d dO[i,d] O[i,d] (8 lanes per row, coalesced 16 B loads) and lse_i, pre-scaled
@@ -497,7 +500,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
     int i = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
       const int slot = i & 1;
-      mbar_wait(&ctl->stats_empty[slot], ((i >> 1) & 1) ^ 1);
+      if (i >= 2) nbar_sync(BWD_BAR_STATS + slot, BWD_COUNT_STATS);   // the compute warps are done with head i - 2
       const int b = w / H, h = w % H;
       const bf16* dob = dout + (long long)b * N * C + h * D;
       const bf16* ob = o + (long long)b * N * C + h * D;
@@ -508,13 +511,17 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
 #pragma unroll 1
         for (int half = 0; half < 2; ++half) {
           uint4 xr[13], yr[13];
+          float lv[13];
+          const float* lrow = lse + ((long long)b * H + h) * N;
 #pragma unroll
           for (int it = 0; it < 13; ++it) {
             const int r = (half * 13 + it) * 8 + (stid >> 3);
             xr[it] = yr[it] = make_uint4(0, 0, 0, 0);
+            lv[it] = 1e30f / LOG2E;   // padded queries: P = 0
             if (r < N) {
               xr[it] = *reinterpret_cast<const uint4*>(dob + (long long)r * C + sub * 8);
               yr[it] = *reinterpret_cast<const uint4*>(ob + (long long)r * C + sub * 8);
+              lv[it] = lrow[r];   // with the batch: a load inside the reduction loop below would expose its latency 26 times
             }
           }
 #pragma unroll
@@ -534,7 +541,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
             acc += __shfl_xor_sync(0xffffffffu, acc, 4);
             if (sub == 0) {
               dsc[r] = acc * SCALE;
-              nl[r] = r < N ? -lse[((long long)b * H + h) * N + r] * LOG2E : -1e30f;   // padded queries: P = 0
+              nl[r] = -lv[it] * LOG2E;
             }
           }
         }
@@ -542,6 +549,9 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl->stats_full[slot]);
     }
+    // the last two heads' releases have no successor to consume them
+    for (int j = i; j < i + 2; ++j)
+      if (j >= 2) nbar_sync(BWD_BAR_STATS + (j & 1), BWD_COUNT_STATS);
   } else {
     // ------------------------------------------------------------------ compute warps: thread = key row (TMEM lane)
     const int wg = (warp - 2) >> 2;
@@ -581,9 +591,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
           }
           fence_proxy_async();   // the staging stores must be visible to the tensor core's (async proxy) reads
           tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&ctl->p_ready[s & 1]);
-          if (t == 1 && c == 3 && lane == 0) mbar_arrive(&ctl->stats_empty[i & 1]);   // last reader of this head's statistics
+          nbar_arrive(BWD_BAR_P + (s & 1), BWD_COUNT_MMA);
+          if (t == 1 && c == 3) nbar_arrive(BWD_BAR_STATS + (i & 1), BWD_COUNT_STATS);   // last reader of this head's statistics
           if (c == 3) {
             // dV (warp group 0) / dK (warp group 1) of key tile t
             mbar_wait(&ctl->dvdk_full, (2 * i + t) & 1);
@@ -591,8 +600,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
             uint4 acc[8];
             if (warp_active) read_row64(tmem_base + lane_off + (wg ? COL_DK : COL_DV), acc, 1.f);
             tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->dvdk_free);
+            nbar_arrive(BWD_BAR_DVDK, BWD_COUNT_MMA);
             const int key = t * 128 + krow;
             (void)key;
             if (warp_active && !(dbg & 64))
@@ -606,8 +614,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
             uint4 acc[8];
             if (rows_here) read_row64(tmem_base + lane_off + COL_DQ + wg * 64, acc, 1.f);
             tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl->dq_free);
+            nbar_arrive(BWD_BAR_DQ, BWD_COUNT_MMA);
             const int qrow = wg * 128 + krow;
             (void)qrow;
             if (rows_here && !(dbg & 64)) store_rows_staged(wstage, dqkv + (long long)b * N * C3 + h * D, C3, wg * 128 + q * 32, N, acc, lane);
