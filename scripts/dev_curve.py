@@ -6,11 +6,11 @@ import torch
 from tests import test_gpu_train as T
 from oracle import ref_port
 for task in (sys.argv[1:] or ["seg"]):
-    sd = ref_port.make_state(None, seed=42, head_classes=23) if task == "cls" else ref_port.make_state(task, seed=42)
-    x, t = T._data(task, 4)
-    ref = T._curve_oracle(task, sd, x, t)
-    a = T._curve_ours(task, sd, x, t, "bf16")
-    b = T._curve_ours(task, sd, x, t, "bf16")
+    sd = T._start_state(task)
+    data = T._data(task, 4)
+    ref = T._curve_oracle(task, sd, data)
+    a = T._curve_ours(task, sd, data, "bf16")
+    b = T._curve_ours(task, sd, data, "bf16")
     scale = torch.maximum(ref.abs(), 0.05 * ref[0].abs()) if task == "cls" else ref.abs()
     da = (a - ref).abs() / scale
     print("%s: max dev %.4f at %d (first 100: %.4f), run1 == run2: %s" % (task, da.max(), da.argmax(), da[:100].max(), torch.equal(a, b)))

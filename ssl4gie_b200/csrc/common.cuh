@@ -156,12 +156,12 @@ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, float 
 // Epilogue shared by the SIMT (validation) and tcgen05 contraction kernels.
 //   v = acc (+ bias[col]) ; mode-specific transform ; (+ residual) ; store as T or fp32
 // ---------------------------------------------------------------------------------------------
-enum { EPI_NONE = 0, EPI_GELU = 1, EPI_DGELU = 2, EPI_RELU = 3 };
+enum { EPI_NONE = 0, EPI_GELU = 1, EPI_DGELU = 2, EPI_RELU = 3, EPI_MUL = 4 };   // EPI_MUL: v *= aux (a stored derivative)
 
 struct EpiParams {
   const float* bias;   // [N] fp32 or null
   const void* res;     // residual [M, ldr] (fp32 if res_f32 else T) or null
-  const void* aux;     // EPI_DGELU: pre-activation u (T) [M, ldo]
+  const void* aux;     // EPI_DGELU: pre-activation u (T) [M, ldo]; EPI_MUL: elementwise factor (T) [M, ldo]
   void* out;           // [M, ldo]
   void* out2;          // EPI_GELU: pre-activation copy (T) or null
   int ldo, ldr;
@@ -183,6 +183,8 @@ __device__ __forceinline__ void epi_store1(const EpiParams& e, long long row, in
     v *= dgelu_f(to_f(reinterpret_cast<const T*>(e.aux)[o]));
   } else if (e.mode == EPI_RELU) {
     v = fmaxf(v, 0.f);
+  } else if (e.mode == EPI_MUL) {
+    v *= to_f(reinterpret_cast<const T*>(e.aux)[o]);
   }
   if (e.res) {
     const long long r = row * e.ldr + col;

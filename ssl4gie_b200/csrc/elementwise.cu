@@ -324,13 +324,14 @@ template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long
   S4G_KERNEL_CHECK();
   return 0;
 }
-// a = gelu(u)
-template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T* __restrict__ u, T* __restrict__ out, long long n8) {
+// a = gelu(u); gprime (optional, may alias u): gelu'(u) -- the backward then needs one multiply per element (EPI_MUL in the
+// fc2 dgrad epilogue) instead of a pass that re-evaluates erf / exp over the 77 MB tensor.  Both come from one (cdf, pdf).
+template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T* u, T* __restrict__ out, T* gprime, long long n8) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
-    Vec8<T> b[2];
+    Vec8<T> b[2], g[2];
 #pragma unroll
     for (int q = 0; q < 2; ++q)
       if (i0 + q * stride < n8) b[q].load(u + (i0 + q * stride) * 8);
@@ -338,13 +339,25 @@ template <typename T> __global__ void __launch_bounds__(256) gelu_kernel(const T
     for (int q = 0; q < 2; ++q)
       if (i0 + q * stride < n8) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) b[q].v[k] = sizeof(T) == 2 ? gelu_fast(b[q].v[k]) : gelu_f(b[q].v[k]);
+        for (int k = 0; k < 8; ++k) {
+          const float x = b[q].v[k];
+          if (sizeof(T) == 2) {
+            float c, pdf;
+            gelu_parts_fast(x, c, pdf);
+            b[q].v[k] = x * c;
+            g[q].v[k] = fmaf(x, pdf, c);
+          } else {
+            b[q].v[k] = gelu_f(x);
+            g[q].v[k] = dgelu_f(x);
+          }
+        }
         b[q].store(out + (i0 + q * stride) * 8);
+        if (gprime) g[q].store(gprime + (i0 + q * stride) * 8);
       }
   }
 }
-template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st) {
-  S4G_CUDA(launch_dep(gelu_kernel<T>, GRID1D(n / 16, 256), 0, st, u, out, n / 8));
+template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st, T* gprime) {
+  S4G_CUDA(launch_dep(gelu_kernel<T>, GRID1D(n / 16, 256), 0, st, u, out, gprime, n / 8));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1566,7 +1579,7 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
   template int k_layernorm_fwd<T>(const float*, const float*, const float*, T*, float*, float*, int, int, float, cudaStream_t); \
   template int k_layernorm_bwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, int, int, cudaStream_t, T*, float*, const Reducer*); \
   template int k_dgelu_mul<T>(const T*, const T*, T*, long long, cudaStream_t, float*, int, const Reducer*);                          \
-  template int k_gelu<T>(const T*, T*, long long, cudaStream_t);                                                       \
+  template int k_gelu<T>(const T*, T*, long long, cudaStream_t, T*);                                                      \
   template int k_colsum<T>(const T*, float*, long long, int, int, cudaStream_t, const Reducer*);                                       \
   template int k_tokens_to_nhwc<T>(const float*, T*, int, cudaStream_t);                                               \
   template int k_tap_grad<T>(const T*, float*, int, int, cudaStream_t, T*);                                                \

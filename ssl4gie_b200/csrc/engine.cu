@@ -155,6 +155,10 @@ struct Builder {
     return simt_conv_wgrad<T>(g, dY, X, dW, st);
   }
   bool umma_path() const { return std::is_same<T, bf16>::value && tensor; }
+  static bool gelu_bwd_fused() {
+    static const bool v = [] { const char* e = getenv("S4G_GELU_BWD"); return !(e && std::string(e) == "pass"); }();
+    return v;
+  }
   static EpiParams epi(void* out, int ldo, const float* bias = nullptr, int mode = EPI_NONE, int out_f32 = 0) {
     EpiParams e{};
     e.bias = bias; e.out = out; e.ldo = ldo; e.mode = mode; e.out_f32 = out_f32; e.alpha = 1.f;
@@ -478,7 +482,9 @@ struct Builder {
           // as its own HBM-bound pass
           S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), h2, mm->template at<T>(b.fc1.wf), epi(mm->template at<T>(b.u), 3072, b.fc1.b->p), st));
           mm->launches++;
-          S4G_TRY(k_gelu<T>(mm->template at<T>(b.u), mm->template at<T>(b.a), Tk * 3072, st));
+          // the same pass leaves gelu'(u) in place of u (u has no other reader): backward multiplies by it in the fc2 dgrad
+          // epilogue (S4G_GELU_BWD=pass keeps the separate GELU' pass over du)
+          S4G_TRY(k_gelu<T>(mm->template at<T>(b.u), mm->template at<T>(b.a), Tk * 3072, st, gelu_bwd_fused() ? mm->template at<T>(b.u) : nullptr));
         } else {
           EpiParams e2 = epi(mm->template at<T>(b.a), 3072, b.fc1.b->p, EPI_GELU);
           e2.out2 = mm->template at<T>(b.u);
@@ -538,7 +544,16 @@ struct Builder {
         else if (i == 11) { mm->launches++; S4G_TRY(k_cast_f32<T>(dxo, dxt, Tk * 768, st)); }
         mm->launches += 2;
         // mlp: x2 = x1 + fc2(gelu(fc1(ln2(x1))))
-        if (self->umma_path()) {
+        if (self->umma_path() && gelu_bwd_fused()) {
+          // du = (dx2 . W2) * gelu'(u): the stored derivative is one multiply in the dgrad epilogue; fc1's bias gradient is
+          // a column sum of du
+          EpiParams e = epi(dub, 3072, nullptr, EPI_MUL);
+          e.aux = mm->template at<T>(b.u);
+          S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), e, st));
+          mm->launches++;
+          const Reducer rg = self->red(b.gelu_red, true);
+          if (b.fc1.b->g) S4G_TRY(k_colsum<T>(dub, b.fc1.b->g, Tk, 3072, 3072, st, &rg));
+        } else if (self->umma_path()) {
           S4G_TRY(self->fprop(linear_geom(Tk, 3072, 768), dxt, mm->template at<T>(b.fc2.wd), epi(dub, 3072), st));
           mm->launches++;
           // fc1's bias gradient (column sums of du) comes out of the same pass

@@ -68,7 +68,7 @@ int k_layernorm_bwd(const T* dy, const float* x, const float* gamma, const float
                     T* dx_cast = nullptr, float* dxsum = nullptr, const Reducer* red = nullptr);
 // dx_cast: optional T copy of dx (the next GEMM's operand); dxsum: optional [C] = column sums of dx
 template <typename T> int k_dgelu_mul(const T* dy, const T* u, T* out, long long n, cudaStream_t st, float* colsum = nullptr, int N = 0, const Reducer* red = nullptr);
-template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st);
+template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t st, T* gprime = nullptr);   // gprime (may alias u) = gelu'(u)
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st, const Reducer* red = nullptr);  // out overwritten
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out = nullptr);  // inverse of above (+ optional T copy of the result)

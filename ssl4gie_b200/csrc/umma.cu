@@ -103,6 +103,17 @@ __device__ __forceinline__ void epi_row32(const EpiParams& e, long long row, int
   } else if (e.mode == EPI_RELU) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = fmaxf(v[i], 0.f);
+  } else if (e.mode == EPI_MUL) {
+    const bf16* pa = reinterpret_cast<const bf16*>(e.aux) + o;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      if (i < ncols) {
+        Vec8<bf16> t;
+        t.load(pa + i);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[i + k] *= t.v[k];
+      }
+    }
   }
   if (e.res) {
     const long long r = row * e.ldr + col0;
@@ -334,6 +345,19 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
                         t8.load(pa + i);
 #pragma unroll
                         for (int k = 0; k < 8; ++k) f[i + k] *= dgelu_fast(t8.v[k]);
+                      }
+                    }
+                  }
+                } else if (p.e.mode == EPI_MUL) {
+                  if (valid) {
+                    const bf16* pa = reinterpret_cast<const bf16*>(p.e.aux) + row * p.e.ldo + col0;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 8) {
+                      if (i < ncols) {
+                        Vec8<bf16> t8;
+                        t8.load(pa + i);
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) f[i + k] *= t8.v[k];
                       }
                     }
                   }

@@ -87,3 +87,24 @@ def warm_state(dense, sd, x, t, steps=50, lr=1e-4, alpha=0.1, fresh=None, device
                     full[p + "running_var"].mul_(0.9).add_(0.1 * var)
                     full[p + "num_batches_tracked"] += 1
     return {k: v.detach().clone() for k, v in full.items()}
+
+
+def warm_state_product(dense, sd, steps=30, lr=1e-4, alpha=0.1, batch=4):
+    """The same warm-up run by the PRODUCT path (bf16 tensor-core schedule + FusedAdamW, fresh task_batch every step).  The
+    product path is bit-reproducible, so every run of a test starts from the identical state (the oracle's cuDNN kernels
+    are not); which arithmetic produced the state does not matter to a test that evaluates both sides AT that state."""
+    from ssl4gie_b200 import FusedAdamW, ScaleAndShiftInvariantLoss, SoftDiceLoss, utils
+    m = utils.get_ImageNet_or_random_ViT(False, 1 if dense == "seg" else None, False, dense, False, False)
+    m.load_state_dict({k: v.cpu() for k, v in sd.items()}, strict=True)
+    if dense == "seg":
+        m.decoder.output_conv[3].p = 0.0
+    m.precision, m.backend = "bf16", "tensor"
+    m = m.cuda().train()
+    opt = FusedAdamW(m, lr=lr)
+    loss_fn = SoftDiceLoss() if dense == "seg" else ScaleAndShiftInvariantLoss(alpha=alpha)
+    for k in range(steps):
+        x, t = (v.cuda() for v in task_batch(dense, batch, 1000 + k))
+        loss_fn(m(x), t).backward()
+        opt.step()
+    torch.cuda.synchronize()
+    return {k: v.detach().clone() for k, v in m.state_dict().items()}
