@@ -8,8 +8,9 @@ import torch
 
 from ssl4gie_b200 import _C as C
 
-B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
-flt = sys.argv[2] if len(sys.argv) > 2 else ""
+_script = __name__ == "__main__"
+B = int(sys.argv[1]) if _script and len(sys.argv) > 1 else int(os.environ.get("S4G_SHAPES_B", 64))
+flt = sys.argv[2] if _script and len(sys.argv) > 2 else ""
 C.init(0)
 L = C.lib()
 T = B * 197
@@ -68,6 +69,7 @@ def conv_wgrad(H, Ci, Co):
 rows = []  # (name, count per step, flops, fn factory)
 
 
+
 def lin(name, M, N, K, cnt, dgrad=True):
     f = 2.0 * M * N * K
     rows.append((f"{name} fwd   M{M} N{N} K{K}", cnt, f, lambda: lin_fwd(M, N, K)))
@@ -105,15 +107,49 @@ conv("head112", 112, 256, 256, 1)
 for H in (14, 28, 56, 112):
     lin(f"out_conv{H}", B * H * H, 256, 256, 1)
 
-tot_ms = tot_f = 0.0
-for name, cnt, f, mk in rows:
-    if flt and flt not in name:
-        continue
-    fn = mk()
-    ms = timeit(fn)
-    del fn
-    torch.cuda.empty_cache()
-    tot_ms += ms * cnt
-    tot_f += f * cnt
-    print(f"{name:42s} x{cnt:2d} {ms:8.3f} ms {f / ms / 1e9:8.1f} TF/s  step {ms * cnt:7.3f} ms", flush=True)
-print(f"TOTAL {tot_ms:.3f} ms/step  {tot_f / 1e12:.2f} TFLOP  {tot_f / tot_ms / 1e9:.1f} TF/s")
+
+
+def attention(n=5):
+    """(fwd ms, bwd ms, algorithmic fwd FLOP) of one attention layer (timm Attention: 4 N^2 d per head forward, 2x backward)."""
+    N, H = 197, 12
+    qkv = torch.randn(B * N, 3 * H * 64, device="cuda").bfloat16()
+    o = torch.empty(B * N, H * 64, device="cuda", dtype=torch.bfloat16)
+    do = torch.randn(B * N, H * 64, device="cuda").bfloat16()
+    dqkv = torch.empty_like(qkv)
+    lse = torch.empty(B, H, N, device="cuda")
+    f = timeit(lambda: C.check(L.s4g_attention_fwd(C.ptr(qkv), C.ptr(o), C.ptr(lse), B, N, H, C.BF16, C.TENSOR, C.stream_ptr())), n)
+    b = timeit(lambda: C.check(L.s4g_attention_bwd(C.ptr(qkv), C.ptr(o), C.ptr(do), C.ptr(lse), C.ptr(dqkv), B, N, H, C.BF16, C.TENSOR, C.stream_ptr())), n)
+    return f, b, 4.0 * N * N * 64 * B * H
+
+
+def run(verbose=True, n=5):
+    """Times every shape; returns {family: (ms per step, FLOP per step)} for the families fprop_dgrad / wgrad / attention."""
+    fam = {"fprop_dgrad": [0.0, 0.0], "wgrad": [0.0, 0.0], "attention": [0.0, 0.0]}
+    tot_ms = tot_f = 0.0
+    for name, cnt, f, mk in rows:
+        if flt and flt not in name:
+            continue
+        fn = mk()
+        ms = timeit(fn, n)
+        del fn
+        torch.cuda.empty_cache()
+        tot_ms += ms * cnt
+        tot_f += f * cnt
+        k = "wgrad" if " wgrad " in name else "fprop_dgrad"
+        fam[k][0] += ms * cnt
+        fam[k][1] += f * cnt
+        if verbose:
+            print(f"{name:42s} x{cnt:2d} {ms:8.3f} ms {f / ms / 1e9:8.1f} TF/s  step {ms * cnt:7.3f} ms", flush=True)
+    if verbose:
+        print(f"TOTAL {tot_ms:.3f} ms/step  {tot_f / 1e12:.2f} TFLOP  {tot_f / tot_ms / 1e9:.1f} TF/s")
+    if not flt:
+        af, ab, aflop = attention(n)
+        fam["attention"] = [12 * (af + ab), 12 * 3 * aflop]
+        if verbose:
+            print(f"attention fwd {af * 1e3:.1f} us ({aflop / af / 1e9:.0f} TF/s)  bwd {ab * 1e3:.1f} us ({2 * aflop / ab / 1e9:.0f} TF/s)  x12 layers: "
+                  f"{12 * (af + ab):.3f} ms/step")
+    return fam
+
+
+if __name__ == "__main__":
+    run()
