@@ -401,9 +401,11 @@ int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int N, int H, cuda
   S4G_KERNEL_CHECK();
   return 0;
 }
+bool attn_uses_umma() { return use_umma_attention(); }
+
 int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int N, int H,
-                 cudaStream_t st) {
-  if (use_umma_attention()) return attn_bwd_umma(qkv, o, dout, lse, dqkv, B, N, H, st);
+                 cudaStream_t st, const float* delta) {
+  if (use_umma_attention()) return attn_bwd_umma(qkv, o, dout, lse, dqkv, B, N, H, st, delta);
   if (N > NP || N < 1) { s4g_set_error("attn_bwd_mma: specialised for sequences of at most 208 tokens"); return S4G_ERR_SHAPE; }
   const size_t smem = 2 * BWD_STAGE_BYTES;
   static bool attr = false;

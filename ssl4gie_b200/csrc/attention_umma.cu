@@ -13,13 +13,14 @@
 //   warps 4-11  softmax + epilogue: 4-7 query tile 0 (rows 0..127), 8-11 query tile 1 (rows 128..196): a thread owns
 //               one query row (= one TMEM lane): row max, exp2, row sum, bf16 P written over the first half of S,
 //               later O / sum -> global.
-// backward, one persistent CTA per SM, same warp roles, keys on the TMEM lanes (S^T = K Q^T, dP^T = V dO^T), so that P^T and
-// dS^T are A operands in tensor memory for dV = P^T dO and dK = dS^T Q; dS^T additionally goes through a 32 KB shared
-// memory tile as the MN-major A operand of dQ = dS K.  Four steps per head (2 key tiles x 2 query halves), accumulators
-// of dV, dK (per key tile) and dQ (both query tiles) stay in tensor memory: 512 columns exactly.  No atomics anywhere:
-// the result is bit-reproducible.
+// backward, one persistent CTA per SM (warp 0 TMA, warp 1 MMA, warps 2-9 compute, 10-11 statistics), keys on the TMEM lanes
+// (S^T = K Q^T, dP^T = V dO^T), so that P^T and dS^T are A operands in tensor memory for dV = P^T dO and dK = dS^T Q; dS^T
+// also goes through a shared-memory tile as the MN-major A operand of dQ = dS K.  Eight pipelined steps per head (2 key
+// tiles x 4 query chunks), accumulators of dV, dK and dQ stay in tensor memory: 512 columns exactly.  delta = rowsum(dO o O)
+// arrives precomputed (epilogue of the GEMM that produces dO).  Outputs leave by TMA store.  No atomics: bit-reproducible.
 #include <cuda.h>
 
+#include <algorithm>
 #include <cstdlib>
 
 #include "kernels.h"
@@ -68,21 +69,17 @@ __device__ __forceinline__ void read_row64(uint32_t taddr, uint4 (&pk)[8], float
                                   pack_bf16(__uint_as_float(a[g * 8 + 6]) * scale, __uint_as_float(a[g * 8 + 7]) * scale));
   }
 }
-// 32 rows x 128 B of one warp -> global, rows `ld` elements apart: every lane holds one row (8 x 16 B) but a warp store
-// that writes 32 different rows touches 32 cache lines; through the warp's 4 KB staging tile (16 B chunks XOR-swizzled by
-// the row: conflict-free both ways) each store instruction instead covers 4 rows x 128 contiguous bytes.
-__device__ __forceinline__ void store_rows_staged(uint8_t* wstage, bf16* base, long long ld, int row0, int nrows, const uint4 (&pk)[8], int lane) {
-  __syncwarp();   // the previous use of the staging tile has been read
+// 32 rows x 128 B of one warp -> global: every lane holds one row (8 x 16 B); a warp store that writes 32 different rows
+// touches 32 cache lines per instruction, so the rows go through the warp's 4 KB staging tile (SWIZZLE_128B: 16 B chunks
+// XOR-ed with the row) and leave with ONE TMA store, which also clips the rows past the end of the sequence.
+__device__ __forceinline__ void store_rows_tma(uint8_t* wstage, const CUtensorMap* map, int col, int row0, int img, const uint4 (&pk)[8], int lane) {
+  if (lane == 0) tma_store_wait_read<0>();   // the previous store has finished reading the staging tile
+  __syncwarp();
 #pragma unroll
   for (int g = 0; g < 8; ++g) *reinterpret_cast<uint4*>(wstage + lane * 128 + ((g ^ (lane & 7)) << 4)) = pk[g];
+  fence_proxy_async();
   __syncwarp();
-  const int sub = lane >> 3, ch = lane & 7;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int r = j * 4 + sub;
-    const uint4 v = *reinterpret_cast<const uint4*>(wstage + r * 128 + ((ch ^ (r & 7)) << 4));
-    if (row0 + r < nrows) *reinterpret_cast<uint4*>(base + (long long)(row0 + r) * ld + ch * 8) = v;
-  }
+  if (lane == 0) { tma_store_3d(map, wstage, col, row0, img); tma_store_commit(); }
 }
 constexpr int WSTAGE_BYTES = 32 * 128;   // per compute warp
 
@@ -112,8 +109,9 @@ __device__ __forceinline__ void softmax_chunk32(const uint32_t (&v)[32], uint32_
   }
 }
 
-__global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o,
-                                                                   float* __restrict__ lse, int N, int H, int total, int dbg) {
+__global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_constant__ CUtensorMap tmQKV,
+                                                                   const __grid_constant__ CUtensorMap tmO, float* __restrict__ lse, int N,
+                                                                   int H, int total, int dbg) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
   uint8_t* ones = smem + FWD_STAGES * FWD_STAGE_BYTES;   // [208 keys][64]: column 0 = 1 (second 64-column group of B = [V | 1])
@@ -124,6 +122,7 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmO);
     for (int i = 0; i < FWD_STAGES; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 2); }
     for (int i = 0; i < 2; ++i) { mbar_init(&ctl->s_full[i], 1); mbar_init(&ctl->o_full[i], 1); }
     fence_barrier_init();
@@ -290,10 +289,11 @@ __global__ void __launch_bounds__(THREADS, 1) attn_fwd_umma_kernel(const __grid_
       tc_fence_before();
       nbar_arrive(FWD_BAR_FREE + t, FWD_BAR_COUNT);   // the slot may take the next head's S while the stores drain
       if (warp_active && !(dbg & 16)) {
-        store_rows_staged(wstages + (warp - 4) * WSTAGE_BYTES, o + (long long)b * N * C + h * D, C, t * 128 + q * 32, N, acc, lane);
+        store_rows_tma(wstages + (warp - 4) * WSTAGE_BYTES, &tmO, h * D, t * 128 + q * 32, b, acc, lane);
         if (row < N) lse[((long long)b * H + h) * N + row] = mx * SCALE + logf(sum);
       }
     }
+    if (lane == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -366,8 +366,8 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
                                                                    const __grid_constant__ CUtensorMap tmQKVhi,
                                                                    const __grid_constant__ CUtensorMap tmDOlo,
                                                                    const __grid_constant__ CUtensorMap tmDOhi,
-                                                                   const bf16* __restrict__ o, const bf16* __restrict__ dout,
-                                                                   const float* __restrict__ lse, bf16* __restrict__ dqkv,
+                                                                   const __grid_constant__ CUtensorMap tmDQKV,
+                                                                   const float* __restrict__ delta, const float* __restrict__ lse,
                                                                    int N, int H, int total, int dbg) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
@@ -376,14 +376,15 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
   uint8_t* sV = smem + 2 * TILE_BYTES;
   uint8_t* sDO = smem + 3 * TILE_BYTES;
   uint8_t* stg = smem + BWD_SMEM_TENSORS;                               // [2][STG_BYTES]
-  float* stats = reinterpret_cast<float*>(stg + 2 * STG_BYTES);         // [2 heads][2][NP]: -lse * log2(e) | delta * scale
-  uint8_t* wstages = reinterpret_cast<uint8_t*>(stats + 4 * NP);        // 8 x 4 KB: output staging of the compute warps
-  BwdCtl* ctl = reinterpret_cast<BwdCtl*>(wstages + 8 * WSTAGE_BYTES);
+  uint8_t* wstages = stg + 2 * STG_BYTES;                               // 8 x 4 KB: output staging of the compute warps
+  float* stats = reinterpret_cast<float*>(wstages + 8 * WSTAGE_BYTES);  // [2 heads][2][NP]: -lse * log2(e) | delta * scale
+  BwdCtl* ctl = reinterpret_cast<BwdCtl*>(stats + 4 * NP);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int C = H * D, C3 = 3 * C;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmQKVlo); tma_prefetch_desc(&tmQKVhi); tma_prefetch_desc(&tmDOlo); tma_prefetch_desc(&tmDOhi);
+    tma_prefetch_desc(&tmDQKV);
     for (int i = 0; i < 3; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&ctl->sdp_full[i], 1); mbar_init(&ctl->stg_free[i], 1); mbar_init(&ctl->stats_full[i], 2); }
     mbar_init(&ctl->dvdk_full, 1); mbar_init(&ctl->dq_full, 1);
@@ -494,57 +495,29 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
     if (nsteps > 0) { nbar_sync(BWD_BAR_DVDK, BWD_COUNT_MMA); nbar_sync(BWD_BAR_DQ, BWD_COUNT_MMA); }   // the last read-outs' arrivals
   } else if (warp >= 10) {
     // ------------------------------------------------------------------ statistics warps: one head ahead of the compute warps
-    // per query: delta_i = sum_d dO[i,d] O[i,d] (8 lanes per row, coalesced 16 B loads) and lse_i, pre-scaled
+    // per query: -lse_i * log2(e) and delta_i * scale, delta_i = sum_d dO[i,d] O[i,d] (precomputed: by the epilogue of the GEMM
+    // that produces dO inside the model schedule, by attn_delta_kernel otherwise)
     const int stid = threadIdx.x - 320;    // 0..63
-    const int sub = stid & 7;
     int i = 0;
     for (int w = blockIdx.x; w < total; w += gridDim.x, ++i) {
       const int slot = i & 1;
       if (i >= 2) nbar_sync(BWD_BAR_STATS + slot, BWD_COUNT_STATS);   // the compute warps are done with head i - 2
-      const int b = w / H, h = w % H;
-      const bf16* dob = dout + (long long)b * N * C + h * D;
-      const bf16* ob = o + (long long)b * N * C + h * D;
       float* nl = stats + slot * 2 * NP;
       float* dsc = nl + NP;
-      if (!(dbg & 32)) {
-        // two batches of 13 rows per 8-lane group: all 26 16 B loads of a batch are in flight together
-#pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
-          uint4 xr[13], yr[13];
-          float lv[13];
-          const float* lrow = lse + ((long long)b * H + h) * N;
+      const float* lrow = lse + (long long)w * N;
+      const float* drow = delta + (long long)w * N;
+      float lv[4], dv[4];
 #pragma unroll
-          for (int it = 0; it < 13; ++it) {
-            const int r = (half * 13 + it) * 8 + (stid >> 3);
-            xr[it] = yr[it] = make_uint4(0, 0, 0, 0);
-            lv[it] = 1e30f / LOG2E;   // padded queries: P = 0
-            if (r < N) {
-              xr[it] = *reinterpret_cast<const uint4*>(dob + (long long)r * C + sub * 8);
-              yr[it] = *reinterpret_cast<const uint4*>(ob + (long long)r * C + sub * 8);
-              lv[it] = lrow[r];   // with the batch: a load inside the reduction loop below would expose its latency 26 times
-            }
-          }
+      for (int it = 0; it < 4; ++it) {
+        const int r = it * 64 + stid;
+        lv[it] = 1e30f / LOG2E;   // padded queries: P = 0
+        dv[it] = 0.f;
+        if (r < N && !(dbg & 32)) { lv[it] = lrow[r]; dv[it] = drow[r]; }
+      }
 #pragma unroll
-          for (int it = 0; it < 13; ++it) {
-            const int r = (half * 13 + it) * 8 + (stid >> 3);
-            const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&xr[it]);
-            const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&yr[it]);
-            float acc = 0.f;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 a = __bfloat1622float2(xh[e]), c2 = __bfloat1622float2(yh[e]);
-              acc = fmaf(a.x, c2.x, acc);
-              acc = fmaf(a.y, c2.y, acc);
-            }
-            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-            if (sub == 0) {
-              dsc[r] = acc * SCALE;
-              nl[r] = -lv[it] * LOG2E;
-            }
-          }
-        }
+      for (int it = 0; it < 4; ++it) {
+        const int r = it * 64 + stid;
+        if (r < NP) { nl[r] = -lv[it] * LOG2E; dsc[r] = dv[it] * SCALE; }
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl->stats_full[slot]);
@@ -603,8 +576,7 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
             nbar_arrive(BWD_BAR_DVDK, BWD_COUNT_MMA);
             const int key = t * 128 + krow;
             (void)key;
-            if (warp_active && !(dbg & 64))
-              store_rows_staged(wstage, dqkv + (long long)b * N * C3 + (wg ? C : 2 * C) + h * D, C3, t * 128 + q * 32, N, acc, lane);
+            if (warp_active && !(dbg & 64)) store_rows_tma(wstage, &tmDQKV, (wg ? C : 2 * C) + h * D, t * 128 + q * 32, b, acc, lane);
           }
           if (t == 1 && c == 3) {
             // dQ: warp group g reads query tile g
@@ -617,11 +589,12 @@ __global__ void __launch_bounds__(BWD_THREADS, 1) attn_bwd_umma_kernel(const __g
             nbar_arrive(BWD_BAR_DQ, BWD_COUNT_MMA);
             const int qrow = wg * 128 + krow;
             (void)qrow;
-            if (rows_here && !(dbg & 64)) store_rows_staged(wstage, dqkv + (long long)b * N * C3 + h * D, C3, wg * 128 + q * 32, N, acc, lane);
+            if (rows_here && !(dbg & 64)) store_rows_tma(wstage, &tmDQKV, h * D, wg * 128 + q * 32, b, acc, lane);
           }
         }
       }
     }
+    if (lane == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -644,6 +617,31 @@ static int attn_dbg() {
   static const int v = getenv("S4G_ATTN_DBG") ? atoi(getenv("S4G_ATTN_DBG")) : 0;
   return v;
 }
+namespace {
+// delta[b, h, i] = sum_d dO[b, i, h, d] * O[b, i, h, d]: 8 lanes per (row, head), one coalesced 16 B load each per tensor
+__global__ void __launch_bounds__(256) attn_delta_kernel(const bf16* __restrict__ o, const bf16* __restrict__ dout, float* __restrict__ delta,
+                                                         long long rows, int N, int H) {
+  pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
+  pdl_trigger();
+  const int sub = threadIdx.x & 7;
+  const long long items = rows * H;   // (row, head) pairs
+  for (long long it = (long long)blockIdx.x * 32 + (threadIdx.x >> 3); it < items; it += (long long)gridDim.x * 32) {
+    const long long row = it / H;
+    const int h = (int)(it % H);
+    Vec8<bf16> x, y;
+    x.load(dout + row * H * D + h * D + sub * 8);
+    y.load(o + row * H * D + h * D + sub * 8);
+    float acc = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc = fmaf(x.v[e], y.v[e], acc);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (sub == 0) delta[((row / N) * H + h) * N + row % N] = acc;
+  }
+}
+}  // namespace
+
 static int attn_umma_grid(int total) {
   const int sms = umma_num_sms();
   return total < sms ? total : sms;
@@ -651,29 +649,41 @@ static int attn_umma_grid(int total) {
 
 int attn_fwd_umma(const bf16* qkv, bf16* o, float* lse, int B, int N, int H, cudaStream_t st) {
   if (N > NP || N < 1) { s4g_set_error("attn_fwd_umma: specialised for sequences of at most 208 tokens"); return S4G_ERR_SHAPE; }
-  CUtensorMap tm;
+  CUtensorMap tm, tmo;
   S4G_TRY(make_rows_map(&tm, qkv, 3 * H * D, N, B, FWD_HALF_ROWS));
+  S4G_TRY(make_rows_map(&tmo, o, H * D, N, B, 32));
   const size_t smem = 1024 + FWD_STAGES * FWD_STAGE_BYTES + TILE_BYTES + 8 * WSTAGE_BYTES + sizeof(FwdCtl);
   static bool attr = false;
   if (!attr) { S4G_CUDA(cudaFuncSetAttribute(attn_fwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  S4G_CUDA(launch_dep(attn_fwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(THREADS), smem, st, tm, o, lse, N, H, B * H, attn_dbg()));
+  S4G_CUDA(launch_dep(attn_fwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(THREADS), smem, st, tm, tmo, lse, N, H, B * H, attn_dbg()));
   S4G_KERNEL_CHECK();
   return 0;
 }
 
 int attn_bwd_umma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int N, int H,
-                  cudaStream_t st) {
+                  cudaStream_t st, const float* delta) {
   if (N > NP || N < 1) { s4g_set_error("attn_bwd_umma: specialised for sequences of at most 208 tokens"); return S4G_ERR_SHAPE; }
+  if (!delta) {
+    // stand-alone call: rowsum(dO o O) by its own pass (inside the model schedule it comes out of the dO-producing GEMM)
+    float* d = reinterpret_cast<float*>(reduce_scratch(nullptr, sizeof(float) * (size_t)B * H * N));
+    if (!d) return S4G_ERR_WORKSPACE;
+    const long long rows = (long long)B * N;
+    S4G_CUDA(launch_dep(attn_delta_kernel, dim3((unsigned)std::min<long long>((rows * H + 31) / 32, 148 * 16)), dim3(256), 0, st, o, dout, d, rows, N, H));
+    S4G_KERNEL_CHECK();
+    delta = d;
+  }
   CUtensorMap qlo, qhi, dlo, dhi;
   S4G_TRY(make_rows_map(&qlo, qkv, 3 * H * D, N, B, LO_ROWS));
   S4G_TRY(make_rows_map(&qhi, qkv, 3 * H * D, N, B, HI_ROWS));
   S4G_TRY(make_rows_map(&dlo, dout, H * D, N, B, LO_ROWS));
   S4G_TRY(make_rows_map(&dhi, dout, H * D, N, B, HI_ROWS));
+  CUtensorMap dmap;
+  S4G_TRY(make_rows_map(&dmap, dqkv, 3 * H * D, N, B, 32));
   const size_t smem = 1024 + BWD_SMEM_TENSORS + 2 * STG_BYTES + 4 * NP * sizeof(float) + 8 * WSTAGE_BYTES + sizeof(BwdCtl);
   static bool attr = false;
   if (!attr) { S4G_CUDA(cudaFuncSetAttribute(attn_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  S4G_CUDA(launch_dep(attn_bwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(BWD_THREADS), smem, st, qlo, qhi, dlo, dhi, o, dout, lse, dqkv, N, H,
-                      B * H, attn_dbg()));
+  S4G_CUDA(launch_dep(attn_bwd_umma_kernel, dim3(attn_umma_grid(B * H)), dim3(BWD_THREADS), smem, st, qlo, qhi, dlo, dhi, dmap, delta, lse, N, H, B * H,
+                      attn_dbg()));
   S4G_KERNEL_CHECK();
   return 0;
 }

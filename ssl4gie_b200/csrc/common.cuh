@@ -169,6 +169,12 @@ struct EpiParams {
   int out_f32, res_f32;
   float alpha;         // scales acc before everything else (1.0 default)
   int accumulate;      // out += (fp32 outputs only)
+  // optional fused row statistic of the tcgen05 bf16 (TMA-store) epilogue: for every 64-column group g of the output (one
+  // attention head) dot_out[(row / dot_rows) * dot_groups * dot_rows + g * dot_rows + row % dot_rows] = sum_c out[row, 64 g + c] *
+  // dot_aux[row, 64 g + c]  -- the attention backward's delta = rowsum(dO o O), produced where dO is produced
+  const void* dot_aux;   // bf16 [M, ldo] or null
+  float* dot_out;
+  int dot_rows, dot_groups;
 };
 
 template <typename T>

@@ -399,7 +399,7 @@ struct Builder {
   std::vector<Block> blocks;
   size_t patches = 0, pe = 0;
   Lin pe_lin{};
-  size_t dxa = 0, dxb = 0, dxT = 0, dh = 0, du = 0, dao = 0, dqkv = 0;  // backward temporaries
+  size_t dxa = 0, dxb = 0, dxT = 0, dh = 0, du = 0, dao = 0, dqkv = 0, attn_delta = 0;  // backward temporaries
   int tap_act[4] = {-1, -1, -1, -1};
 
   int attn_fwd(const T* qkv, T* o, float* lse, cudaStream_t st) const {
@@ -409,10 +409,10 @@ struct Builder {
     }
     return attn_fwd_simt<T>(qkv, o, lse, B, 197, 12, st);
   }
-  int attn_bwd(const T* qkv, const T* o, const T* dout, const float* lse, T* dqkv_, cudaStream_t st) const {
+  int attn_bwd(const T* qkv, const T* o, const T* dout, const float* lse, T* dqkv_, cudaStream_t st, const float* delta = nullptr) const {
     m->launches++;
     if constexpr (std::is_same<T, bf16>::value) {
-      if (tensor) return attn_bwd_mma(qkv, o, dout, lse, dqkv_, B, 197, 12, st);
+      if (tensor) return attn_bwd_mma(qkv, o, dout, lse, dqkv_, B, 197, 12, st, delta);
     }
     return attn_bwd_simt<T>(qkv, o, dout, lse, dqkv_, B, 197, 12, st);
   }
@@ -509,6 +509,7 @@ struct Builder {
     dxa = alloc(sizeof(float) * Tk * 768); dxb = alloc(sizeof(float) * Tk * 768);
     dxT = alloc(sizeof(T) * Tk * 768); dh = alloc(sizeof(T) * Tk * 768);
     du = alloc(sizeof(T) * Tk * 3072); dao = alloc(sizeof(T) * Tk * 768); dqkv = alloc(sizeof(T) * Tk * 2304);
+    attn_delta = alloc(sizeof(float) * (size_t)B * 12 * 197);
     // patch-embed / token-assembly backward: gradient arrives in dxa (12 blocks => even number of ping-pongs)
     m->bwd_enc.push_back([=](cudaStream_t st) {
       float* dx = mm->template at<float>(self->dxa);
@@ -570,9 +571,17 @@ struct Builder {
         const Reducer r2 = self->red(b.ln2_red, true), r1 = self->red(b.ln1_red, true);
         S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, 768, st, dxt, b.proj.b->g, &r2));
         // attention: x1 = x0 + proj(attn(qkv(ln1(x0))))
-        S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), dxt, mm->template at<T>(b.proj.wd), epi(daob, 768), st));
+        // d(attention output) = dx1 . Wproj; on the tcgen05 path its epilogue also yields delta = rowsum(dO o O) per head, which
+        // the attention backward would otherwise compute with its own pass over O and dO
+        EpiParams ep = epi(daob, 768);
+        const float* delta = nullptr;
+        if (self->umma_path() && attn_uses_umma()) {
+          ep.dot_aux = mm->template at<T>(b.ao); ep.dot_out = mm->template at<float>(self->attn_delta); ep.dot_rows = 197; ep.dot_groups = 12;
+          delta = ep.dot_out;
+        }
+        S4G_TRY(self->fprop(linear_geom(Tk, 768, 768), dxt, mm->template at<T>(b.proj.wd), ep, st));
         S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st, true));
-        S4G_TRY(self->attn_bwd(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, st));
+        S4G_TRY(self->attn_bwd(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, st, delta));
         S4G_TRY(self->fprop(linear_geom(Tk, 768, 2304), dqkvb, mm->template at<T>(b.qkv.wd), epi(dhb, 768), st));
         S4G_TRY(self->linear_param_grads(b.qkv, dqkvb, mm->template at<T>(b.h1), Tk, st));
         return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, 768, st, i > 0 ? dxt : nullptr,

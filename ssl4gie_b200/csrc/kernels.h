@@ -158,11 +158,13 @@ int attn_bwd_simt(const T* qkv, const T* o, const T* dout, const float* lse, T* 
                   cudaStream_t st);
 // tcgen05 attention (attention_umma.cu): S and P in tensor memory, Q/K/V by TMA; head dim 64, Ntok <= 208
 int attn_fwd_umma(const bf16* qkv, bf16* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
+// delta (optional): precomputed rowsum(dO o O) [B, H, Ntok]; null = computed by a pass over o and dout
 int attn_bwd_umma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int Ntok, int H,
-                  cudaStream_t st);
+                  cudaStream_t st, const float* delta = nullptr);
+bool attn_uses_umma();   // false under S4G_ATTN=mma
 int attn_fwd_mma(const bf16* qkv, bf16* o, float* lse, int B, int Ntok, int H, cudaStream_t st);
 int attn_bwd_mma(const bf16* qkv, const bf16* o, const bf16* dout, const float* lse, bf16* dqkv, int B, int Ntok, int H,
-                 cudaStream_t st);
+                 cudaStream_t st, const float* delta = nullptr);
 
 // ---- losses: loss.cu   (scratch holds the per-block partial rows and the combined sums; nothing to zero)
 size_t dice_scratch_doubles(int B);

@@ -298,6 +298,7 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
         const int nslabs = (p.block_n + 63) >> 6;
         uint8_t* buf = epi_smem + (warp - 2) * EPI_WARP_BYTES;
         for (int sl = half; sl < nslabs; sl += 2) {
+          float rowdot = 0.f;
           for (int pass = 0; pass < npass; ++pass) {
             if (lane == 0) tma_store_wait_read<0>();  // the previous store is done reading the staging slab
             __syncwarp();
@@ -363,6 +364,18 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
                   }
                 }
               }
+              if (p.e.dot_aux && valid) {
+                const bf16* pa = reinterpret_cast<const bf16*>(p.e.dot_aux) + row * p.e.ldo + col0;
+#pragma unroll
+                for (int i = 0; i < 32; i += 8) {
+                  if (i < ncols) {
+                    Vec8<bf16> t8;
+                    t8.load(pa + i);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) rowdot = fmaf(f[i + k], t8.v[k], rowdot);
+                  }
+                }
+              }
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 uint4 pk;
@@ -375,6 +388,11 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
             }
             fence_proxy_async();
             __syncwarp();
+            if (p.e.dot_aux && valid) {
+              const int g = (tn * p.block_n + sl * 64) >> 6;   // 64-column group = attention head
+              if (g < p.e.dot_groups)
+                p.e.dot_out[(row / p.e.dot_rows) * (long long)p.e.dot_groups * p.e.dot_rows + (long long)g * p.e.dot_rows + row % p.e.dot_rows] = rowdot;
+            }
             if (lane == 0) {
               const int cc = tn * p.block_n + sl * 64;
               if (cc < p.N) {
@@ -871,6 +889,10 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
               (e.mode == EPI_NONE || e.mode == EPI_RELU) && e.ldo % 4 == 0 && (!e.res || e.ldr % 4 == 0) && g.Cout % 4 == 0 &&
               (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 && (reinterpret_cast<uintptr_t>(e.res) & 15) == 0 &&
               (!e.bias || (reinterpret_cast<uintptr_t>(e.bias) & 15) == 0);
+  if (e.dot_aux && (!p.tma_epi || p.block_n % 64 || !matrix || e.out2)) {
+    s4g_set_error("umma_conv_fprop: the fused row-dot needs the bf16 TMA-store epilogue of a plain matrix with 64-column slabs");
+    return S4G_ERR_SHAPE;
+  }
   CUtensorMap tmO = tmA, tmO2 = tmA;
   if (p.tma_epi) {
     S4G_TRY(make_act_map(&tmO, reinterpret_cast<const bf16*>(e.out), g, g.Cout, e.ldo, p.tg, matrix, g.Hi, g.Wi, 4));
