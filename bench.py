@@ -289,7 +289,16 @@ def run_ours(args):
     extra = None
     if rank == 0 and world == 1 and not args.no_extras:
         # free this process's 17 GB workspace before the side measurements share the GPU with it
-        host_enqueue_ms = 1e3 * sum(launch_host) / max(1, len(launch_host))
+        # host time to ENQUEUE one step: measured on an idle device (inside the timed loop the host blocks on the full launch
+        # queue, which measures the GPU, not the host)
+        enq = []
+        for _ in range(5):
+            torch.cuda.synchronize()
+            del launch_host[:]
+            step(x_d, t_d, False)
+            enq.append(launch_host[-1])
+        torch.cuda.synchronize()
+        host_enqueue_ms = 1e3 * sorted(enq)[len(enq) // 2]
         extra = side_measurements(task, B, roof)
         extra["host_enqueue_ms_per_step"] = host_enqueue_ms
     cpu = None
