@@ -76,11 +76,11 @@ def main():
     m_peer = build(True)
     o_peer, g_peer = run(m_peer, x, w)
     from ssl4gie_b200.engine import Engine
-    assert Engine.of(m_peer).handle(B).peer is not None, "peer exchange not installed"
+    assert Engine.of(m_peer).handle(B).syncbn_via == "peer", "peer exchange not installed"
     os.environ["S4G_SYNCBN"] = "nccl"
     m_nccl = build(True)
     o_nccl, g_nccl = run(m_nccl, x, w)
-    assert Engine.of(m_nccl).handle(B).peer is None
+    assert Engine.of(m_nccl).handle(B).syncbn_via == "nccl"
     e = rel(o_peer, o_nccl)
     eg = max(rel(g_peer[n], g_nccl[n]) for n in g_peer)
     rm = max(rel(a, b) for (_, a), (_, b) in zip(m_peer.named_buffers(), m_nccl.named_buffers()) if a.is_floating_point())

@@ -192,6 +192,7 @@ class _Handle:
         self.ws_off = (-base) % 256
         _C.check(lib.s4g_model_set_workspace(self.ptr, ctypes.c_void_p(base + self.ws_off), nbytes))
         self.buffers = [b for _, b in model.named_buffers()]
+        self.syncbn_via = None  # "peer" (NVLink mailboxes, csrc/peer.cu) | "nccl" (callback) when world_size > 1
         if world_size > 1:
             self._install_allreduce()
 
@@ -205,6 +206,7 @@ class _Handle:
             boxes = shared_mailboxes()
             if boxes.ok:
                 _C.check(_C.lib().s4g_model_set_peer_exchange(self.ptr, boxes.ptrs, boxes.rank, boxes.world))
+                self.syncbn_via = "peer"
                 return
             print("ssl4gie_b200: peer mailboxes unavailable (%s); SyncBN statistics go through NCCL" % getattr(boxes, "error", "a peer failed"))
         ws_f64 = self.workspace[self.ws_off:self.ws_off + (self.workspace.numel() - 256) // 8 * 8].view(torch.float64)
@@ -220,6 +222,7 @@ class _Handle:
                 return -6
 
         self._cb = _C.ALLREDUCE_FN(cb)
+        self.syncbn_via = "nccl"
         _C.check(_C.lib().s4g_model_set_allreduce(self.ptr, self._cb, None))
 
     def destroy(self):
