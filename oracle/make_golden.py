@@ -215,6 +215,52 @@ def loss_kats():
     print("loss KATs:", kat["dice_loss"], kat["ssi_loss_a0.1"], kat["ssi_loss_a0.0"], kat["ssi_scale"], kat["ssi_shift"])
 
 
+def mae_inputs(B=2):
+    g = torch.Generator().manual_seed(5)
+    return torch.randn(B, 3, 224, 224, generator=g), torch.rand(B, 196, generator=g)
+
+
+def run_mae():
+    """One MAE pretraining step (BASELINE config 5) through the UNMODIFIED Models/mae/models_mae.py at B=2, with the
+    masking noise of random_masking (:132) supplied by patching torch.rand for the duration of the call."""
+    from Models.mae import models_mae
+
+    torch.manual_seed(42)
+    model = models_mae.mae_vit_base_patch16(norm_pix_loss=True)
+    sd = ref_port.mae_make_state(seed=42)
+    ref_pos = model.pos_embed.detach().clone(), model.decoder_pos_embed.detach().clone()
+    assert torch.equal(ref_pos[0], sd["pos_embed"]) and torch.equal(ref_pos[1], sd["decoder_pos_embed"]), "sin-cos tables"
+    missing, unexpected = model.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+    model.train()
+    x, noise = mae_inputs()
+    real_rand = torch.rand
+    torch.rand = lambda *a, **k: noise.clone()
+    try:
+        loss, pred, mask = model(x, mask_ratio=0.75)
+    finally:
+        torch.rand = real_rand
+    loss.backward()
+    none_grads = sorted(n for n, p in model.named_parameters() if p.requires_grad and p.grad is None)
+    frozen = sorted(n for n, p in model.named_parameters() if not p.requires_grad)
+    assert frozen == sorted(ref_port.MAE_FROZEN) and not none_grads, (frozen, none_grads)
+    grads = {n: p.grad for n, p in model.named_parameters() if p.grad is not None}
+    l2, p2, m2, g2 = ref_port.mae_loss_and_grads(sd, x, noise)
+    assert torch.equal(m2, mask)
+    err = (p2 - pred.detach()).abs().max().item() / pred.detach().abs().max().item()
+    worst = max((g2[n] - g).abs().max().item() / (g.abs().max().item() + 1e-20) for n, g in grads.items())
+    assert err < 1e-5 and abs(l2.item() - loss.item()) < 1e-6 and worst < 1e-4, (err, l2.item(), loss.item(), worst)
+    print(f"[mae] ref_port vs reference: pred {err:.2e} loss {abs(l2.item()-loss.item()):.2e} grads {worst:.2e}")
+    names = sorted(grads)
+    fix = {"loss": np.float64(loss.item()), "pred_sub": pred.detach()[:, ::7, ::16].numpy(), "mask": mask.numpy(),
+           "pred_absmax": np.float64(pred.detach().abs().max().item()), "grad_names": np.array(names),
+           "grad_norm": np.array([grads[n].double().norm().item() for n in names]),
+           "grad_head": np.stack([np.pad(grads[n].flatten()[:8].numpy(), (0, max(0, 8 - grads[n].numel()))) for n in names])}
+    np.savez_compressed(os.path.join(OUT, "step_mae_b2.npz"), **fix)
+    with open(os.path.join(OUT, "manifest_mae.json"), "w") as f:
+        json.dump({k: [list(v.shape), str(v.dtype)] for k, v in model.state_dict().items()}, f, indent=0, sort_keys=True)
+
+
 def variants_manifest():
     """Key/shape manifests for the MAE- and MoCo-based wrappers (Models/models.py:360-578)."""
     from Models import models as ref_models
@@ -249,11 +295,15 @@ if __name__ == "__main__":
     loss_kats()
     if "--kats-only" in sys.argv:
         sys.exit(0)
+    if "--mae-only" in sys.argv:
+        run_mae()
+        sys.exit(0)
     if "--cls-only" not in sys.argv:
         run("seg")
         run("depth")
     run_cls("cls")
     run_cls("spatial")
+    run_mae()
     if "--cls-only" in sys.argv:
         sys.exit(0)
     try:

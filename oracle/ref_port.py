@@ -60,11 +60,11 @@ def attention(sd, p, x, num_heads=12):
     return F.linear(y, sd[p + "proj.weight"], sd[p + "proj.bias"])
 
 
-def block(sd, i, x):
+def block(sd, i, x, prefix="blocks.", num_heads=12):
     """timm 0.6.12 Block.forward: pre-LN residual x2, LN eps 1e-6 (Models/models.py:384,498), exact GELU."""
-    p = f"blocks.{i}."
+    p = f"{prefix}{i}."
     h = F.layer_norm(x, (x.shape[-1],), sd[p + "norm1.weight"], sd[p + "norm1.bias"], 1e-6)
-    x = x + attention(sd, p + "attn.", h)
+    x = x + attention(sd, p + "attn.", h, num_heads)
     h = F.layer_norm(x, (x.shape[-1],), sd[p + "norm2.weight"], sd[p + "norm2.bias"], 1e-6)
     h = F.linear(h, sd[p + "mlp.fc1.weight"], sd[p + "mlp.fc1.bias"])
     h = F.gelu(h)
@@ -373,3 +373,132 @@ def adamw_step(p, g, m, v, step, lr=1e-4, b1=0.9, b2=0.999, eps=1e-8, wd=0.01):
     bc2 = 1 - b2 ** step
     denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
     p.addcdiv_(m, denom, value=-lr / bc1)
+
+
+# --------------------------------------------------------------------------- MAE pretraining step (BASELINE config 5)
+def sincos_2d(embed_dim, grid_size=14):
+    """Models/mae/util/pos_embed.py:20-69 (get_2d_sincos_pos_embed, cls_token=True): w-coordinate first, then h."""
+    import numpy as np
+
+    def one(d, pos):
+        omega = 1.0 / 10000 ** (np.arange(d // 2, dtype=float) / (d / 2.0))
+        out = np.einsum("m,d->md", pos.reshape(-1), omega)
+        return np.concatenate([np.sin(out), np.cos(out)], axis=1)
+
+    gh, gw = np.arange(grid_size, dtype=np.float32), np.arange(grid_size, dtype=np.float32)
+    grid = np.stack(np.meshgrid(gw, gh), axis=0).reshape(2, 1, grid_size, grid_size)
+    emb = np.concatenate([one(embed_dim // 2, grid[0]), one(embed_dim // 2, grid[1])], axis=1)
+    return torch.from_numpy(np.concatenate([np.zeros([1, embed_dim]), emb], axis=0)).float().unsqueeze(0)
+
+
+def mae_make_state(seed=42, device="cpu"):
+    """state_dict of mae_vit_base_patch16 (Models/mae/models_mae.py:26-59,223-228): names / shapes as the module's,
+    initial values by the laws of initialize_weights (:63-93) from a seeded generator (not the module's RNG stream)."""
+    g = torch.Generator().manual_seed(seed)
+
+    def xavier(o, c):
+        b = math.sqrt(6.0 / (o + c))
+        return (torch.rand(o, c, generator=g) * 2 - 1) * b
+
+    sd = {"cls_token": torch.randn(1, 1, 768, generator=g) * 0.02, "pos_embed": sincos_2d(768),
+          "mask_token": torch.randn(1, 1, 512, generator=g) * 0.02, "decoder_pos_embed": sincos_2d(512)}
+    sd["patch_embed.proj.weight"] = xavier(768, 768).reshape(768, 3, 16, 16)
+    sd["patch_embed.proj.bias"] = (torch.rand(768, generator=g) * 2 - 1) / math.sqrt(768)
+
+    def blocks(prefix, depth, C):
+        for i in range(depth):
+            p = f"{prefix}{i}."
+            for n in ("norm1", "norm2"):
+                sd[p + n + ".weight"] = torch.ones(C)
+                sd[p + n + ".bias"] = torch.zeros(C)
+            for n, (o, c) in {"attn.qkv": (3 * C, C), "attn.proj": (C, C), "mlp.fc1": (4 * C, C), "mlp.fc2": (C, 4 * C)}.items():
+                sd[p + n + ".weight"] = xavier(o, c)
+                sd[p + n + ".bias"] = torch.zeros(o)
+
+    blocks("blocks.", 12, 768)
+    sd["norm.weight"], sd["norm.bias"] = torch.ones(768), torch.zeros(768)
+    sd["decoder_embed.weight"], sd["decoder_embed.bias"] = xavier(512, 768), torch.zeros(512)
+    blocks("decoder_blocks.", 8, 512)
+    sd["decoder_norm.weight"], sd["decoder_norm.bias"] = torch.ones(512), torch.zeros(512)
+    sd["decoder_pred.weight"], sd["decoder_pred.bias"] = xavier(768, 512), torch.zeros(768)
+    return {k: v.to(device) for k, v in sd.items()}
+
+
+MAE_FROZEN = ("pos_embed", "decoder_pos_embed")  # requires_grad=False, models_mae.py:37,50
+
+
+def mae_random_masking(x, noise, mask_ratio=0.75):
+    """models_mae.py:123-148 with the uniform noise passed in (the reference draws torch.rand(N, L) at :132)."""
+    N, L, D = x.shape
+    len_keep = int(L * (1 - mask_ratio))
+    ids_shuffle = torch.argsort(noise, dim=1)
+    ids_restore = torch.argsort(ids_shuffle, dim=1)
+    ids_keep = ids_shuffle[:, :len_keep]
+    x_masked = torch.gather(x, 1, ids_keep.unsqueeze(-1).repeat(1, 1, D))
+    mask = torch.ones([N, L], device=x.device, dtype=x.dtype)
+    mask[:, :len_keep] = 0
+    return x_masked, torch.gather(mask, 1, ids_restore), ids_restore
+
+
+def mae_patchify(imgs, p=16):
+    """models_mae.py:95-107."""
+    h = w = imgs.shape[2] // p
+    x = imgs.reshape(imgs.shape[0], 3, h, p, w, p)
+    return torch.einsum("nchpwq->nhwpqc", x).reshape(imgs.shape[0], h * w, p * p * 3)
+
+
+def mae_forward(sd, imgs, noise, mask_ratio=0.75, norm_pix_loss=True):
+    """MaskedAutoencoderViT.forward (models_mae.py:216-220): forward_encoder :150-170, forward_decoder :172-196,
+    forward_loss :198-214.  Returns (loss, pred [N, 196, 768], mask [N, 196])."""
+    x = patch_embed(sd, imgs) + sd["pos_embed"][:, 1:, :]
+    x, mask, ids_restore = mae_random_masking(x, noise, mask_ratio)
+    cls = (sd["cls_token"] + sd["pos_embed"][:, :1, :]).expand(x.shape[0], -1, -1)
+    x = torch.cat((cls, x), dim=1)
+    for i in range(12):
+        x = block(sd, i, x)
+    x = F.layer_norm(x, (768,), sd["norm.weight"], sd["norm.bias"], 1e-6)
+    x = F.linear(x, sd["decoder_embed.weight"], sd["decoder_embed.bias"])
+    mask_tokens = sd["mask_token"].repeat(x.shape[0], ids_restore.shape[1] + 1 - x.shape[1], 1)
+    x_ = torch.cat([x[:, 1:, :], mask_tokens], dim=1)
+    x_ = torch.gather(x_, 1, ids_restore.unsqueeze(-1).repeat(1, 1, x.shape[2]))
+    x = torch.cat([x[:, :1, :], x_], dim=1) + sd["decoder_pos_embed"]
+    for i in range(8):
+        x = block(sd, i, x, "decoder_blocks.", 16)
+    x = F.layer_norm(x, (512,), sd["decoder_norm.weight"], sd["decoder_norm.bias"], 1e-6)
+    pred = F.linear(x, sd["decoder_pred.weight"], sd["decoder_pred.bias"])[:, 1:, :]
+    target = mae_patchify(imgs)
+    if norm_pix_loss:
+        mean = target.mean(dim=-1, keepdim=True)
+        var = target.var(dim=-1, keepdim=True)
+        target = (target - mean) / (var + 1.0e-6) ** 0.5
+    loss = ((pred - target) ** 2).mean(dim=-1)
+    return (loss * mask).sum() / mask.sum(), pred, mask
+
+
+def mae_loss_and_grads(sd, imgs, noise, mask_ratio=0.75, norm_pix_loss=True):
+    """One MAE step's loss and parameter gradients (engine_pretrain.py:47-58 without the scaler)."""
+    params = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items() if k not in MAE_FROZEN}
+    full = dict(sd)
+    full.update(params)
+    loss, pred, mask = mae_forward(full, imgs, noise, mask_ratio, norm_pix_loss)
+    loss.backward()
+    return loss.detach(), pred.detach(), mask, {k: v.grad for k, v in params.items()}
+
+
+def mae_param_groups(sd, weight_decay=0.05):
+    """timm optim_factory.add_weight_decay as called at Models/mae/main_pretrain.py:179: no decay for 1-D tensors and
+    biases (cls_token / mask_token are 3-D and DO decay); frozen tensors are skipped."""
+    decay, no_decay = [], []
+    for k, v in sd.items():
+        if k in MAE_FROZEN:
+            continue
+        (no_decay if v.dim() == 1 or k.endswith(".bias") else decay).append(k)
+    return [{"names": no_decay, "weight_decay": 0.0}, {"names": decay, "weight_decay": weight_decay}]
+
+
+def mae_lr(it, it_per_epoch, base_lr, warmup_epochs=40, epochs=800, min_lr=0.0):
+    """Models/mae/util/lr_sched.py:9-21 called per iteration with epoch = it / len(loader) + epoch (engine_pretrain.py:42-43)."""
+    e = it / it_per_epoch
+    if e < warmup_epochs:
+        return base_lr * e / warmup_epochs
+    return min_lr + (base_lr - min_lr) * 0.5 * (1.0 + math.cos(math.pi * (e - warmup_epochs) / (epochs - warmup_epochs)))

@@ -200,3 +200,49 @@ def test_weighted_ce_restatement_matches_torch():
     w = torch.rand(23, generator=g) + 0.5
     assert torch.allclose(ref_port.weighted_ce_loss(x, y, w), torch.nn.CrossEntropyLoss(w)(x, y), rtol=1e-6)
     assert torch.allclose(ref_port.weighted_ce_loss(x, y), torch.nn.CrossEntropyLoss()(x, y), rtol=1e-6)
+
+
+def mae_inputs(B=2):
+    """The inputs of oracle/make_golden.py:mae_inputs (image batch, masking noise)."""
+    g = torch.Generator().manual_seed(5)
+    return torch.randn(B, 3, 224, 224, generator=g), torch.rand(B, 196, generator=g)
+
+
+def test_mae_step_matches_reference_fixture(golden_dir):
+    """One MAE pretraining step at B=2 fp32 (BASELINE.json config 5: mae_vit_base_patch16, norm_pix_loss, mask 0.75)
+    reproduces the unmodified Models/mae/models_mae.py: mask, prediction, loss, every gradient's norm and head."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    fix = np.load(os.path.join(golden_dir, "step_mae_b2.npz"))
+    sd = ref_port.mae_make_state(seed=42)
+    with open(os.path.join(golden_dir, "manifest_mae.json")) as f:
+        man = json.load(f)
+    assert sorted(sd) == sorted(man)
+    for k, (shape, dtype) in man.items():
+        assert list(sd[k].shape) == shape and str(sd[k].dtype) == dtype, k
+    x, noise = mae_inputs()
+    loss, pred, mask, grads = ref_port.mae_loss_and_grads(sd, x, noise)
+    assert torch.equal(mask, torch.from_numpy(fix["mask"]))
+    assert (pred[:, ::7, ::16] - torch.from_numpy(fix["pred_sub"])).abs().max().item() < 1e-4 * float(fix["pred_absmax"])
+    assert abs(loss.item() - float(fix["loss"])) < 1e-5 * abs(float(fix["loss"]))
+    assert sorted(grads) == sorted(fix["grad_names"].tolist())
+    floor = 1e-3 * float(np.median(fix["grad_norm"]))
+    for i, n in enumerate(fix["grad_names"].tolist()):
+        g, rn = grads[n], float(fix["grad_norm"][i])
+        assert abs(g.double().norm().item() - rn) < 2e-3 * max(rn, floor), n
+        k = min(8, g.numel())
+        assert (g.flatten()[:k] - torch.from_numpy(fix["grad_head"][i][:k])).abs().max().item() < 2e-3 * max(g.abs().max().item(), floor), n
+
+
+def test_mae_param_groups_and_lr():
+    """timm add_weight_decay rule (main_pretrain.py:179) and the per-iteration half-cosine (lr_sched.py:9-21)."""
+    sd = ref_port.mae_make_state(seed=1)
+    nd, d = ref_port.mae_param_groups(sd, 0.05)
+    assert nd["weight_decay"] == 0.0 and d["weight_decay"] == 0.05
+    assert "cls_token" in d["names"] and "mask_token" in d["names"] and "blocks.0.attn.qkv.weight" in d["names"]
+    assert "blocks.0.norm1.weight" in nd["names"] and "decoder_pred.bias" in nd["names"]
+    assert "pos_embed" not in nd["names"] + d["names"]
+    assert len(nd["names"]) + len(d["names"]) == len(sd) - 2
+    assert ref_port.mae_lr(0, 100, 1e-3) == 0.0
+    assert abs(ref_port.mae_lr(2000, 100, 1e-3) - 0.5e-3) < 1e-12         # half-way through warm-up (epoch 20 of 40)
+    assert abs(ref_port.mae_lr(4000, 100, 1e-3) - 1e-3) < 1e-12           # end of warm-up
+    assert abs(ref_port.mae_lr(80000, 100, 1e-3)) < 1e-12                 # end of the schedule
