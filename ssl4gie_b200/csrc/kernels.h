@@ -72,6 +72,23 @@ template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t s
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st, const Reducer* red = nullptr);  // out overwritten
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out = nullptr);  // inverse of above (+ optional T copy of the result)
+// MAE pretraining step (mae.cu; Models/mae/models_mae.py:123-214)
+int k_mae_masking(const float* noise, int* ids_restore, int* ids_keep, float* mask, int B, int L, int keep, cudaStream_t st);
+template <typename T> int k_mae_patchify_kept(const float* img, const int* ids_keep, T* out, int B, int keep, cudaStream_t st);
+int k_mae_assemble(const float* pe, const float* cls, const float* pos, const int* ids_keep, float* x, int B, int keep, int C, cudaStream_t st);
+template <typename T> int k_mae_assemble_bwd(const float* dx, T* dpe, float* dcls, int B, int keep, int C, cudaStream_t st);
+int k_mae_unshuffle(const float* de, const float* mask_token, const float* dpos, const int* ids_restore, float* y, int B, int L, int keep, int C, cudaStream_t st);
+size_t mae_unshuffle_scratch_bytes(int B, int C);
+template <typename T>
+int k_mae_unshuffle_bwd(const float* dy, const int* ids_restore, T* dde, float* dmask_token, int B, int L, int keep, int C, cudaStream_t st, const Reducer* r);
+// [rows, heads*32] <-> [rows, heads*64] (zero upper half); the first `scaled` heads are multiplied by `scale`
+template <typename T> int k_head_pad(const T* in, T* out, long long rows, int heads, int scaled, float scale, cudaStream_t st);
+template <typename T> int k_head_unpad(const T* in, T* out, long long rows, int heads, int scaled, float scale, cudaStream_t st);
+int k_drop_cls(const float* full, float* out, int B, int L, int C, cudaStream_t st);
+template <typename T> int k_add_cls_row(const float* dout, T* dfull, int B, int L, int C, cudaStream_t st);
+size_t mae_loss_scratch_bytes(int B);
+int k_mae_loss_fwd(const float* pred, const float* img, const float* mask, void* scratch, float* loss, int B, int norm_pix, cudaStream_t st);
+int k_mae_loss_bwd(const float* pred, const float* img, const float* mask, const void* scratch, const float* grad_out, float* dpred, int B, int norm_pix, cudaStream_t st);
 // classification tail (cls_head.cu): token pooling + lin_head on fp32 master weights; W == nullptr: no head (out = pooled)
 template <typename T>
 int k_cls_head_fwd(const T* hn, const float* W, const float* bias, float* pooled, float* out, int B, int N, int C,

