@@ -21,6 +21,19 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 GFLOP_PER_IMG = {"seg": 225.97, "depth": 214.86, "cls": 105.38}  # fwd+bwd = 3 x fwd, BASELINE.md §2 / SURVEY.md §8d
+
+
+def _mae_gflop_per_img():
+    """MAE pretraining step (config 5), 3 x forward: encoder on 50 tokens (49 kept patches embedded), decoder on 197."""
+    def stack(tokens, depth, C, heads):
+        lin = 2.0 * tokens * (3 * C * C + C * C + 8 * C * C)
+        att = heads * 4.0 * tokens * tokens * (C // heads)
+        return depth * (lin + att)
+    fwd = 2.0 * 49 * 768 * 768 + stack(50, 12, 768, 12) + 2.0 * 50 * 768 * 512 + stack(197, 8, 512, 16) + 2.0 * 197 * 512 * 768
+    return 3.0 * fwd / 1e9
+
+
+GFLOP_PER_IMG["mae"] = _mae_gflop_per_img()
 METRIC = "ViT-B/DPT seg train img/s @1/2/4/8 B200; % tensor-pipe peak; CPU baseline"
 
 
@@ -91,6 +104,8 @@ def synth(task, B, seed):
     x = torch.randn(B, 3, 224, 224, generator=g)
     if task == "seg":
         t = (torch.rand(B, 1, 224, 224, generator=g) > 0.5).float()
+    elif task == "mae":
+        t = torch.rand(B, 196, generator=g)  # the uniform noise of random_masking (models_mae.py:132)
     elif task == "cls":
         t = torch.randint(0, 23, (B,), generator=g)
     else:
@@ -107,6 +122,24 @@ def cpu_step_time(task, steps, warmup, batch=2):
     import torch
     from oracle import ref_port
     torch.set_num_threads(os.cpu_count())
+    if task == "mae":
+        sd = ref_port.mae_make_state(seed=42)
+        params = {k: v.clone().requires_grad_(True) for k, v in sd.items() if k not in ref_port.MAE_FROZEN}
+        full = dict(sd)
+        full.update(params)
+        opt = torch.optim.AdamW([{"params": [params[n] for n in g["names"]], "weight_decay": g["weight_decay"]}
+                                 for g in ref_port.mae_param_groups(sd)], lr=1e-3 * batch / 256, betas=(0.9, 0.95))
+        x, noise = synth(task, batch, 0)
+        times = []
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            opt.zero_grad()
+            loss, _, _ = ref_port.mae_forward(full, x, noise)
+            loss.backward()
+            opt.step()
+            if i >= warmup:
+                times.append(time.perf_counter() - t0)
+        return sum(times) / len(times), torch.get_num_threads()
     sd = ref_port.make_state(None, seed=42, head_classes=23) if task == "cls" else ref_port.make_state(task, seed=42)
     params = {k: v.clone().requires_grad_(True) for k, v in ref_port.trainable(sd).items()}
     full = dict(sd)
@@ -170,6 +203,9 @@ def run_ours(args):
     torch.manual_seed(42)
     if task == "cls":  # BASELINE.json configs[3]: 23-class Hyperkvasir-labelled fine-tune
         model = utils.get_ImageNet_or_random_ViT(True, 23, False, None, False, False)
+    elif task == "mae":  # BASELINE.json configs[4]: Models/mae/main_pretrain.py (mae_vit_base_patch16, norm_pix_loss, mask 0.75)
+        import ssl4gie_b200
+        model = ssl4gie_b200.mae_vit_base_patch16(norm_pix_loss=True)
     else:
         model = utils.get_ImageNet_or_random_ViT(False, 1 if task == "seg" else None, False, task, False, False)
     model.precision, model.backend = "bf16", "tensor"
@@ -179,9 +215,16 @@ def run_ours(args):
     model.train()
     if task == "cls":
         loss_fn = CrossEntropyLoss(torch.ones(23)).cuda(local)
+    elif task == "mae":
+        loss_fn = None  # the model returns its loss (models_mae.py:216-220)
     else:
         loss_fn = SoftDiceLoss() if task == "seg" else ScaleAndShiftInvariantLoss(alpha=0.1)
-    opt = FusedAdamW(model, lr=1e-4, grad_scale=1.0 / world)
+    if task == "mae":  # main_pretrain.py:179-180: timm add_weight_decay groups, AdamW betas (0.9, 0.95); blr 1e-3 * 64 * world / 256
+        import ssl4gie_b200
+        opt = FusedAdamW(model, lr=1e-3 * B * world / 256, betas=(0.9, 0.95), grad_scale=1.0 / world,
+                         param_groups=ssl4gie_b200.add_weight_decay(model, 0.05))
+    else:
+        opt = FusedAdamW(model, lr=1e-4, grad_scale=1.0 / world)
     ddp = GradientAllReduce(model)
     ddp.prepare(B)
     engine = Engine.of(model)
@@ -195,11 +238,14 @@ def run_ours(args):
     def step(x, t, readback):
         t_host = time.perf_counter()
         h = engine.handle(B)
-        out = model(x)
+        if task == "mae":
+            loss, _, _ = model(x, mask_ratio=0.75, noise=t)
+        else:
+            out = model(x)
+            loss = loss_fn(out, t)
         launches["n"] += h.launches()
-        loss = loss_fn(out, t)
         loss.backward()
-        launches["n"] += h.launches() + {"seg": 4, "depth": 8, "cls": 2}[task]
+        launches["n"] += h.launches() + {"seg": 4, "depth": 8, "cls": 2, "mae": 3}[task]
         ddp.reduce()
         opt.step()
         launches["n"] += 1
@@ -287,7 +333,7 @@ def run_ours(args):
 
     roof = kernel_roofline(min(B, 64)) if rank == 0 else None
     extra = None
-    if rank == 0 and world == 1 and not args.no_extras:
+    if rank == 0 and world == 1 and not args.no_extras and task != "mae":
         # free this process's 17 GB workspace before the side measurements share the GPU with it
         # host time to ENQUEUE one step: measured on an idle device (inside the timed loop the host blocks on the full launch
         # queue, which measures the GPU, not the host)
@@ -313,7 +359,8 @@ def run_ours(args):
         line = {"metric": METRIC, "value": img_s, "unit": "img/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic",
-                "config": {"workload": f"vitb16_dpt_{task}_train_step_bf16_b{B}_per_gpu_224", "images_per_gpu": B,
+                "config": {"workload": (f"mae_vitb16_pretrain_step_mask75_bf16_b{B}_per_gpu_224" if task == "mae" else
+                                        f"vitb16_dpt_{task}_train_step_bf16_b{B}_per_gpu_224"), "images_per_gpu": B,
                            "step": "fwd + loss + bwd + grad all-reduce + AdamW", "parallelism": f"dp{world}",
                            "l2": "per-step working set (>10 GB of activations) is far larger than the 126 MB L2; no flush needed"},
                 "model_tflops_per_gpu": tflops, "mfu_of_measured_sustained": tflops / sustained, "mfu_of_spec_2250": tflops / 2250.0,
@@ -431,7 +478,7 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--task", default="seg", choices=["seg", "depth", "cls"])
+    ap.add_argument("--task", default="seg", choices=["seg", "depth", "cls", "mae"])
     ap.add_argument("--batch", type=int, default=0, help="images per GPU (default: 64 seg/depth, 128 cls as BASELINE.json)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the depth / cls / torch-eager / per-family side measurements")

@@ -38,6 +38,7 @@ extern "C" {
 #define S4G_DENSE_NONE 0  /* classification branch, Models/models.py:348-354 */
 #define S4G_DENSE_SEG 1   /* dense="seg"   */
 #define S4G_DENSE_DEPTH 2 /* dense="depth" */
+#define S4G_DENSE_MAE 3   /* MaskedAutoencoderViT (mae_vit_base_patch16): out = pred [B,196,768], Models/mae/models_mae.py:150-196 */
 
 #define S4G_BACKEND_SIMT 0    /* FFMA kernels: fp32 validation mode / cross-check */
 #define S4G_BACKEND_TENSOR 1  /* tcgen05 + TMEM + TMA contractions, tensor-core attention (bf16 only) */
@@ -82,6 +83,10 @@ int s4g_model_set_workspace(S4GModel* m, void* workspace, size_t bytes);
  * dropout_mask: optional [B*112*112*256] bytes (NHWC) overriding the RNG (parity tests); NULL = RNG. */
 int s4g_model_forward(S4GModel* m, const float* images, float* out, int training, uint64_t seed,
                       const uint8_t* dropout_mask, void* stream);
+/* S4G_DENSE_MAE only, before s4g_model_forward: noise [B,196] = the uniform noise random_masking draws
+ * (Models/mae/models_mae.py:132; smallest 49 per image are kept); mask_out [B,196] float (0 keep, 1 remove, :141-145) and
+ * ids_restore_out [B,196] int32 (:136) are optional.  The pointers are read / written by every later forward. */
+int s4g_model_set_mae_io(S4GModel* m, const float* noise, float* mask_out, int* ids_restore_out);
 /* dout: gradient w.r.t. `out`.  Writes (overwrites) the gradient of every bound parameter that has one. */
 int s4g_model_backward(S4GModel* m, const float* dout, void* stream);
 /* Cross-rank sum used by SyncBatchNorm statistics (forward: sum/sumsq, backward: sum dy / sum dy*xhat).  Called
@@ -167,6 +172,14 @@ int s4g_ssi_fwd(const float* pred, const float* target, void* scratch, float* lo
                 int W, float alpha, int scales, int image_based, void* stream);
 int s4g_ssi_bwd(const float* pred, const float* target, void* scratch, const float* grad_out, float* dpred, int B,
                 int H, int W, float alpha, int scales, void* stream);
+/* MaskedAutoencoderViT.forward_loss (Models/mae/models_mae.py:198-214): target = patchify(images) (:95-107), per-patch
+ * (t - mean) / sqrt(var + 1e-6) with the unbiased variance when norm_pix != 0, loss = sum(mean_e (pred - t)^2 * mask) /
+ * sum(mask).  pred / dpred [B,196,768], images [B,3,224,224], mask [B,196]; scratch kept between fwd and bwd. */
+size_t s4g_mae_loss_scratch_bytes(int B);
+int s4g_mae_loss_fwd(const float* pred, const float* images, const float* mask, void* scratch, float* loss, int B,
+                     int norm_pix, void* stream);
+int s4g_mae_loss_bwd(const float* pred, const float* images, const float* mask, const void* scratch,
+                     const float* grad_out, float* dpred, int B, int norm_pix, void* stream);
 /* nn.CrossEntropyLoss(weight) of the classification fine-tune (Classification/train_classification.py:278):
  * loss = sum_i w[y_i] * -log softmax(x_i)[y_i] / sum_i w[y_i].  labels int64 [B]; class_weight [num_classes] or NULL.
  * dlogits_unit [B,num_classes] receives dloss/dlogits for grad_out = 1 (kept between fwd and bwd). */
@@ -178,6 +191,11 @@ int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits,
  * (1/world_size after a sum-all-reduce). step counts from 1. */
 int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                    float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);
+/* The same with parameter groups (timm add_weight_decay + AdamW(betas=(0.9, 0.95)), Models/mae/main_pretrain.py:179-180):
+ * weight_decay_per_slot[n / 64] holds the weight decay of each 64-float arena slot (parameters start on slot boundaries). */
+int s4g_adamw_step_groups(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                          float beta1, float beta2, float eps, const float* weight_decay_per_slot, int step,
+                          float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

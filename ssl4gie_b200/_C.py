@@ -6,7 +6,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssl4gie_b200.so")
 
 F32, BF16 = 0, 1
-DENSE = {None: 0, False: 0, "seg": 1, "depth": 2}
+DENSE = {None: 0, False: 0, "seg": 1, "depth": 2, "mae": 3}
 SIMT, TENSOR = 0, 1
 
 
@@ -33,6 +33,7 @@ SIGNATURES = {
     "s4g_model_set_workspace": (_i, [_vp, _vp, _sz]),
     "s4g_model_forward": (_i, [_vp, _vp, _vp, _i, _u64, _vp, _vp]),
     "s4g_model_backward": (_i, [_vp, _vp, _vp]),
+    "s4g_model_set_mae_io": (_i, [_vp, _vp, _vp, _vp]),
     "s4g_model_set_allreduce": (_i, [_vp, ALLREDUCE_FN, _vp]),
     "s4g_peer_mailbox_bytes": (_sz, []),
     "s4g_peer_alloc": (_i, [_sz, ctypes.POINTER(_vp), ctypes.c_char_p]),
@@ -65,6 +66,10 @@ SIGNATURES = {
     "s4g_ce_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "s4g_ce_bwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "s4g_adamw_step": (_i, [_vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _f, _i, _f, _vp]),
+    "s4g_adamw_step_groups": (_i, [_vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _vp, _i, _f, _vp]),
+    "s4g_mae_loss_scratch_bytes": (_sz, [_i]),
+    "s4g_mae_loss_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "s4g_mae_loss_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
 }
 
 _lib = None

@@ -141,6 +141,12 @@ int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp
                    float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
   return k_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, grad_scale, ST(stream));
 }
+int s4g_adamw_step_groups(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                          float beta1, float beta2, float eps, const float* weight_decay_per_slot, int step, float grad_scale,
+                          void* stream) {
+  if (!weight_decay_per_slot || n % 64) { s4g_set_error("adamw_step_groups: need one weight decay per 64-float slot"); return S4G_ERR_SHAPE; }
+  return k_adamw(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, 0.f, step, grad_scale, ST(stream), weight_decay_per_slot);
+}
 
 size_t s4g_peer_mailbox_bytes(void) { return k_peer_mailbox_bytes(); }
 int s4g_peer_alloc(size_t bytes, void** dptr, unsigned char handle[S4G_PEER_HANDLE_BYTES]) {
@@ -178,6 +184,18 @@ int s4g_peer_check(void* own_mailbox) {
     return S4G_ERR_STATE;
   }
   return 0;
+}
+
+size_t s4g_mae_loss_scratch_bytes(int B) { return mae_loss_scratch_bytes(B); }
+int s4g_mae_loss_fwd(const float* pred, const float* images, const float* mask, void* scratch, float* loss, int B,
+                     int norm_pix, void* stream) {
+  if (!pred || !images || !mask || !scratch || !loss || B < 1) { s4g_set_error("mae_loss_fwd: bad argument"); return S4G_ERR_STATE; }
+  return k_mae_loss_fwd(pred, images, mask, scratch, loss, B, norm_pix, ST(stream));
+}
+int s4g_mae_loss_bwd(const float* pred, const float* images, const float* mask, const void* scratch,
+                     const float* grad_out, float* dpred, int B, int norm_pix, void* stream) {
+  if (!pred || !images || !mask || !scratch || !grad_out || !dpred || B < 1) { s4g_set_error("mae_loss_bwd: bad argument"); return S4G_ERR_STATE; }
+  return k_mae_loss_bwd(pred, images, mask, scratch, grad_out, dpred, B, norm_pix, ST(stream));
 }
 
 }  // extern "C"

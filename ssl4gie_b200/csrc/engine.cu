@@ -78,6 +78,11 @@ struct S4GModel {
   int training = 1;
   uint64_t seed = 0;
   const uint8_t* dropout_mask = nullptr;
+  // MAE pretraining step (S4G_DENSE_MAE): masking noise in, mask / ids_restore out (s4g_model_set_mae_io)
+  const float* mae_noise = nullptr;
+  float* mae_mask_out = nullptr;
+  int* mae_ids_restore_out = nullptr;
+  size_t mae_mask_off = 0, mae_ids_restore_off = 0;
   std::vector<std::string> enc_param_order;  // names in backward completion order (for buckets)
   std::vector<std::string> dec_param_names;
   std::vector<size_t> enc_block_mark;         // bwd_enc index at which block i's grads are complete
@@ -798,24 +803,294 @@ struct Builder {
     });
   }
 
+  // ---- generic pre-LN transformer stack (timm 0.6.12 Block) for the MAE pretraining step ---------------------------------
+  // The fine-tuning encoder above is specialised (taps, 197 tokens, fused delta); this one takes (tokens, C, heads) and is
+  // used for the 50-token encoder and the 512-d / 16-head decoder of Models/mae/models_mae.py:41-59.  Head dims of 32 run on
+  // the 64-dim attention kernels through a zero-padded copy of q | k | v: q is scaled by sqrt(2) in the pad pass, so the
+  // kernels' 64^-1/2 becomes 32^-1/2, and dq by sqrt(2) in the un-pad pass.
+  struct TBlock {
+    Param *n1w, *n1b, *n2w, *n2b;
+    Lin qkv, proj, fc1, fc2;
+    size_t h1, mean1, rstd1, qkvb, qkvp, ao, aop, lse, h2, mean2, rstd2, u, a;
+    RedSlot ln1_red, ln2_red, gelu_red;
+  };
+  struct TStack {
+    int C = 0, H = 0, D = 0, N = 0, depth = 0;
+    long long Tk = 0;
+    std::vector<TBlock> blocks;
+    std::vector<size_t> xs;  // fp32 residual stream: xs[2i] block i input, xs[2i+1] after attention, xs[2*depth] output
+    size_t dxa = 0, dxb = 0, dxT = 0, dh = 0, du = 0, dao = 0, daop = 0, dqkv = 0, dqkvp = 0;
+  };
+  int attn_fwd_g(const T* qkv, T* o, float* lse, int N, int H, cudaStream_t st) const {
+    m->launches++;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (tensor) return attn_fwd_mma(qkv, o, lse, B, N, H, st);
+    }
+    return attn_fwd_simt<T>(qkv, o, lse, B, N, H, st);
+  }
+  int attn_bwd_g(const T* qkv, const T* o, const T* dout, const float* lse, T* dqkv_, int N, int H, cudaStream_t st) const {
+    m->launches++;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (tensor) return attn_bwd_mma(qkv, o, dout, lse, dqkv_, B, N, H, st, nullptr);
+    }
+    return attn_bwd_simt<T>(qkv, o, dout, lse, dqkv_, B, N, H, st);
+  }
+  // forward closures go to m->fwd, backward closures (one per block, forward order) to *bl
+  TStack* tstack(const std::string& prefix, int depth, int C, int H, int N, std::vector<Op>* bl) {
+    stacks.emplace_back(new TStack());
+    TStack* s = stacks.back().get();
+    s->C = C; s->H = H; s->D = C / H; s->N = N; s->depth = depth; s->Tk = (long long)B * N;
+    Builder* self = this;
+    S4GModel* mm = m;
+    const long long Tk = s->Tk;
+    const int C3 = 3 * C, C4 = 4 * C, HP = H * 64;
+    const bool pad = s->D == 32;
+    s->xs.resize(2 * depth + 1);
+    for (auto& x : s->xs) x = alloc(sizeof(float) * Tk * C);
+    for (int i = 0; i < depth; ++i) {
+      const std::string p = prefix + std::to_string(i) + ".";
+      TBlock b{};
+      b.n1w = P(p + "norm1.weight"); b.n1b = P(p + "norm1.bias");
+      b.n2w = P(p + "norm2.weight"); b.n2b = P(p + "norm2.bias");
+      b.qkv = linear(p + "attn.qkv", C3, C); b.proj = linear(p + "attn.proj", C, C);
+      b.fc1 = linear(p + "mlp.fc1", C4, C); b.fc2 = linear(p + "mlp.fc2", C, C4);
+      b.h1 = alloc(sizeof(T) * Tk * C); b.h2 = alloc(sizeof(T) * Tk * C);
+      b.mean1 = alloc(sizeof(float) * Tk); b.rstd1 = alloc(sizeof(float) * Tk);
+      b.mean2 = alloc(sizeof(float) * Tk); b.rstd2 = alloc(sizeof(float) * Tk);
+      b.qkvb = alloc(sizeof(T) * Tk * C3); b.ao = alloc(sizeof(T) * Tk * C);
+      if (pad) { b.qkvp = alloc(sizeof(T) * Tk * 3 * HP); b.aop = alloc(sizeof(T) * Tk * HP); }
+      b.lse = alloc(sizeof(float) * (size_t)B * H * N);
+      b.u = alloc(sizeof(T) * Tk * C4); b.a = alloc(sizeof(T) * Tk * C4);
+      b.ln1_red = red_alloc(ln_bwd_scratch_bytes(C)); b.ln2_red = red_alloc(ln_bwd_scratch_bytes(C));
+      b.gelu_red = red_alloc(colsum_scratch_bytes(C4));
+      note_wgrad(linear_geom(Tk, C3, C)); note_wgrad(linear_geom(Tk, C, C));
+      note_wgrad(linear_geom(Tk, C4, C)); note_wgrad(linear_geom(Tk, C, C4));
+      s->blocks.push_back(b);
+      const size_t xin = s->xs[2 * i], xmid = s->xs[2 * i + 1], xout = s->xs[2 * i + 2];
+      m->fwd.push_back([=](cudaStream_t st) {
+        float* x0 = mm->template at<float>(xin);
+        float* x1 = mm->template at<float>(xmid);
+        float* x2 = mm->template at<float>(xout);
+        T* h1 = mm->template at<T>(b.h1);
+        T* h2 = mm->template at<T>(b.h2);
+        T* qkv = mm->template at<T>(b.qkvb);
+        T* ao = mm->template at<T>(b.ao);
+        mm->launches += 2;
+        S4G_TRY(k_layernorm_fwd<T>(x0, b.n1w->p, b.n1b->p, h1, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), (int)Tk, C, 1e-6f, st));
+        S4G_TRY(self->fprop(linear_geom(Tk, C3, C), h1, mm->template at<T>(b.qkv.wf), epi(qkv, C3, b.qkv.b->p), st));
+        if (pad) {
+          T* qp = mm->template at<T>(b.qkvp);
+          T* op = mm->template at<T>(b.aop);
+          mm->launches += 2;
+          S4G_TRY(k_head_pad<T>(qkv, qp, Tk, 3 * H, H, 1.41421356237309505f, st));
+          S4G_TRY(self->attn_fwd_g(qp, op, mm->template at<float>(b.lse), N, H, st));
+          S4G_TRY(k_head_unpad<T>(op, ao, Tk, H, 0, 1.f, st));
+        } else {
+          S4G_TRY(self->attn_fwd_g(qkv, ao, mm->template at<float>(b.lse), N, H, st));
+        }
+        EpiParams e1 = epi(x1, C, b.proj.b->p, EPI_NONE, 1);
+        e1.res = x0; e1.res_f32 = 1; e1.ldr = C;
+        S4G_TRY(self->fprop(linear_geom(Tk, C, C), ao, mm->template at<T>(b.proj.wf), e1, st));
+        S4G_TRY(k_layernorm_fwd<T>(x1, b.n2w->p, b.n2b->p, h2, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), (int)Tk, C, 1e-6f, st));
+        if (self->umma_path()) {
+          S4G_TRY(self->fprop(linear_geom(Tk, C4, C), h2, mm->template at<T>(b.fc1.wf), epi(mm->template at<T>(b.u), C4, b.fc1.b->p), st));
+          mm->launches++;
+          S4G_TRY(k_gelu<T>(mm->template at<T>(b.u), mm->template at<T>(b.a), Tk * C4, st, mm->template at<T>(b.u)));
+        } else {
+          EpiParams e2 = epi(mm->template at<T>(b.a), C4, b.fc1.b->p, EPI_GELU);
+          e2.out2 = mm->template at<T>(b.u);
+          S4G_TRY(self->fprop(linear_geom(Tk, C4, C), h2, mm->template at<T>(b.fc1.wf), e2, st));
+        }
+        EpiParams e3 = epi(x2, C, b.fc2.b->p, EPI_NONE, 1);
+        e3.res = x1; e3.res_f32 = 1; e3.ldr = C;
+        return self->fprop(linear_geom(Tk, C, C4), mm->template at<T>(b.a), mm->template at<T>(b.fc2.wf), e3, st);
+      });
+    }
+    s->dxa = alloc(sizeof(float) * Tk * C); s->dxb = alloc(sizeof(float) * Tk * C);
+    s->dxT = alloc(sizeof(T) * Tk * C); s->dh = alloc(sizeof(T) * Tk * C);
+    s->du = alloc(sizeof(T) * Tk * C4); s->dao = alloc(sizeof(T) * Tk * C); s->dqkv = alloc(sizeof(T) * Tk * C3);
+    if (pad) { s->daop = alloc(sizeof(T) * Tk * HP); s->dqkvp = alloc(sizeof(T) * Tk * 3 * HP); }
+    for (int i = 0; i < depth; ++i) {
+      const TBlock b = s->blocks[i];
+      const size_t xin = s->xs[2 * i], xmid = s->xs[2 * i + 1];
+      float* prev_fc2_bias_g = i > 0 ? s->blocks[i - 1].fc2.b->g : nullptr;
+      const bool last = i == depth - 1;
+      bl->push_back([=](cudaStream_t st) {
+        // incoming: fp32 gradient of the block output in dxa and its T copy in dxT (written by whoever produced dxa); the
+        // gradient of the block input is left the same way
+        float* dxo = mm->template at<float>(s->dxa);
+        float* dxm = mm->template at<float>(s->dxb);
+        T* dxt = mm->template at<T>(s->dxT);
+        T* dhb = mm->template at<T>(s->dh);
+        T* dub = mm->template at<T>(s->du);
+        T* daob = mm->template at<T>(s->dao);
+        T* dqkvb = mm->template at<T>(s->dqkv);
+        mm->launches += 2;
+        const Reducer rg = self->red(b.gelu_red, true);
+        if (self->umma_path()) {
+          EpiParams e = epi(dub, C4, nullptr, EPI_MUL);
+          e.aux = mm->template at<T>(b.u);
+          S4G_TRY(self->fprop(linear_geom(Tk, C4, C), dxt, mm->template at<T>(b.fc2.wd), e, st));
+          mm->launches++;
+          if (b.fc1.b->g) S4G_TRY(k_colsum<T>(dub, b.fc1.b->g, Tk, C4, C4, st, &rg));
+        } else {
+          EpiParams e = epi(dub, C4, nullptr, EPI_DGELU);
+          e.aux = mm->template at<T>(b.u);
+          S4G_TRY(self->fprop(linear_geom(Tk, C4, C), dxt, mm->template at<T>(b.fc2.wd), e, st));
+        }
+        S4G_TRY(self->linear_param_grads(b.fc2, dxt, mm->template at<T>(b.a), Tk, st, !last));
+        S4G_TRY(self->fprop(linear_geom(Tk, C, C4), dub, mm->template at<T>(b.fc1.wd), epi(dhb, C), st));
+        S4G_TRY(self->linear_param_grads(b.fc1, dub, mm->template at<T>(b.h2), Tk, st, self->umma_path()));
+        const Reducer r2 = self->red(b.ln2_red, true), r1 = self->red(b.ln1_red, true);
+        S4G_TRY(k_layernorm_bwd<T>(dhb, mm->template at<float>(xmid), b.n2w->p, mm->template at<float>(b.mean2), mm->template at<float>(b.rstd2), dxo, dxm, b.n2w->g, b.n2b->g, (int)Tk, C, st, dxt, b.proj.b->g, &r2));
+        S4G_TRY(self->fprop(linear_geom(Tk, C, C), dxt, mm->template at<T>(b.proj.wd), epi(daob, C), st));
+        S4G_TRY(self->linear_param_grads(b.proj, dxt, mm->template at<T>(b.ao), Tk, st, true));
+        if (pad) {
+          T* dop = mm->template at<T>(s->daop);
+          T* dqp = mm->template at<T>(s->dqkvp);
+          mm->launches += 2;
+          S4G_TRY(k_head_pad<T>(daob, dop, Tk, H, 0, 1.f, st));
+          S4G_TRY(self->attn_bwd_g(mm->template at<T>(b.qkvp), mm->template at<T>(b.aop), dop, mm->template at<float>(b.lse), dqp, N, H, st));
+          S4G_TRY(k_head_unpad<T>(dqp, dqkvb, Tk, 3 * H, H, 1.41421356237309505f, st));
+        } else {
+          S4G_TRY(self->attn_bwd_g(mm->template at<T>(b.qkvb), mm->template at<T>(b.ao), daob, mm->template at<float>(b.lse), dqkvb, N, H, st));
+        }
+        S4G_TRY(self->fprop(linear_geom(Tk, C, C3), dqkvb, mm->template at<T>(b.qkv.wd), epi(dhb, C), st));
+        S4G_TRY(self->linear_param_grads(b.qkv, dqkvb, mm->template at<T>(b.h1), Tk, st));
+        return k_layernorm_bwd<T>(dhb, mm->template at<float>(xin), b.n1w->p, mm->template at<float>(b.mean1), mm->template at<float>(b.rstd1), dxm, dxo, b.n1w->g, b.n1b->g, (int)Tk, C, st, dxt, prev_fc2_bias_g, &r1);
+      });
+    }
+    return s;
+  }
+  std::vector<std::unique_ptr<TStack>> stacks;
+
+  // ---- MAE pretraining step: MaskedAutoencoderViT.forward up to `pred` (Models/mae/models_mae.py:150-196) ----------------
+  // out = pred [B, 196, 768] (fp32); the masked norm-pix loss (:198-214) is its own entry point (k_mae_loss_*).
+  void build_mae() {
+    Builder* self = this;
+    S4GModel* mm = m;
+    constexpr int L = 196, KEEP = 49, CE = 768, CD = 512;   // int(L * (1 - 0.75)) = 49 (:130)
+    const long long Pk = (long long)B * KEEP, Te = (long long)B * (KEEP + 1), Td = (long long)B * (L + 1);
+    const size_t ids_restore = alloc(sizeof(int) * (size_t)B * L), ids_keep = alloc(sizeof(int) * (size_t)Pk);
+    const size_t mask = alloc(sizeof(float) * (size_t)B * L);
+    m->mae_mask_off = mask; m->mae_ids_restore_off = ids_restore;
+    patches = alloc(sizeof(T) * Pk * CE);
+    pe = alloc(sizeof(float) * Pk * CE);
+    pe_lin = linear("patch_embed.proj", CE, CE, false);
+    note_wgrad(linear_geom(Pk, CE, CE));
+    Param* cls = P("cls_token");
+    Param* pos = P("pos_embed");
+    Param* dpos = P("decoder_pos_embed");
+    Param* mtok = P("mask_token");
+    // ---------------- forward ----------------
+    const size_t fwd_head = m->fwd.size();
+    m->fwd.push_back(nullptr);  // filled below once the encoder stack (its xs[0]) exists
+    bwd = &m->bwd_enc;
+    m->bwd_enc.push_back(nullptr);  // [0] = patch embed / token assembly backward, filled below
+    TStack* enc = tstack("blocks.", 12, CE, 12, KEEP + 1, &m->bwd_enc);
+    m->fwd[fwd_head] = [=](cudaStream_t st) {
+      if (!mm->mae_noise) { s4g_set_error("MAE forward: s4g_model_set_mae_io(noise, ...) has not been called"); return (int)S4G_ERR_STATE; }
+      int* keep = mm->template at<int>(ids_keep);
+      mm->launches += 4;
+      S4G_TRY(k_mae_masking(mm->mae_noise, mm->template at<int>(ids_restore), keep, mm->template at<float>(mask), self->B, L, KEEP, st));
+      S4G_TRY(k_mae_patchify_kept<T>(mm->images, keep, mm->template at<T>(self->patches), self->B, KEEP, st));
+      EpiParams e = epi(mm->template at<float>(self->pe), CE, self->pe_lin.b->p, EPI_NONE, 1);
+      S4G_TRY(self->fprop(linear_geom(Pk, CE, CE), mm->template at<T>(self->patches), mm->template at<T>(self->pe_lin.wf), e, st));
+      return k_mae_assemble(mm->template at<float>(self->pe), cls->p, pos->p, keep, mm->template at<float>(enc->xs[0]), self->B, KEEP, CE, st);
+    };
+    m->bwd_enc[0] = [=](cudaStream_t st) {
+      T* dpe = mm->template at<T>(enc->dxT);   // [B*49, 768] fits in the [B*50, 768] buffer
+      mm->launches++;
+      S4G_TRY(k_mae_assemble_bwd<T>(mm->template at<float>(enc->dxa), dpe, cls->g, self->B, KEEP, CE, st));
+      return self->linear_param_grads(self->pe_lin, dpe, mm->template at<T>(self->patches), Pk, st);
+    };
+    // encoder norm -> decoder_embed -> mask tokens + un-shuffle + decoder pos (:173-185)
+    bwd = &m->bwd_dec;
+    Param* nw = P("norm.weight");
+    Param* nb = P("norm.bias");
+    const Lin dembed = linear("decoder_embed", CD, CE);
+    note_wgrad(linear_geom(Te, CD, CE));
+    const size_t hn = alloc(sizeof(T) * Te * CE), nmean = alloc(sizeof(float) * Te), nrstd = alloc(sizeof(float) * Te);
+    const size_t de = alloc(sizeof(float) * Te * CD), dde = alloc(sizeof(T) * Te * CD), dhn = alloc(sizeof(T) * Te * CE);
+    const RedSlot n_red = red_alloc(ln_bwd_scratch_bytes(CE)), mt_red = red_alloc(mae_unshuffle_scratch_bytes(B, CD));
+    const size_t fwd_mid = m->fwd.size();
+    m->fwd.push_back(nullptr);
+    const size_t bwd_mid = m->bwd_dec.size();
+    m->bwd_dec.push_back(nullptr);
+    TStack* dec = tstack("decoder_blocks.", 8, CD, 16, L + 1, &m->bwd_dec);
+    const size_t x_enc_out = enc->xs[2 * enc->depth];
+    m->fwd[fwd_mid] = [=](cudaStream_t st) {
+      mm->launches += 2;
+      S4G_TRY(k_layernorm_fwd<T>(mm->template at<float>(x_enc_out), nw->p, nb->p, mm->template at<T>(hn), mm->template at<float>(nmean),
+                                 mm->template at<float>(nrstd), (int)Te, CE, 1e-6f, st));
+      EpiParams e = epi(mm->template at<float>(de), CD, dembed.b->p, EPI_NONE, 1);
+      S4G_TRY(self->fprop(linear_geom(Te, CD, CE), mm->template at<T>(hn), mm->template at<T>(dembed.wf), e, st));
+      return k_mae_unshuffle(mm->template at<float>(de), mtok->p, dpos->p, mm->template at<int>(ids_restore),
+                             mm->template at<float>(dec->xs[0]), self->B, L, KEEP, CD, st);
+    };
+    m->bwd_dec[bwd_mid] = [=](cudaStream_t st) {
+      T* ddeb = mm->template at<T>(dde);
+      T* dhnb = mm->template at<T>(dhn);
+      mm->launches += 2;
+      const Reducer rm = self->red(mt_red, true), rn = self->red(n_red, true);
+      S4G_TRY(k_mae_unshuffle_bwd<T>(mm->template at<float>(dec->dxa), mm->template at<int>(ids_restore), ddeb, mtok->g, self->B, L, KEEP, CD, st, &rm));
+      S4G_TRY(self->fprop(linear_geom(Te, CE, CD), ddeb, mm->template at<T>(dembed.wd), epi(dhnb, CE), st));
+      S4G_TRY(self->linear_param_grads(dembed, ddeb, mm->template at<T>(hn), Te, st));
+      // gradient of the encoder output: fp32 in enc->dxa with its T copy in enc->dxT, as the block backward expects
+      return k_layernorm_bwd<T>(dhnb, mm->template at<float>(x_enc_out), nw->p, mm->template at<float>(nmean), mm->template at<float>(nrstd),
+                                nullptr, mm->template at<float>(enc->dxa), nw->g, nb->g, (int)Te, CE, st, mm->template at<T>(enc->dxT), nullptr, &rn);
+    };
+    // decoder_norm -> decoder_pred -> drop cls (:190-194)
+    Param* dnw = P("decoder_norm.weight");
+    Param* dnb = P("decoder_norm.bias");
+    const Lin pred = linear("decoder_pred", CE, CD);
+    note_wgrad(linear_geom(Td, CE, CD));
+    const size_t hd = alloc(sizeof(T) * Td * CD), dmean = alloc(sizeof(float) * Td), drstd = alloc(sizeof(float) * Td);
+    const size_t pfull = alloc(sizeof(float) * Td * CE), dpf = alloc(sizeof(T) * Td * CE), dhd = alloc(sizeof(T) * Td * CD);
+    const RedSlot dn_red = red_alloc(ln_bwd_scratch_bytes(CD));
+    const size_t x_dec_out = dec->xs[2 * dec->depth];
+    m->fwd.push_back([=](cudaStream_t st) {
+      mm->launches += 2;
+      S4G_TRY(k_layernorm_fwd<T>(mm->template at<float>(x_dec_out), dnw->p, dnb->p, mm->template at<T>(hd), mm->template at<float>(dmean),
+                                 mm->template at<float>(drstd), (int)Td, CD, 1e-6f, st));
+      EpiParams e = epi(mm->template at<float>(pfull), CE, pred.b->p, EPI_NONE, 1);
+      S4G_TRY(self->fprop(linear_geom(Td, CE, CD), mm->template at<T>(hd), mm->template at<T>(pred.wf), e, st));
+      return k_drop_cls(mm->template at<float>(pfull), mm->out, self->B, L, CE, st);
+    });
+    m->bwd_dec.push_back([=](cudaStream_t st) {
+      T* dpfb = mm->template at<T>(dpf);
+      T* dhdb = mm->template at<T>(dhd);
+      mm->launches += 2;
+      S4G_TRY(k_add_cls_row<T>(mm->dout, dpfb, self->B, L, CE, st));
+      S4G_TRY(self->fprop(linear_geom(Td, CD, CE), dpfb, mm->template at<T>(pred.wd), epi(dhdb, CD), st));
+      S4G_TRY(self->linear_param_grads(pred, dpfb, mm->template at<T>(hd), Td, st));
+      const Reducer rn = self->red(dn_red, true);
+      return k_layernorm_bwd<T>(dhdb, mm->template at<float>(x_dec_out), dnw->p, mm->template at<float>(dmean), mm->template at<float>(drstd),
+                                nullptr, mm->template at<float>(dec->dxa), dnw->g, dnb->g, (int)Td, CD, st, mm->template at<T>(dec->dxT), nullptr, &rn);
+    });
+  }
+
   int finish() {
     if (!lin_jobs.empty()) {
-      if (lin_jobs.size() > 80) { s4g_set_error("internal: more than 80 linear layers"); return S4G_ERR_STATE; }
       Builder* self = this;
       S4GModel* mm = m;
-      // first in the pack list: conv_s2 re-packs through the same kernel family afterwards
+      // first in the pack list: conv_s2 re-packs through the same kernel family afterwards.  80 layers per grouped launch.
       m->pack.insert(m->pack.begin(), [self, mm](cudaStream_t st) {
-        PackLinearJobs jobs;
-        int tiles = 0, n = 0;
-        for (const Lin& l : self->lin_jobs) {
-          PackLinearJob& j = jobs.job[n++];
-          j.src = l.w->p; j.wp = mm->template at<T>(l.wf); j.wt = l.wd ? (void*)mm->template at<T>(l.wd) : nullptr;
-          j.N = l.N; j.K = l.K; j.tile0 = tiles; j.pad = 0;
-          tiles += cdiv(l.N, 32) * cdiv(l.K, 32);
+        for (size_t first = 0; first < self->lin_jobs.size(); first += 80) {
+          PackLinearJobs jobs;
+          int tiles = 0, n = 0;
+          for (size_t k = first; k < self->lin_jobs.size() && k < first + 80; ++k) {
+            const Lin& l = self->lin_jobs[k];
+            PackLinearJob& j = jobs.job[n++];
+            j.src = l.w->p; j.wp = mm->template at<T>(l.wf); j.wt = l.wd ? (void*)mm->template at<T>(l.wd) : nullptr;
+            j.N = l.N; j.K = l.K; j.tile0 = tiles; j.pad = 0;
+            tiles += cdiv(l.N, 32) * cdiv(l.K, 32);
+          }
+          jobs.n = n;
+          mm->launches++;
+          S4G_TRY(k_pack_linear_grouped<T>(jobs, tiles, st));
         }
-        jobs.n = n;
-        mm->launches++;
-        return k_pack_linear_grouped<T>(jobs, tiles, st);
+        return 0;
       });
     }
     if (!conv_jobs.empty()) {
@@ -861,6 +1136,10 @@ int build(S4GModel* m, std::unique_ptr<Builder<T>>& slot) {
   slot.reset(new Builder<T>(m));
   Builder<T>& b = *slot;
   b.bwd = &m->bwd_dec;
+  if (m->d.dense == S4G_DENSE_MAE) {
+    b.build_mae();
+    return b.finish();
+  }
   b.build_encoder(m->d.dense != S4G_DENSE_NONE);
   if (m->d.dense != S4G_DENSE_NONE) b.build_decoder();
   else b.build_cls_head();
@@ -953,7 +1232,8 @@ const char* s4g_model_bucket_params(S4GModel* m, int bucket, int n_buckets) {
     const std::string& name = kv.first;
     if (!kv.second.g) continue;
     int bkt;
-    if (name.compare(0, 8, "decoder.") == 0 || name.compare(0, 8, "lin_head") == 0 || name.compare(0, 5, "norm.") == 0) bkt = 0;
+    if (name.compare(0, 7, "decoder") == 0 || name.compare(0, 8, "lin_head") == 0 || name.compare(0, 5, "norm.") == 0 ||
+        name == "mask_token") bkt = 0;   // decoder. (DPT) | decoder_blocks. / decoder_embed / decoder_norm / decoder_pred (MAE)
     else if (name.compare(0, 7, "blocks.") == 0) bkt = bucket_of_block(atoi(name.c_str() + 7), n_buckets);
     else bkt = n_buckets - 1;
     if (bkt == bucket) { m->bucket_str += name; m->bucket_str += '\n'; }
@@ -971,6 +1251,16 @@ int s4g_model_forward(S4GModel* m, const float* images, float* out, int training
   m->launches = 0;
   for (auto& op : m->pack) S4G_TRY(op(st));
   for (auto& op : m->fwd) S4G_TRY(op(st));
+  if (m->d.dense == S4G_DENSE_MAE) {
+    const size_t n = (size_t)m->d.batch * 196;
+    if (m->mae_mask_out) S4G_CUDA(cudaMemcpyAsync(m->mae_mask_out, m->at<float>(m->mae_mask_off), sizeof(float) * n, cudaMemcpyDeviceToDevice, st));
+    if (m->mae_ids_restore_out) S4G_CUDA(cudaMemcpyAsync(m->mae_ids_restore_out, m->at<int>(m->mae_ids_restore_off), sizeof(int) * n, cudaMemcpyDeviceToDevice, st));
+  }
+  return 0;
+}
+int s4g_model_set_mae_io(S4GModel* m, const float* noise, float* mask_out, int* ids_restore_out) {
+  if (!m || m->d.dense != S4G_DENSE_MAE) { s4g_set_error("model_set_mae_io: not an S4G_DENSE_MAE model"); return S4G_ERR_STATE; }
+  m->mae_noise = noise; m->mae_mask_out = mask_out; m->mae_ids_restore_out = ids_restore_out;
   return 0;
 }
 

@@ -200,7 +200,7 @@ size_t ssi_scratch_floats(int B);
 
 // ---- optimizer: optim.cu
 int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps, float wd,
-            int step, float grad_scale, cudaStream_t st);
+            int step, float grad_scale, cudaStream_t st, const float* wd_slot = nullptr);
 
 // peer.cu: SyncBN statistic exchange over NVLink peer memory
 size_t k_peer_mailbox_bytes();

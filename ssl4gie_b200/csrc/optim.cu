@@ -5,9 +5,11 @@
 
 __global__ void __launch_bounds__(256) adamw_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ m,
                                                     float4* __restrict__ v, long long n4, float lr, float b1, float b2, float eps,
-                                                    float wd, float bc1, float bc2_sqrt, float gs) {
+                                                    float wd, float bc1, float bc2_sqrt, float gs,
+                                                    const float* __restrict__ wd_slot) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     float4 pv = p[i], gv = g[i], mv = m[i], vv = v[i];
+    if (wd_slot) wd = wd_slot[i >> 4];   // one weight decay per 64-float arena slot (parameter groups)
     float* pp = &pv.x; float* gp = &gv.x; float* mp = &mv.x; float* vp = &vv.x;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -22,12 +24,12 @@ __global__ void __launch_bounds__(256) adamw_kernel(float4* __restrict__ p, cons
   }
 }
 int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps, float wd,
-            int step, float grad_scale, cudaStream_t st) {
+            int step, float grad_scale, cudaStream_t st, const float* wd_slot) {
   if (n % 4) { s4g_set_error("adamw: arena length must be a multiple of 4"); return S4G_ERR_SHAPE; }
   const float bc1 = 1.f - powf(b1, (float)step), bc2 = 1.f - powf(b2, (float)step);
   adamw_kernel<<<148 * 8, 256, 0, st>>>(reinterpret_cast<float4*>(p), reinterpret_cast<const float4*>(g),
                                         reinterpret_cast<float4*>(m), reinterpret_cast<float4*>(v), n / 4, lr, b1, b2, eps, wd,
-                                        bc1, sqrtf(bc2), grad_scale);
+                                        bc1, sqrtf(bc2), grad_scale, wd_slot);
   S4G_KERNEL_CHECK();
   return 0;
 }

@@ -75,6 +75,8 @@ class Engine:
     def produces_grad(self, name, p, model):
         if not p.requires_grad:
             return False
+        if getattr(model, "dense", None) == "mae":
+            return True  # every trainable tensor of MaskedAutoencoderViT is used (the sin-cos tables are frozen)
         if getattr(model, "dense", None):
             if _unused_in_dense(name):
                 return False
@@ -245,6 +247,17 @@ class _Handle:
         _C.check(_C.lib().s4g_model_forward(self.ptr, _C.ptr(x), _C.ptr(out), int(training), seed, _C.ptr(mask), _C.stream_ptr()))
         return out
 
+    def forward_mae(self, x, noise):
+        """MaskedAutoencoderViT up to `pred`: returns (pred [B,196,768], mask [B,196], ids_restore [B,196] int32)."""
+        B = x.shape[0]
+        pred = torch.empty((B, 196, 768), dtype=torch.float32, device=x.device)
+        mask = torch.empty((B, 196), dtype=torch.float32, device=x.device)
+        ids = torch.empty((B, 196), dtype=torch.int32, device=x.device)
+        lib = _C.lib()
+        _C.check(lib.s4g_model_set_mae_io(self.ptr, _C.ptr(noise), _C.ptr(mask), _C.ptr(ids)))
+        _C.check(lib.s4g_model_forward(self.ptr, _C.ptr(x), _C.ptr(pred), 1, 0, None, _C.stream_ptr()))
+        return pred, mask, ids
+
     def backward(self, gout):
         ev = self.engine.bucket_events
         if ev is not None:
@@ -277,6 +290,46 @@ class _ModelFn(torch.autograd.Function):
             g = e.grad_views.get(n)
             grads.append(g.clone() if g is not None else None)
         return (None, None, None, None, None, *grads)
+
+
+class _MaeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, engine, handle, x, noise, *params):
+        ctx.engine, ctx.handle = engine, handle
+        ctx.n = len(params)
+        pred, mask, ids = handle.forward_mae(x, noise)
+        ctx.mark_non_differentiable(mask, ids)
+        return pred, mask, ids
+
+    @staticmethod
+    def backward(ctx, gpred, _gmask, _gids):
+        e = ctx.engine
+        ctx.handle.backward(gpred.contiguous().float())
+        if e.direct_grads:
+            return (None,) * (4 + ctx.n)
+        grads = []
+        for n, p in e.model_ref().named_parameters():
+            g = e.grad_views.get(n)
+            grads.append(g.clone() if g is not None else None)
+        return (None, None, None, None, *grads)
+
+
+def run_mae(model, x, noise):
+    """MaskedAutoencoderViT.forward_encoder + forward_decoder (Models/mae/models_mae.py:150-196) with the masking noise given:
+    (pred [B,196,768] fp32, mask [B,196], ids_restore [B,196] int32)."""
+    _C.require_cuda(x, "input")
+    if x.dim() != 4 or tuple(x.shape[1:]) != (3, 224, 224):
+        raise AssertionError(f"Input image size ({tuple(x.shape[2:])}) doesn't match model (224, 224).")
+    if tuple(noise.shape) != (x.shape[0], 196):
+        raise ValueError("noise must be [B, 196]")
+    engine = Engine.of(model)
+    x = x.detach().float().contiguous()
+    noise = noise.detach().float().contiguous()
+    h = engine.handle(x.shape[0])
+    if torch.is_grad_enabled():
+        params = [p for _, p in model.named_parameters()]
+        return _MaeFn.apply(engine, h, x, noise, *params)
+    return h.forward_mae(x, noise)
 
 
 def run_model(model, x):

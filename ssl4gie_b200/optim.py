@@ -12,7 +12,7 @@ class FusedAdamW(torch.optim.Optimizer):
     for ``grad is None``.
     """
 
-    def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, grad_scale=1.0):
+    def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, grad_scale=1.0, param_groups=None):
         from .engine import Engine
         core = model.module if hasattr(model, "module") else model
         self.engine = Engine.of(core)
@@ -23,18 +23,53 @@ class FusedAdamW(torch.optim.Optimizer):
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         # every parameter, in model.parameters() order, as the reference's torch.optim.AdamW(model.parameters()) holds
         # them: the indices in state_dict() are then the reference checkpoint's indices
-        super().__init__(list(core.parameters()), defaults)
+        # param_groups: torch-style groups of the model's parameters that differ in weight_decay only (timm add_weight_decay,
+        # Models/mae/main_pretrain.py:179-180); lr / betas / eps are shared by all groups
+        super().__init__(list(core.parameters()) if param_groups is None else param_groups, defaults)
         n = self.engine.n_active
+        self.wd_slots = None
+        if param_groups is not None:
+            self._build_wd_slots()
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=self.engine.flat_params.device)
         self.exp_avg_sq = torch.zeros_like(self.exp_avg)
         self.step_count = 0
         self.grad_scale = grad_scale
+
+    def _build_wd_slots(self):
+        """One weight decay per 64-float arena slot (every parameter starts on a slot boundary)."""
+        e = self.engine
+        base = e.flat_grads.data_ptr()
+        by_id = {id(p): g for n, p in e.model_ref().named_parameters() if (g := e.grad_views.get(n)) is not None}
+        wd = torch.zeros(e.n_active // 64, dtype=torch.float32)
+        seen = 0
+        for group in self.param_groups:
+            for p in group["params"]:
+                g = by_id.get(id(p))
+                if g is None:
+                    continue
+                off = (g.data_ptr() - base) // 4
+                wd[off // 64:(off + p.numel() + 63) // 64] = group["weight_decay"]
+                seen += 1
+        if seen != len(by_id):
+            raise ValueError("param_groups must cover every trainable parameter of the model (got %d of %d)" % (seen, len(by_id)))
+        self.wd_slots = wd.to(e.flat_params.device)
+        self._wd_key = tuple(g["weight_decay"] for g in self.param_groups)
 
     @torch.no_grad()
     def step(self, closure=None):
         g = self.param_groups[0]
         self.step_count += 1
         e = self.engine
+        if self.wd_slots is not None:
+            for o in self.param_groups[1:]:
+                if (o["lr"], tuple(o["betas"]), o["eps"]) != (g["lr"], tuple(g["betas"]), g["eps"]):
+                    raise ValueError("FusedAdamW: parameter groups may differ in weight_decay only")
+            if tuple(o["weight_decay"] for o in self.param_groups) != self._wd_key:
+                self._build_wd_slots()
+            _C.check(_C.lib().s4g_adamw_step_groups(_C.ptr(e.flat_params), _C.ptr(e.flat_grads), _C.ptr(self.exp_avg),
+                                                    _C.ptr(self.exp_avg_sq), e.n_active, g["lr"], g["betas"][0], g["betas"][1],
+                                                    g["eps"], _C.ptr(self.wd_slots), self.step_count, self.grad_scale, _C.stream_ptr()))
+            return
         _C.check(_C.lib().s4g_adamw_step(_C.ptr(e.flat_params), _C.ptr(e.flat_grads), _C.ptr(self.exp_avg), _C.ptr(self.exp_avg_sq),
                                          e.n_active, g["lr"], g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"],
                                          self.step_count, self.grad_scale, _C.stream_ptr()))

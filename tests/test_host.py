@@ -203,3 +203,37 @@ def test_bucketed_allreduce_two_ranks_gloo(tmp_path):
     for n, (off, numel) in offsets.items():
         if off < n_active:
             assert torch.allclose(got[off:off + numel], want[off:off + numel]), n
+
+
+def test_mae_module_manifest_groups_and_schedule(golden_dir):
+    """MaskedAutoencoderViT (ssl4gie_b200/mae.py) has the reference module's state_dict (fixture written from the unmodified
+    Models/mae/models_mae.py), the same frozen tensors, timm's add_weight_decay grouping and lr_sched's schedule."""
+    import json
+    import os
+
+    import ssl4gie_b200
+    from oracle import ref_port
+    m = ssl4gie_b200.mae_vit_base_patch16(norm_pix_loss=True)
+    with open(os.path.join(golden_dir, "manifest_mae.json")) as f:
+        man = json.load(f)
+    sd = m.state_dict()
+    assert sorted(sd) == sorted(man)
+    for k, (shape, dtype) in man.items():
+        assert list(sd[k].shape) == shape and str(sd[k].dtype) == dtype, k
+    assert sorted(n for n, p in m.named_parameters() if not p.requires_grad) == sorted(ref_port.MAE_FROZEN)
+    assert torch.equal(sd["pos_embed"], ref_port.sincos_2d(768)) and torch.equal(sd["decoder_pos_embed"], ref_port.sincos_2d(512))
+    groups = ssl4gie_b200.add_weight_decay(m, 0.05)
+    names = {id(p): n for n, p in m.named_parameters()}
+    ref_groups = ref_port.mae_param_groups({k: v for k, v in sd.items()}, 0.05)
+    for g, r in zip(groups, ref_groups):
+        assert g["weight_decay"] == r["weight_decay"] and sorted(names[id(p)] for p in g["params"]) == sorted(r["names"])
+
+    class _Opt:
+        param_groups = [{"lr": 0.0}, {"lr": 0.0, "lr_scale": 0.5}]
+
+    for it in (0, 7, 400, 4000, 50000):
+        lr = ssl4gie_b200.adjust_learning_rate(_Opt, it / 100, 1.5e-4, warmup_epochs=40, epochs=800)
+        assert abs(lr - ref_port.mae_lr(it, 100, 1.5e-4)) < 1e-15
+        assert _Opt.param_groups[0]["lr"] == lr and _Opt.param_groups[1]["lr"] == lr * 0.5
+    with pytest.raises(NotImplementedError):
+        ssl4gie_b200.MaskedAutoencoderViT()  # mae_vit_large defaults: outside the B200 schedule
