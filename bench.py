@@ -221,7 +221,8 @@ def run_ours(args):
         loss_fn = SoftDiceLoss() if task == "seg" else ScaleAndShiftInvariantLoss(alpha=0.1)
     if task == "mae":  # main_pretrain.py:179-180: timm add_weight_decay groups, AdamW betas (0.9, 0.95); blr 1e-3 * 64 * world / 256
         import ssl4gie_b200
-        opt = FusedAdamW(model, lr=1e-3 * B * world / 256, betas=(0.9, 0.95), grad_scale=1.0 / world,
+        mae_lr = 1e-3 * B * world / 256
+        opt = FusedAdamW(model, lr=mae_lr, betas=(0.9, 0.95), grad_scale=1.0 / world,
                          param_groups=ssl4gie_b200.add_weight_decay(model, 0.05))
     else:
         opt = FusedAdamW(model, lr=1e-4, grad_scale=1.0 / world)
@@ -239,6 +240,8 @@ def run_ours(args):
         t_host = time.perf_counter()
         h = engine.handle(B)
         if task == "mae":
+            # per-iteration LR schedule of the reference step (engine_pretrain.py:42-43; 40 warm-up epochs of 1000 iterations)
+            ssl4gie_b200.adjust_learning_rate(opt, len(launch_host) / 1000.0, mae_lr)
             loss, _, _ = model(x, mask_ratio=0.75, noise=t)
         else:
             out = model(x)

@@ -1,0 +1,152 @@
+"""ORACLE — test infrastructure, NOT product code.
+
+numpy restatement of the reference's training-time input pipeline:
+  Binary_segmentation/Data/dataset.py:34-64   PIL resize to 224, transforms, joint flips, joint affine (fill -1 / 0)
+  Binary_segmentation/Data/dataloaders.py:62-76 ColorJitter(0.4, 0.5, 0.25, 0.01), GaussianBlur((25, 25), (0.001, 2.0)),
+                                               ToTensor, Normalize(ImageNet)
+The arithmetic lives in third-party dependencies that are not in /root/reference: Pillow (requirements.txt pins 9.x; the
+8-bit resampler, ImageEnhance and the RGB<->HSV converters have not changed since) and torchvision 0.x
+(transforms.functional: adjust_hue, gaussian_blur, affine).  Both are installed in this image, so tests/test_aug_oracle.py
+pins every function below against the real libraries (bit-exact for the uint8 paths, exhaustively over all 2^24 colours for
+the HSV round trip); nothing here is imported by the product package.
+"""
+import math
+
+import numpy as np
+
+# ----------------------------------------------------------------------------------------------- PIL Image.resize
+PRECISION_BITS = 32 - 8 - 2  # Pillow src/libImaging/Resample.c
+
+
+def _bicubic(x, a=-0.5):
+    x = abs(x)
+    if x < 1.0:
+        return ((a + 2.0) * x - (a + 3.0)) * x * x + 1
+    if x < 2.0:
+        return (((x - 5) * x + 8) * x - 4) * a
+    return 0.0
+
+
+def resample_coeffs(in_size, out_size, support=2.0, filt=_bicubic):
+    """precompute_coeffs + normalize_coeffs_8bpc: per output index (xmin, integer weights)."""
+    scale = filterscale = in_size / out_size
+    if filterscale < 1.0:
+        filterscale = 1.0
+    support = support * filterscale
+    ss = 1.0 / filterscale
+    out = []
+    for xx in range(out_size):
+        center = (xx + 0.5) * scale
+        xmin = max(int(center - support + 0.5), 0)
+        xmax = min(int(center + support + 0.5), in_size) - xmin
+        w = np.array([filt((x + xmin - center + 0.5) * ss) for x in range(xmax)], dtype=np.float64)
+        tot = w.sum()
+        if tot != 0.0:
+            w = w / tot
+        k = np.where(w < 0, (-0.5 + w * (1 << PRECISION_BITS)).astype(np.int64), (0.5 + w * (1 << PRECISION_BITS)).astype(np.int64))
+        # C casts truncate toward zero: astype(int64) does the same
+        out.append((xmin, k))
+    return out
+
+
+def _resample_axis0(img, out_size):
+    """img [N, ...] uint8 -> [out_size, ...] uint8 along axis 0 with the 8-bit fixed-point accumulator."""
+    coeffs = resample_coeffs(img.shape[0], out_size)
+    res = np.empty((out_size,) + img.shape[1:], dtype=np.uint8)
+    src = img.astype(np.int64)
+    for i, (xmin, k) in enumerate(coeffs):
+        acc = (1 << (PRECISION_BITS - 1)) + np.tensordot(k, src[xmin:xmin + len(k)], axes=(0, 0))
+        res[i] = np.clip(acc >> PRECISION_BITS, 0, 255).astype(np.uint8)
+    return res
+
+
+def pil_resize_bicubic(img, out_w=224, out_h=224):
+    """Image.resize((out_w, out_h)) of an 8-bit image [H, W] or [H, W, C] (default resample BICUBIC, dataset.py:38-41):
+    horizontal pass, then vertical pass, each rounding to uint8."""
+    h = np.swapaxes(_resample_axis0(np.swapaxes(img, 0, 1), out_w), 0, 1) if img.shape[1] != out_w else img
+    return _resample_axis0(h, out_h) if img.shape[0] != out_h else h
+
+
+# ----------------------------------------------------------------------------------------------- ColorJitter on PIL images
+def to_l(rgb):
+    """Image.convert("L"): ITU-R 601-2 luma in 16.16 fixed point."""
+    r, g, b = (rgb[..., i].astype(np.int64) for i in range(3))
+    return ((r * 19595 + g * 38470 + b * 7471 + 0x8000) >> 16).astype(np.uint8)
+
+
+def _blend(deg, img, f):
+    """Image.blend(degenerate, image, factor) for 8-bit images: float32 interpolation, truncation (factor in [0, 1]) or
+    clipping + truncation (extrapolation)."""
+    a = deg.astype(np.float32)
+    t = a + np.float32(f) * (img.astype(np.float32) - a)
+    if 0.0 <= f <= 1.0:
+        return t.astype(np.uint8)
+    return np.where(t <= 0, 0, np.where(t >= 255, 255, t)).astype(np.uint8)
+
+
+def adjust_brightness(rgb, f):
+    """F.adjust_brightness on a PIL image = ImageEnhance.Brightness: blend with black."""
+    return _blend(np.zeros_like(rgb), rgb, f)
+
+
+def adjust_contrast(rgb, f):
+    """ImageEnhance.Contrast: blend with the constant image of the rounded mean luma."""
+    mean = int(to_l(rgb).astype(np.float64).mean() + 0.5)
+    return _blend(np.full_like(rgb, mean), rgb, f)
+
+
+def adjust_saturation(rgb, f):
+    """ImageEnhance.Color: blend with the grey version of the image."""
+    return _blend(np.repeat(to_l(rgb)[..., None], 3, axis=-1), rgb, f)
+
+
+def rgb_to_hsv(rgb):
+    """Pillow Convert.c rgb2hsv (8-bit H, S, V).  The C code mixes float variables with double literals; the promotions
+    below are the ones that reproduce it for all 2^24 colours (tests/test_aug_oracle.py)."""
+    f32, f64 = np.float32, np.float64
+    r, g, b = (rgb[..., i].astype(np.int64) for i in range(3))
+    maxc = np.maximum(r, np.maximum(g, b))
+    minc = np.minimum(r, np.minimum(g, b))
+    cr = (maxc - minc).astype(f32)
+    safe = np.where(cr == 0, f32(1), cr).astype(f32)
+    s = cr / np.where(maxc == 0, 1, maxc).astype(f32)
+    rc, gc, bc = ((maxc - c).astype(f32) / safe for c in (r, g, b))
+    h = np.where(r == maxc, (bc - gc).astype(f32),                                      # float - float
+                 np.where(g == maxc, (2.0 + rc.astype(f64) - bc.astype(f64)).astype(f32),   # 2.0 + rc - bc in double -> float
+                          (4.0 + gc.astype(f64) - rc.astype(f64)).astype(f32)))
+    h = np.fmod(h.astype(f64) / 6.0 + 1.0, 1.0).astype(f32)                            # double, stored to the float h
+    uh = np.clip((h.astype(f64) * 255.0).astype(np.int64), 0, 255)
+    us = np.clip((s.astype(f64) * 255.0).astype(np.int64), 0, 255)
+    grey = maxc == minc
+    return np.stack([np.where(grey, 0, uh), np.where(grey, 0, us), maxc], axis=-1).astype(np.uint8)
+
+
+def hsv_to_rgb(hsv):
+    """Pillow Convert.c hsv2rgb: i / f from h * 6.0 / 255.0 in double (f, fs stored as float), C round() (half away from 0)."""
+    f32, f64 = np.float32, np.float64
+    h, s, v = (hsv[..., i].astype(np.int64) for i in range(3))
+    hd = h.astype(f64) * 6.0 / 255.0
+    i = np.floor(hd).astype(np.int64)
+    f = (hd - i.astype(f64)).astype(f32)
+    fs = (s.astype(f64) / 255.0).astype(f32)
+    vf = v.astype(f64)
+
+    def rnd(x):  # x >= 0 here
+        return np.clip(np.floor(x + 0.5).astype(np.int64), 0, 255)
+
+    p = rnd(vf * (1.0 - fs.astype(f64)))
+    q = rnd(vf * (1.0 - (fs * f).astype(f64)))                     # fs * f is a float product
+    t = rnd(vf * (1.0 - fs.astype(f64) * (1.0 - f.astype(f64))))
+    i = i % 6
+    r = np.choose(i, [v, q, p, p, t, v])
+    g = np.choose(i, [t, v, v, q, p, p])
+    b = np.choose(i, [p, p, t, v, v, q])
+    grey = s == 0
+    return np.stack([np.where(grey, v, r), np.where(grey, v, g), np.where(grey, v, b)], axis=-1).astype(np.uint8)
+
+
+def adjust_hue(rgb, f):
+    """torchvision F.adjust_hue on a PIL image (_functional_pil.adjust_hue): H += uint8(f * 255) with wrap-around."""
+    hsv = rgb_to_hsv(rgb)
+    hsv[..., 0] = (hsv[..., 0].astype(np.int64) + int(np.uint8(np.int64(f * 255)))) & 255
+    return hsv_to_rgb(hsv)

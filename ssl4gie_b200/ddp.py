@@ -16,28 +16,35 @@ from .engine import Engine
 
 
 def bucket_slices(names_by_bucket, offsets):
-    """Contiguous [lo, hi) float ranges of the flat gradient arena covered by each bucket.
-    names_by_bucket: list of parameter-name lists; offsets: name -> (offset, numel) in floats."""
-    slices = []
-    for names in names_by_bucket:
-        if not names:
-            slices.append(None)
-            continue
-        lo = min(offsets[n][0] for n in names)
-        hi = max(offsets[n][0] + offsets[n][1] for n in names)
-        slices.append((lo, hi))
-    return slices
+    """[lo, hi) float ranges of the flat gradient arena that make up each bucket: one list of ranges per bucket, a range
+    being a run of parameters of that bucket that are adjacent in the arena (alignment padding between them included).
+    A bucket is usually ONE range; it is several when the arena order (nn.Module.named_parameters: a module's own
+    parameters before its children's, e.g. cls_token / mask_token of MaskedAutoencoderViT) interleaves buckets.  Every
+    parameter lies in exactly one range.  names_by_bucket: list of parameter-name lists; offsets: name -> (offset, numel)."""
+    owner = {n: b for b, names in enumerate(names_by_bucket) for n in names}
+    runs = [[] for _ in names_by_bucket]
+    prev = None
+    for n in sorted(owner, key=lambda k: offsets[k][0]):
+        off, numel = offsets[n]
+        b = owner[n]
+        if prev == b:
+            runs[b][-1][1] = off + numel
+        else:
+            runs[b].append([off, off + numel])
+        prev = b
+    return [[(lo, hi) for lo, hi in r] for r in runs]
 
 
 def allreduce_buckets(flat, slices, group=None, events=None, comm_stream=None):
-    """Sum-all-reduce every bucket slice of `flat` (in place).  On CUDA each bucket waits for its event on the
+    """Sum-all-reduce every range of every bucket of `flat` (in place).  On CUDA each bucket waits for its event on the
     communication stream; on CPU (gloo, used by the tests) the calls are issued in order."""
-    for i, sl in enumerate(slices):
-        if sl is None:
+    for i, ranges in enumerate(slices):
+        if not ranges:
             continue
         if events is not None and comm_stream is not None:
             comm_stream.wait_event(events[i])
-        dist.all_reduce(flat[sl[0]:sl[1]], group=group)
+        for lo, hi in ranges:
+            dist.all_reduce(flat[lo:hi], group=group)
 
 
 class GradientAllReduce:

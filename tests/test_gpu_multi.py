@@ -30,3 +30,13 @@ def test_train_epoch_two_ranks():
            "--master-port", "29542", os.path.join(ROOT, "scripts", "check_train_n2.py")]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "CHECK_TRAIN_N2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_mae_pretrain_two_ranks():
+    """MAE pretraining step under data parallelism (scripts/check_mae_n2.py): bucketed all-reduce of the gradient arena,
+    replicas bit-identical after 5 steps, and equal to one process stepping on the concatenated batch."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29543", os.path.join(ROOT, "scripts", "check_mae_n2.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "CHECK_MAE_N2 OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

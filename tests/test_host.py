@@ -165,11 +165,11 @@ def test_arena_layout_and_bucket_plan():
     assert all(n.startswith("decoder.") for n in plan[0])
     assert "blocks.11.mlp.fc2.weight" in plan[1] and "blocks.0.attn.qkv.weight" in plan[-1] and "patch_embed.proj.weight" in plan[-1]
     sl = bucket_slices(plan, offsets)
-    assert all(s is not None and 0 <= s[0] < s[1] <= n_active for s in sl)
+    assert all(len(r) == 1 and 0 <= r[0][0] < r[0][1] <= n_active for r in sl)   # one contiguous range per bucket
     # one bucket = the whole gradient arena (its event is recorded at the END of backward, csrc/engine.cu)
     plan1, _, _ = _bucket_plan(m, 1)
     assert sorted(plan1[0]) == sorted(with_grad)
-    assert bucket_slices(plan1, offsets)[0][0] == 0
+    assert bucket_slices(plan1, offsets)[0][0][0] == 0
     # two buckets: decoder | whole encoder
     plan2, _, _ = _bucket_plan(m, 2)
     assert all(n.startswith("decoder.") for n in plan2[0]) and sorted(plan2[0] + plan2[1]) == sorted(with_grad)
@@ -188,12 +188,24 @@ def _gloo_worker(rank, world, port, plan, offsets, n_active, out):
     dist.destroy_process_group()
 
 
-def test_bucketed_allreduce_two_ranks_gloo(tmp_path):
-    """world_size 2 on CPU: the union of the bucket slices covers every gradient exactly once, so the bucketed exchange
-    equals one flat all-reduce."""
+@pytest.mark.parametrize("which", ["depth", "mae"])
+def test_bucketed_allreduce_two_ranks_gloo(tmp_path, which):
+    """world_size 2 on CPU: the bucket ranges cover every gradient exactly once, so the bucketed exchange equals one flat
+    all-reduce -- also for MaskedAutoencoderViT, whose root-level parameters (cls_token, mask_token) sit at the front of the
+    arena although they belong to the last / first bucket."""
+    import ssl4gie_b200
     from ssl4gie_b200 import utils
-    m = utils.get_ImageNet_or_random_ViT(False, None, False, "depth", False, False)
+    from ssl4gie_b200.ddp import bucket_slices
+    if which == "mae":
+        m = ssl4gie_b200.mae_vit_base_patch16(norm_pix_loss=True)
+    else:
+        m = utils.get_ImageNet_or_random_ViT(False, None, False, "depth", False, False)
     plan, offsets, n_active = _bucket_plan(m, 4)
+    ranges = sorted(r for b in bucket_slices(plan, offsets) for r in b)
+    assert all(a[1] <= b[0] for a, b in zip(ranges, ranges[1:])), "bucket ranges overlap"
+    if which == "mae":
+        assert "mask_token" in plan[0] and "decoder_pred.weight" in plan[0] and "norm.weight" in plan[0]
+        assert "cls_token" in plan[-1] and "patch_embed.proj.weight" in plan[-1] and "pos_embed" not in sum(plan, [])
     out = str(tmp_path / "r0.pt")
     port = 29500 + os.getpid() % 2000
     mp.spawn(_gloo_worker, args=(2, port, plan, offsets, n_active, out), nprocs=2, join=True)
