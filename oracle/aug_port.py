@@ -150,3 +150,97 @@ def adjust_hue(rgb, f):
     hsv = rgb_to_hsv(rgb)
     hsv[..., 0] = (hsv[..., 0].astype(np.int64) + int(np.uint8(np.int64(f * 255)))) & 255
     return hsv_to_rgb(hsv)
+
+
+COLOR_OPS = (adjust_brightness, adjust_contrast, adjust_saturation, adjust_hue)
+
+
+def color_jitter(rgb, order, factors):
+    """transforms.ColorJitter.forward (dataloaders.py:64-66): the four adjustments in the drawn order `order` (a permutation
+    of 0..3 = brightness, contrast, saturation, hue) with the drawn factors[4]; every step re-quantises to uint8."""
+    for k in order:
+        rgb = COLOR_OPS[k](rgb, factors[k])
+    return rgb
+
+
+# ----------------------------------------------------------------------------------------------- GaussianBlur((25, 25), sigma)
+def gaussian_kernel1d(ksize, sigma):
+    """torchvision _get_gaussian_kernel1d in float32."""
+    half = (ksize - 1) * 0.5
+    x = np.linspace(-half, half, ksize, dtype=np.float32)
+    pdf = np.exp(np.float32(-0.5) * (x / np.float32(sigma)) ** 2).astype(np.float32)
+    return (pdf / pdf.sum(dtype=np.float32)).astype(np.float32)
+
+
+def gaussian_blur(rgb, sigma, ksize=25):
+    """F.gaussian_blur on an 8-bit image: float conv with the outer-product kernel on reflect-padded input, round half to
+    even, back to uint8.  Accumulated here in float64 (torchvision: float32 conv2d, order unspecified): results agree except
+    where the exact value sits within float32 noise of a .5 boundary (a handful of pixels per image, +-1)."""
+    k = gaussian_kernel1d(ksize, sigma).astype(np.float64)
+    pad = ksize // 2
+    x = np.pad(rgb.astype(np.float64), ((pad, pad), (pad, pad), (0, 0)), mode="reflect")
+    h = sum(k[i] * x[:, i:i + rgb.shape[1]] for i in range(ksize))
+    v = sum(k[i] * h[i:i + rgb.shape[0]] for i in range(ksize))
+    return np.clip(np.rint(v), 0, 255).astype(np.uint8)
+
+
+IMAGENET_MEAN = np.array([0.485, 0.456, 0.406], dtype=np.float32)
+IMAGENET_STD = np.array([0.229, 0.224, 0.225], dtype=np.float32)
+
+
+def to_tensor_normalize(rgb):
+    """ToTensor + Normalize (dataloaders.py:67-68): [H, W, 3] uint8 -> [3, H, W] float32."""
+    x = rgb.astype(np.float32) / np.float32(255)
+    return np.transpose((x - IMAGENET_MEAN) / IMAGENET_STD, (2, 0, 1))
+
+
+def mask_to_tensor(rgb_or_l):
+    """ToTensor + Grayscale (dataloaders.py:72-74): 3-channel masks through torchvision's rgb_to_grayscale
+    (0.2989 r + 0.587 g + 0.114 b in float32), single-channel masks unchanged."""
+    x = rgb_or_l.astype(np.float32) / np.float32(255)
+    if x.ndim == 2:
+        return x[None]
+    return (np.float32(0.2989) * x[..., 0] + np.float32(0.587) * x[..., 1] + np.float32(0.114) * x[..., 2])[None]
+
+
+# ----------------------------------------------------------------------------------------------- flips + affine (dataset.py:46-63)
+def inverse_affine_matrix(angle, translate, scale, shear):
+    """torchvision _get_inverse_affine_matrix with center (0, 0) (F.affine on tensors) and shear = (shear, 0)."""
+    rot, sx, sy = math.radians(angle), math.radians(shear), 0.0
+    tx, ty = translate
+    a = math.cos(rot - sy) / math.cos(sy)
+    b = -math.cos(rot - sy) * math.tan(sx) / math.cos(sy) - math.sin(rot)
+    c = math.sin(rot - sy) / math.cos(sy)
+    d = -math.sin(rot - sy) * math.tan(sx) / math.cos(sy) + math.cos(rot)
+    m = [x / scale for x in (d, -b, 0.0, -c, a, 0.0)]
+    m[2] += m[0] * (-tx) + m[1] * (-ty)
+    m[5] += m[3] * (-tx) + m[4] * (-ty)
+    return m
+
+
+def affine_source_index(matrix, size=224):
+    """Source pixel (iy, ix) of every output pixel for F.affine(..., interpolation=NEAREST) on a size x size tensor:
+    _gen_affine_grid + grid_sample(nearest, zeros, align_corners=False) in float32; (-1, -1) where the source is outside."""
+    f32 = np.float32
+    theta = np.array(matrix, dtype=f32).reshape(2, 3)
+    r = (theta.T / np.array([0.5 * size, 0.5 * size], dtype=f32)).astype(f32)   # [3, 2]
+    xs = np.linspace(-size * 0.5 + 0.5, size * 0.5 + 0.5 - 1, size, dtype=f32)
+    gx = (xs[None, :] * r[0, 0] + xs[:, None] * r[1, 0] + r[2, 0]).astype(f32)
+    gy = (xs[None, :] * r[0, 1] + xs[:, None] * r[1, 1] + r[2, 1]).astype(f32)
+    ix = np.rint((((gx + f32(1)) * f32(size) - f32(1)) / f32(2)).astype(f32)).astype(np.int64)
+    iy = np.rint((((gy + f32(1)) * f32(size) - f32(1)) / f32(2)).astype(f32)).astype(np.int64)
+    ok = (ix >= 0) & (ix < size) & (iy >= 0) & (iy < size)
+    return np.where(ok, iy, -1), np.where(ok, ix, -1)
+
+
+def geometric(x, hflip, vflip, matrix, fill):
+    """dataset.py:46-63 on a [C, H, W] float tensor: TF.hflip, TF.vflip, then TF.affine(nearest, fill)."""
+    if hflip:
+        x = x[:, :, ::-1]
+    if vflip:
+        x = x[:, ::-1, :]
+    if matrix is None:
+        return np.ascontiguousarray(x)
+    iy, ix = affine_source_index(matrix, x.shape[-1])
+    out = x[:, np.clip(iy, 0, None), np.clip(ix, 0, None)]
+    return np.where((iy < 0)[None], np.float32(fill), out).astype(np.float32)
