@@ -227,6 +227,9 @@ def run_ours(args):
     else:
         opt = FusedAdamW(model, lr=1e-4, grad_scale=1.0 / world)
     ddp = GradientAllReduce(model)
+    # N > 1: AdamW of each gradient bucket runs on the communication stream right after that bucket's all-reduce (same
+    # arithmetic, hidden under the rest of backward); S4G_FUSED_STEP=0 keeps one optimizer kernel after the exchange
+    ddp.attach(opt, fused_step=world > 1 and os.environ.get("S4G_FUSED_STEP", "1") != "0")
     ddp.prepare(B)
     engine = Engine.of(model)
     x_h, t_h = synth(task, B, rank)

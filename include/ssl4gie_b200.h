@@ -187,6 +187,30 @@ int s4g_ce_fwd(const float* logits, const long long* labels, const float* class_
                int B, int num_classes, void* stream);
 int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits, int B, int num_classes, void* stream);
 
+/* ---- GPU-side input pipeline: the per-sample Pillow / torchvision work of the reference's DataLoader workers
+ * (Binary_segmentation/Data/dataset.py:34-64, Data/dataloaders.py:62-76) on a batch of decoded 8-bit images.  Every entry
+ * point works on B images of 224 x 224 except s4g_aug_resize, which produces them.
+ * s4g_aug_resize: Image.resize((224, 224)) (Pillow 8-bit bicubic, bit-exact).  src = packed images [h][w][C]; desc [B][4] =
+ *   {byte offset into src, height, width, channels (== C, 1 or 3)} given both as a device and a host array; out [B,224,224,C]. */
+size_t s4g_aug_resize_scratch_bytes(const long long* desc_host, int B, int C);
+int s4g_aug_resize(const unsigned char* src, const long long* desc_dev, const long long* desc_host, int B, int C,
+                   void* scratch, size_t scratch_bytes, unsigned char* out, void* stream);
+/* transforms.ColorJitter on 8-bit RGB [B,224,224,3] in place (ImageEnhance blends, Pillow RGB<->HSV; bit-exact).
+ * params (device) [B] of {int order[4] (permutation of 0 brightness, 1 contrast, 2 saturation, 3 hue); int hue_shift
+ * (= uint8(hue_factor * 255)); float factor[3] (brightness, contrast, saturation)}. */
+int s4g_aug_color_jitter(unsigned char* img, const void* params, int B, void* stream);
+/* transforms.GaussianBlur((25, 25), sigma[b]) + ToTensor + Normalize(mean, std): [B,224,224,3] u8 -> [B,3,224,224] f32.
+ * sigma (device, [B]) may be NULL or <= 0 per image: no blur (the evaluation transform, dataloaders.py:104-111). */
+int s4g_aug_blur_normalize(const unsigned char* img, const float* sigma, float* out, const float* mean3_host,
+                           const float* std3_host, int B, void* stream);
+/* ToTensor + Grayscale of the masks (dataloaders.py:72-74): [B,224,224,C] u8 -> [B,1,224,224] f32. */
+int s4g_aug_mask_to_tensor(const unsigned char* img, float* out, int B, int C, void* stream);
+/* TF.hflip, TF.vflip, TF.affine(interpolation=NEAREST, fill) applied jointly to x [B,3,224,224] and y [B,1,224,224] (y, yo
+ * may be NULL) (dataset.py:46-63).  params (device) [B] of {int hflip, vflip, affine; float m[6]} with m = torchvision's
+ * _get_inverse_affine_matrix((0, 0), angle, translate, scale, (shear, 0)). */
+int s4g_aug_geometric(const float* x, const float* y, float* xo, float* yo, const void* params, float fill_x, float fill_y,
+                      int B, void* stream);
+
 /* torch.optim.AdamW step over a flat fp32 arena (train_segmentation.py:204). grad_scale multiplies g first
  * (1/world_size after a sum-all-reduce). step counts from 1. */
 int s4g_adamw_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,

@@ -40,7 +40,9 @@ def resample_coeffs(in_size, out_size, support=2.0, filt=_bicubic):
         xmin = max(int(center - support + 0.5), 0)
         xmax = min(int(center + support + 0.5), in_size) - xmin
         w = np.array([filt((x + xmin - center + 0.5) * ss) for x in range(xmax)], dtype=np.float64)
-        tot = w.sum()
+        tot = 0.0
+        for v in w:      # sequential, as the C loop (numpy's sum is pairwise for longer runs)
+            tot += float(v)
         if tot != 0.0:
             w = w / tot
         k = np.where(w < 0, (-0.5 + w * (1 << PRECISION_BITS)).astype(np.int64), (0.5 + w * (1 << PRECISION_BITS)).astype(np.int64))

@@ -69,6 +69,25 @@ def main():
     dist.all_gather(other, flat)
     assert all(torch.equal(o, other[0]) for o in other), "parameters diverged between ranks"
     assert all(torch.isfinite(torch.tensor(losses))), losses
+    # 4. the bucket-wise optimizer step (attach(optimizer, fused_step=True): AdamW of each bucket right after its all-reduce,
+    #    on the communication stream) is the same arithmetic: bit-identical parameters after the same five steps
+    m2 = build()
+    o2 = FusedAdamW(m2, lr=1e-3, betas=(0.9, 0.95), param_groups=ssl4gie_b200.add_weight_decay(m2, 0.05))
+    d2 = GradientAllReduce(m2)
+    d2.attach(o2, fused_step=True)
+    d2.prepare(B)
+    for step in range(5):
+        x, noise = data(step)
+        xs, ns = x[rank * B:(rank + 1) * B].cuda(), noise[rank * B:(rank + 1) * B].cuda()
+        ssl4gie_b200.adjust_learning_rate(o2, step / 10, 1e-3, warmup_epochs=1, epochs=4)
+        loss, _, _ = m2(xs, noise=ns)
+        loss.backward()
+        d2.reduce()
+        o2.step()
+    torch.cuda.synchronize()
+    assert o2.step_count == 5 and torch.equal(Engine.of(m2).flat_params, flat), "fused bucket-wise step differs"
+    if rank == 0:
+        print("bucket-wise optimizer step on the communication stream: parameters bit-identical to the plain step", flush=True)
     if rank == 0:
         print("5 steps on 2 ranks: mean losses", ["%.5f" % v for v in losses], "parameters bit-identical across ranks", flush=True)
         # the same five steps in one process over the concatenated batch: loss = mean over 2B images' removed patches; every image

@@ -66,6 +66,12 @@ SIGNATURES = {
     "s4g_ce_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "s4g_ce_bwd": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "s4g_adamw_step": (_i, [_vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _f, _i, _f, _vp]),
+    "s4g_aug_resize_scratch_bytes": (_sz, [_vp, _i, _i]),
+    "s4g_aug_resize": (_i, [_vp, _vp, _vp, _i, _i, _vp, _sz, _vp, _vp]),
+    "s4g_aug_color_jitter": (_i, [_vp, _vp, _i, _vp]),
+    "s4g_aug_blur_normalize": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "s4g_aug_mask_to_tensor": (_i, [_vp, _vp, _i, _i, _vp]),
+    "s4g_aug_geometric": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp]),
     "s4g_adamw_step_groups": (_i, [_vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _vp, _i, _f, _vp]),
     "s4g_mae_loss_scratch_bytes": (_sz, [_i]),
     "s4g_mae_loss_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),

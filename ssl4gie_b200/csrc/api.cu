@@ -198,4 +198,32 @@ int s4g_mae_loss_bwd(const float* pred, const float* images, const float* mask, 
   return k_mae_loss_bwd(pred, images, mask, scratch, grad_out, dpred, B, norm_pix, ST(stream));
 }
 
+size_t s4g_aug_resize_scratch_bytes(const long long* desc_host, int B, int C) {
+  if (!desc_host || B < 1) return 0;
+  return aug_resize_scratch_bytes(desc_host, B, C, nullptr);
+}
+int s4g_aug_resize(const unsigned char* src, const long long* desc_dev, const long long* desc_host, int B, int C, void* scratch,
+                   size_t scratch_bytes, unsigned char* out, void* stream) {
+  if (!src || !desc_dev || !desc_host || !scratch || !out || B < 1) { s4g_set_error("aug_resize: bad argument"); return S4G_ERR_STATE; }
+  return k_aug_resize(src, desc_dev, desc_host, B, C, scratch, scratch_bytes, out, ST(stream));
+}
+int s4g_aug_color_jitter(unsigned char* img, const void* params, int B, void* stream) {
+  if (!img || !params || B < 1) { s4g_set_error("aug_color_jitter: bad argument"); return S4G_ERR_STATE; }
+  return k_aug_color_jitter(img, params, B, ST(stream));
+}
+int s4g_aug_blur_normalize(const unsigned char* img, const float* sigma, float* out, const float* mean3_host,
+                           const float* std3_host, int B, void* stream) {
+  if (!img || !out || !mean3_host || !std3_host || B < 1) { s4g_set_error("aug_blur_normalize: bad argument"); return S4G_ERR_STATE; }
+  return k_aug_blur_normalize(img, sigma, out, mean3_host, std3_host, B, ST(stream));
+}
+int s4g_aug_mask_to_tensor(const unsigned char* img, float* out, int B, int C, void* stream) {
+  if (!img || !out || B < 1) { s4g_set_error("aug_mask_to_tensor: bad argument"); return S4G_ERR_STATE; }
+  return k_aug_mask_to_tensor(img, out, B, C, ST(stream));
+}
+int s4g_aug_geometric(const float* x, const float* y, float* xo, float* yo, const void* params, float fill_x, float fill_y,
+                      int B, void* stream) {
+  if (!x || !xo || !params || (y && !yo) || B < 1) { s4g_set_error("aug_geometric: bad argument"); return S4G_ERR_STATE; }
+  return k_aug_geometric(x, y, xo, yo, params, fill_x, fill_y, B, ST(stream));
+}
+
 }  // extern "C"

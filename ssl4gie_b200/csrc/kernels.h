@@ -72,6 +72,13 @@ template <typename T> int k_gelu(const T* u, T* out, long long n, cudaStream_t s
 template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, int ld, cudaStream_t st, const Reducer* red = nullptr);  // out overwritten
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out = nullptr);  // inverse of above (+ optional T copy of the result)
+// GPU input pipeline (augment.cu; Binary_segmentation/Data/dataset.py:34-64, dataloaders.py:62-76)
+size_t aug_resize_scratch_bytes(const long long* desc_host, int B, int C, long long* tmp_off_host);
+int k_aug_resize(const uint8_t* src, const long long* desc_dev, const long long* desc_host, int B, int C, void* scratch, size_t scratch_bytes, uint8_t* out, cudaStream_t st);
+int k_aug_color_jitter(uint8_t* img, const void* params, int B, cudaStream_t st);
+int k_aug_blur_normalize(const uint8_t* img, const float* sigma, float* out, const float* mean3, const float* std3, int B, cudaStream_t st);
+int k_aug_mask_to_tensor(const uint8_t* img, float* out, int B, int C, cudaStream_t st);
+int k_aug_geometric(const float* x, const float* y, float* xo, float* yo, const void* params, float fill_x, float fill_y, int B, cudaStream_t st);
 // MAE pretraining step (mae.cu; Models/mae/models_mae.py:123-214)
 int k_mae_masking(const float* noise, int* ids_restore, int* ids_keep, float* mask, int B, int L, int keep, cudaStream_t st);
 template <typename T> int k_mae_patchify_kept(const float* img, const int* ids_keep, T* out, int B, int keep, cudaStream_t st);

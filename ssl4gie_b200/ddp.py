@@ -35,9 +35,10 @@ def bucket_slices(names_by_bucket, offsets):
     return [[(lo, hi) for lo, hi in r] for r in runs]
 
 
-def allreduce_buckets(flat, slices, group=None, events=None, comm_stream=None):
+def allreduce_buckets(flat, slices, group=None, events=None, comm_stream=None, after_bucket=None):
     """Sum-all-reduce every range of every bucket of `flat` (in place).  On CUDA each bucket waits for its event on the
-    communication stream; on CPU (gloo, used by the tests) the calls are issued in order."""
+    communication stream; on CPU (gloo, used by the tests) the calls are issued in order.  after_bucket(ranges) is called
+    once a bucket's exchanges are enqueued (the fused optimizer step of that bucket)."""
     for i, ranges in enumerate(slices):
         if not ranges:
             continue
@@ -45,6 +46,8 @@ def allreduce_buckets(flat, slices, group=None, events=None, comm_stream=None):
             comm_stream.wait_event(events[i])
         for lo, hi in ranges:
             dist.all_reduce(flat[lo:hi], group=group)
+        if after_bucket is not None:
+            after_bucket(ranges)
 
 
 class GradientAllReduce:
@@ -61,12 +64,21 @@ class GradientAllReduce:
         self.slices = None
         self.events = None
         self.handles = []
+        # fused_step (opt-in, attach(optimizer, fused_step=True)): FusedAdamW updates each bucket on the communication
+        # stream right after that bucket's all-reduce, i.e. underneath the rest of backward; the optimizer.step() that
+        # follows reduce() is then only the bookkeeping.  Same arithmetic, same result; only for loops that do nothing to
+        # the gradients between reduce() and step() (no clipping / unscaling).
+        self.fused_optimizer = None
         if self.n_buckets < 1:
             raise ValueError("GradientAllReduce: n_buckets must be >= 1")
 
-    def attach(self, optimizer):
+    def attach(self, optimizer, fused_step=False):
         """Fold the 1/world_size of DDP's gradient MEAN (train_segmentation.py:203) into the optimizer kernel: the
         all-reduce here is a sum.  Called by train_epoch; call it yourself in a hand-written loop."""
+        if fused_step:
+            if not hasattr(optimizer, "step_range"):
+                raise TypeError("fused_step needs ssl4gie_b200.FusedAdamW")
+            self.fused_optimizer = optimizer
         if hasattr(optimizer, "grad_scale"):
             optimizer.grad_scale = 1.0 / self.world_size
         elif self.world_size > 1:
@@ -111,6 +123,10 @@ class GradientAllReduce:
         if not self.overlap:  # one all-reduce of the whole arena after backward (S4G_DDP_OVERLAP=0)
             dist.all_reduce(flat, group=self.group)
             return
+        opt = self.fused_optimizer
         with torch.cuda.stream(self.comm_stream):
-            allreduce_buckets(flat, self.slices, self.group, self.events, self.comm_stream)
+            if opt is not None:
+                opt.begin_external_step()
+            allreduce_buckets(flat, self.slices, self.group, self.events, self.comm_stream,
+                              None if opt is None else lambda ranges: [opt.step_range(lo, hi) for lo, hi in ranges])
         cur.wait_stream(self.comm_stream)

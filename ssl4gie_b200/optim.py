@@ -55,8 +55,40 @@ class FusedAdamW(torch.optim.Optimizer):
         self.wd_slots = wd.to(e.flat_params.device)
         self._wd_key = tuple(g["weight_decay"] for g in self.param_groups)
 
+    # ---- bucket-wise stepping (GradientAllReduce.attach(optimizer, fused_step=True)) ----
+    def begin_external_step(self):
+        """The next step is applied range by range through step_range(); step() then only acknowledges it."""
+        self.step_count += 1
+        self._external = True
+
+    @torch.no_grad()
+    def step_range(self, lo, hi):
+        """AdamW on floats [lo, hi) of the arena (lo on a 64-float slot boundary; hi is rounded up to one: padding is zero)."""
+        g = self.param_groups[0]
+        e = self.engine
+        hi = min((hi + 63) // 64 * 64, e.n_active)
+        if lo % 64:
+            raise ValueError("step_range: lo must be a multiple of 64")
+        import ctypes
+
+        def ptr(t):
+            return ctypes.c_void_p(t.data_ptr() + 4 * lo)
+
+        if self.wd_slots is not None:
+            wd = ctypes.c_void_p(self.wd_slots.data_ptr() + 4 * (lo // 64))
+            _C.check(_C.lib().s4g_adamw_step_groups(ptr(e.flat_params), ptr(e.flat_grads), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                                                    hi - lo, g["lr"], g["betas"][0], g["betas"][1], g["eps"], wd, self.step_count,
+                                                    self.grad_scale, _C.stream_ptr()))
+        else:
+            _C.check(_C.lib().s4g_adamw_step(ptr(e.flat_params), ptr(e.flat_grads), ptr(self.exp_avg), ptr(self.exp_avg_sq), hi - lo,
+                                             g["lr"], g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"], self.step_count,
+                                             self.grad_scale, _C.stream_ptr()))
+
     @torch.no_grad()
     def step(self, closure=None):
+        if getattr(self, "_external", False):   # already applied bucket by bucket during the gradient exchange
+            self._external = False
+            return
         g = self.param_groups[0]
         self.step_count += 1
         e = self.engine
