@@ -190,8 +190,10 @@ int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits,
 /* ---- GPU-side input pipeline: the per-sample Pillow / torchvision work of the reference's DataLoader workers
  * (Binary_segmentation/Data/dataset.py:34-64, Data/dataloaders.py:62-76) on a batch of decoded 8-bit images.  Every entry
  * point works on B images of 224 x 224 except s4g_aug_resize, which produces them.
- * s4g_aug_resize: Image.resize((224, 224)) (Pillow 8-bit bicubic, bit-exact).  src = packed images [h][w][C]; desc [B][4] =
- *   {byte offset into src, height, width, channels (== C, 1 or 3)} given both as a device and a host array; out [B,224,224,C]. */
+ * s4g_aug_resize: Image.resize((224, 224)) (Pillow 8-bit bicubic, bit-exact).  src = packed images [h][w][C]; desc [B][5] =
+ *   {byte offset into src, height, width, channels (== C, 1 or 3), byte offset of this image's [h][224][C] intermediate inside
+ *   the scratch (caller-chosen, non-overlapping)} given both as a device and a host array; out [B,224,224,C].  No host
+ *   synchronisation. */
 size_t s4g_aug_resize_scratch_bytes(const long long* desc_host, int B, int C);
 int s4g_aug_resize(const unsigned char* src, const long long* desc_dev, const long long* desc_host, int B, int C,
                    void* scratch, size_t scratch_bytes, unsigned char* out, void* stream);

@@ -6,6 +6,7 @@ hand-written CUDA kernels behind the C ABI in include/ssl4gie_b200.h.  There is 
 every compute call raises if libssl4gie_b200.so is missing or the device is not sm_100.
 """
 from . import utils  # noqa: F401
+from .augment import GpuInputPipeline  # noqa: F401
 from .dpt_decoder import DPT_decoder  # noqa: F401
 from .losses import CrossEntropyLoss, ScaleAndShiftInvariantLoss, SoftDiceLoss  # noqa: F401
 from .mae import MaskedAutoencoderViT, add_weight_decay, adjust_learning_rate, mae_vit_base_patch16  # noqa: F401

@@ -200,7 +200,7 @@ int s4g_mae_loss_bwd(const float* pred, const float* images, const float* mask, 
 
 size_t s4g_aug_resize_scratch_bytes(const long long* desc_host, int B, int C) {
   if (!desc_host || B < 1) return 0;
-  return aug_resize_scratch_bytes(desc_host, B, C, nullptr);
+  return aug_resize_scratch_bytes(desc_host, B, C);
 }
 int s4g_aug_resize(const unsigned char* src, const long long* desc_dev, const long long* desc_host, int B, int C, void* scratch,
                    size_t scratch_bytes, unsigned char* out, void* stream) {

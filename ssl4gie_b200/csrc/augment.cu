@@ -35,7 +35,7 @@ __global__ void resize_coeffs_kernel(const long long* __restrict__ desc, CoefRow
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= B * 2 * OUT) return;
   const int xx = idx % OUT, axis = (idx / OUT) % 2, img = idx / (2 * OUT);
-  const int in_size = (int)desc[img * 4 + (axis == 0 ? 2 : 1)];   // axis 0: width, axis 1: height
+  const int in_size = (int)desc[img * 5 + (axis == 0 ? 2 : 1)];   // axis 0: width, axis 1: height
   const double scale = (double)in_size / (double)OUT;
   const double filterscale = scale < 1.0 ? 1.0 : scale;
   const double support = __dmul_rn(2.0, filterscale);
@@ -72,13 +72,12 @@ __device__ __forceinline__ uint8_t clip8(long long acc) {
 // horizontal pass: tmp[img][y][xx][c] from src[img][y][x][c]; one thread per (y, xx), all channels
 template <int C>
 __global__ void resize_h_kernel(const uint8_t* __restrict__ src, const long long* __restrict__ desc,
-                                const long long* __restrict__ tmp_off, const CoefRow* __restrict__ table,
-                                uint8_t* __restrict__ tmp) {
+                                const CoefRow* __restrict__ table, uint8_t* __restrict__ tmp) {
   const int img = blockIdx.y;
-  const long long off = desc[img * 4];
-  const int h = (int)desc[img * 4 + 1], w = (int)desc[img * 4 + 2];
+  const long long off = desc[img * 5];
+  const int h = (int)desc[img * 5 + 1], w = (int)desc[img * 5 + 2];
   const CoefRow* rows = table + (size_t)(img * 2) * OUT;
-  uint8_t* dst = tmp + tmp_off[img];
+  uint8_t* dst = tmp + desc[img * 5 + 4];
   for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < (long long)h * OUT; t += (long long)gridDim.x * blockDim.x) {
     const int xx = (int)(t % OUT), y = (int)(t / OUT);
     const CoefRow& r = rows[xx];
@@ -97,11 +96,11 @@ __global__ void resize_h_kernel(const uint8_t* __restrict__ src, const long long
 }
 // vertical pass: out[img][yy][x][c] from tmp[img][y][x][c]
 template <int C>
-__global__ void resize_v_kernel(const uint8_t* __restrict__ tmp, const long long* __restrict__ tmp_off,
+__global__ void resize_v_kernel(const uint8_t* __restrict__ tmp, const long long* __restrict__ desc,
                                 const CoefRow* __restrict__ table, uint8_t* __restrict__ out) {
   const int img = blockIdx.y;
   const CoefRow* rows = table + (size_t)(img * 2 + 1) * OUT;
-  const uint8_t* s = tmp + tmp_off[img];
+  const uint8_t* s = tmp + desc[img * 5 + 4];
   uint8_t* dst = out + (size_t)img * OUT * OUT * C;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < OUT * OUT * C; t += gridDim.x * blockDim.x) {
     const int xc = t % (OUT * C), yy = t / (OUT * C);
@@ -309,50 +308,36 @@ __global__ void geometric_kernel(const float* __restrict__ x, const float* __res
 }  // namespace
 
 // ================================================================================================ host entry points
-size_t aug_resize_scratch_bytes(const long long* desc_host, int B, int C, long long* tmp_off_host) {
-  size_t off = (sizeof(CoefRow) * (size_t)B * 2 * OUT + 255) & ~(size_t)255;
-  const size_t table = off;
-  off += (sizeof(long long) * (size_t)B + 255) & ~(size_t)255;
+// desc [B][5] = {byte offset into src, height, width, channels, byte offset of the [h][224][C] intermediate inside tmp}
+static size_t aug_table_bytes(int B) { return (sizeof(CoefRow) * (size_t)B * 2 * OUT + 255) & ~(size_t)255; }
+size_t aug_resize_scratch_bytes(const long long* desc_host, int B, int C) {
   size_t tmp = 0;
-  for (int b = 0; b < B; ++b) {
-    if (tmp_off_host) tmp_off_host[b] = (long long)tmp;
-    tmp += ((size_t)desc_host[b * 4 + 1] * OUT * C + 15) & ~(size_t)15;
-  }
-  (void)table;
-  return off + tmp;
+  for (int b = 0; b < B; ++b) tmp = std::max(tmp, (size_t)desc_host[b * 5 + 4] + (size_t)desc_host[b * 5 + 1] * OUT * C);
+  return aug_table_bytes(B) + tmp + 16;
 }
-// src: packed 8-bit images; desc (host AND device copies): [B][4] = {byte offset, height, width, channels == C}
 int k_aug_resize(const uint8_t* src, const long long* desc_dev, const long long* desc_host, int B, int C, void* scratch,
                  size_t scratch_bytes, uint8_t* out, cudaStream_t st) {
   if (C != 1 && C != 3) { s4g_set_error("aug_resize: 1 or 3 channels"); return S4G_ERR_SHAPE; }
   long long max_h = 1;
-  std::vector<long long> tmp_off(B);
   for (int b = 0; b < B; ++b) {
-    const long long h = desc_host[b * 4 + 1], w = desc_host[b * 4 + 2];
-    if (desc_host[b * 4 + 3] != C || h < 1 || w < 1) { s4g_set_error("aug_resize: bad image descriptor"); return S4G_ERR_SHAPE; }
+    const long long h = desc_host[b * 5 + 1], w = desc_host[b * 5 + 2];
+    if (desc_host[b * 5 + 3] != C || h < 1 || w < 1 || desc_host[b * 5 + 4] < 0) { s4g_set_error("aug_resize: bad image descriptor"); return S4G_ERR_SHAPE; }
     // coefficients per output index: ceil(2 * scale) * 2 + 1 <= KMAX
     if (std::max(h, w) > (long long)OUT * (KMAX - 3) / 4) { s4g_set_error("aug_resize: source side too long for the coefficient table"); return S4G_ERR_SHAPE; }
     max_h = std::max(max_h, h);
   }
-  const size_t need = aug_resize_scratch_bytes(desc_host, B, C, tmp_off.data());
-  if (scratch_bytes < need) { s4g_set_error("aug_resize: scratch too small"); return S4G_ERR_WORKSPACE; }
-  char* base = reinterpret_cast<char*>(scratch);
-  CoefRow* table = reinterpret_cast<CoefRow*>(base);
-  size_t off = (sizeof(CoefRow) * (size_t)B * 2 * OUT + 255) & ~(size_t)255;
-  long long* tmp_off_dev = reinterpret_cast<long long*>(base + off);
-  off += (sizeof(long long) * (size_t)B + 255) & ~(size_t)255;
-  uint8_t* tmp = reinterpret_cast<uint8_t*>(base + off);
-  S4G_CUDA(cudaMemcpyAsync(tmp_off_dev, tmp_off.data(), sizeof(long long) * B, cudaMemcpyHostToDevice, st));
-  S4G_CUDA(cudaStreamSynchronize(st));   // tmp_off is a stack-owned host vector
+  if (scratch_bytes < aug_resize_scratch_bytes(desc_host, B, C)) { s4g_set_error("aug_resize: scratch too small"); return S4G_ERR_WORKSPACE; }
+  CoefRow* table = reinterpret_cast<CoefRow*>(scratch);
+  uint8_t* tmp = reinterpret_cast<uint8_t*>(scratch) + aug_table_bytes(B);
   resize_coeffs_kernel<<<cdiv((long long)B * 2 * OUT, 128), 128, 0, st>>>(desc_dev, table, B);
   S4G_KERNEL_CHECK();
   const dim3 gh((unsigned)std::min<long long>(cdiv(max_h * OUT, 256), 148 * 4), B), gv(cdiv((long long)OUT * OUT * C, 256), B);
   if (C == 3) {
-    resize_h_kernel<3><<<gh, 256, 0, st>>>(src, desc_dev, tmp_off_dev, table, tmp);
-    resize_v_kernel<3><<<gv, 256, 0, st>>>(tmp, tmp_off_dev, table, out);
+    resize_h_kernel<3><<<gh, 256, 0, st>>>(src, desc_dev, table, tmp);
+    resize_v_kernel<3><<<gv, 256, 0, st>>>(tmp, desc_dev, table, out);
   } else {
-    resize_h_kernel<1><<<gh, 256, 0, st>>>(src, desc_dev, tmp_off_dev, table, tmp);
-    resize_v_kernel<1><<<gv, 256, 0, st>>>(tmp, tmp_off_dev, table, out);
+    resize_h_kernel<1><<<gh, 256, 0, st>>>(src, desc_dev, table, tmp);
+    resize_v_kernel<1><<<gv, 256, 0, st>>>(tmp, desc_dev, table, out);
   }
   S4G_KERNEL_CHECK();
   return 0;

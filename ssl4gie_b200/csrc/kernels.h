@@ -73,7 +73,7 @@ template <typename T> int k_colsum(const T* dy, float* out, long long M, int N, 
 template <typename T> int k_tokens_to_nhwc(const float* x, T* out, int B, cudaStream_t st);                // drop cls, cast
 template <typename T> int k_tap_grad(const T* dtap, float* dx, int B, int accumulate, cudaStream_t st, T* cast_out = nullptr);  // inverse of above (+ optional T copy of the result)
 // GPU input pipeline (augment.cu; Binary_segmentation/Data/dataset.py:34-64, dataloaders.py:62-76)
-size_t aug_resize_scratch_bytes(const long long* desc_host, int B, int C, long long* tmp_off_host);
+size_t aug_resize_scratch_bytes(const long long* desc_host, int B, int C);
 int k_aug_resize(const uint8_t* src, const long long* desc_dev, const long long* desc_host, int B, int C, void* scratch, size_t scratch_bytes, uint8_t* out, cudaStream_t st);
 int k_aug_color_jitter(uint8_t* img, const void* params, int B, cudaStream_t st);
 int k_aug_blur_normalize(const uint8_t* img, const float* sigma, float* out, const float* mean3, const float* std3, int B, cudaStream_t st);

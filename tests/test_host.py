@@ -249,3 +249,31 @@ def test_mae_module_manifest_groups_and_schedule(golden_dir):
         assert _Opt.param_groups[0]["lr"] == lr and _Opt.param_groups[1]["lr"] == lr * 0.5
     with pytest.raises(NotImplementedError):
         ssl4gie_b200.MaskedAutoencoderViT()  # mae_vit_large defaults: outside the B200 schedule
+
+
+def test_input_pipeline_draws_like_the_reference():
+    """GpuInputPipeline.draw consumes torch's generator and `random` exactly as one sample of the reference does:
+    ColorJitter.get_params, GaussianBlur.get_params (dataloaders.py:64-66), then dataset.py:46-60."""
+    import random
+
+    T = pytest.importorskip("torchvision.transforms")
+    from ssl4gie_b200 import GpuInputPipeline
+    from ssl4gie_b200.augment import inverse_affine_matrix
+    from torchvision.transforms.functional import _get_inverse_affine_matrix
+    pipe = GpuInputPipeline(train=True)
+    jit = T.ColorJitter(brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01)
+    for seed in range(5):
+        torch.manual_seed(seed)
+        random.seed(seed)
+        p, p2 = pipe.draw(), pipe.draw()
+        torch.manual_seed(seed)
+        random.seed(seed)
+        for q in (p, p2):
+            order, b, c, s, h = T.ColorJitter.get_params(jit.brightness, jit.contrast, jit.saturation, jit.hue)
+            sigma = T.GaussianBlur.get_params(0.001, 2.0)
+            assert (q.order, q.brightness, q.contrast, q.saturation, q.hue, q.sigma) == (order.tolist(), b, c, s, h, sigma)
+            assert q.hflip == (random.uniform(0.0, 1.0) > 0.5) and q.vflip == (random.uniform(0.0, 1.0) > 0.5)
+            ref = (random.uniform(-180.0, 180.0), (random.uniform(-28.0, 28.0), random.uniform(-28.0, 28.0)),
+                   random.uniform(0.5, 1.5), random.uniform(-22.5, 22.5))
+            assert q.affine == ref
+            assert inverse_affine_matrix(*ref) == _get_inverse_affine_matrix([0.0, 0.0], ref[0], list(ref[1]), ref[2], [ref[3], 0.0])
