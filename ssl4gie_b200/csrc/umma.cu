@@ -31,9 +31,66 @@ constexpr int FPROP_THREADS = 64 + 32 * EPI_WARPS;
 using namespace s4g_ptx;
 
 // ------------------------------------------------------------------------------------------ shared layout
+constexpr int TQ = 4;   // tile queue depth (dynamic scheduling)
 struct SmemCtl {
   uint64_t full[MAX_STAGES], empty[MAX_STAGES], tfull[2], tempty[2];
+  uint64_t qfull[TQ], qempty[TQ];   // dynamic tile scheduler: queue of tile indices, filled by the leader CTA's producer thread
+  int qtile[TQ];
   uint32_t tmem_base;
+};
+
+// Dynamic tile scheduling.  With a static partition (tile = group + k * groups) a CTA that cannot be placed -- another
+// kernel (an NCCL collective on the communication stream) holds its SM -- keeps its whole share of tiles waiting while the
+// resident CTAs go idle.  Here the leader CTA's producer thread draws tile indices from a global counter and publishes each
+// one to the MMA / epilogue warps of the pair and to the peer CTA's producer through a small shared-memory queue
+// (st.async + mbarrier complete_tx, so the value is visible with the barrier phase); late CTAs simply find no work left.
+// tile -> output mapping is unchanged, so results do not depend on who computed what.  counter[0] = next tile,
+// counter[1] = groups that have finished; the last group to finish resets both for the next launch.
+struct TileSched {
+  SmemCtl* ctl;
+  int* counter;      // null: static partition
+  int group, num_groups, num_tiles, rank, cg, consumers;
+  __device__ __forceinline__ bool dyn() const { return counter != nullptr; }
+  __device__ __forceinline__ int fetch() const { return atomicAdd(counter, 1); }
+  // leader producer thread: hand tile `t` (or -1 = no more work) of step k to every consumer of the pair
+  __device__ __forceinline__ void publish(int k, int t) const {
+    const int slot = k & (TQ - 1);
+    mbar_wait(&ctl->qempty[slot], ((k / TQ) & 1) ^ 1);
+    if (cg == 1) {   // no cluster: an ordinary store, published by the barrier arrival (release) / wait (acquire)
+      *reinterpret_cast<volatile int*>(&ctl->qtile[slot]) = t;
+      mbar_arrive(&ctl->qfull[slot]);
+      return;
+    }
+    for (int c = 0; c < cg; ++c) st_async_u32(map_to_cta(&ctl->qtile[slot], c), (uint32_t)t, map_to_cta(&ctl->qfull[slot], c));
+    mbar_expect_tx(&ctl->qfull[slot], 4);   // this CTA's arrival for the phase (the leader's producer does not read the queue)
+  }
+  // peer producer thread: arm this CTA's barrier, then read like any consumer
+  __device__ __forceinline__ int take_armed(int k) const {
+    mbar_expect_tx(&ctl->qfull[k & (TQ - 1)], 4);
+    const int t = take(k);
+    release(k);
+    return t;
+  }
+  // read step k (any number of threads); ONE thread per consumer then calls release(k) once all of them have read
+  __device__ __forceinline__ int take(int k) const {
+    if (!dyn()) { const int t = group + k * num_groups; return t < num_tiles ? t : -1; }
+    const int slot = k & (TQ - 1);
+    mbar_wait(&ctl->qfull[slot], (k / TQ) & 1);
+    return *reinterpret_cast<volatile int*>(&ctl->qtile[slot]);
+  }
+  __device__ __forceinline__ void release(int k) const {
+    if (!dyn()) return;
+    if (cg == 1) mbar_arrive(&ctl->qempty[k & (TQ - 1)]);
+    else mbar_arrive_leader(&ctl->qempty[k & (TQ - 1)]);
+  }
+  __device__ __forceinline__ void init_barriers() const {
+    for (int i = 0; i < TQ; ++i) { mbar_init(&ctl->qfull[i], 1); mbar_init(&ctl->qempty[i], consumers); }
+  }
+  // after the kernel's final barrier, one thread of the leader CTA
+  __device__ __forceinline__ void finish() const {
+    if (!dyn()) return;
+    if (atomicAdd(counter + 1, 1) == num_groups - 1) { counter[0] = 0; counter[1] = 0; __threadfence(); }
+  }
 };
 
 struct TileGeom {  // how a row tile maps onto the NHWC tensor: rows = (dn, dy, dx) boxes
@@ -54,6 +111,7 @@ struct FpropParams {
   int tma_epi;       // 1: bf16 outputs staged in swizzled smem and written with TMA stores
   int f32_epi;       // 1: fp32 outputs (+ fp32 residual) of a plain matrix, transposed through the staging slab (coalesced)
   long long M;       // rows of the output matrix (for the aux read guard)
+  int* tile_counter; // dynamic tile scheduler (null: static partition)
   EpiParams e;
 };
 
@@ -192,6 +250,8 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
   const int k_iters = p.taps * p.chunks;
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
   const int group = blockIdx.x / CG, num_groups = gridDim.x / CG;
+  // queue consumers that release a slot: the epilogue warps of every CTA of the group, the MMA warp, the peer's producer
+  const TileSched sched{ctl, p.tile_counter, group, num_groups, num_tiles, rank, CG, CG * EPI_WARPS + 1 + (CG - 1)};
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -199,6 +259,7 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
     if (p.tma_epi) { tma_prefetch_desc(&tmO); if (p.e.out2) tma_prefetch_desc(&tmO2); }
     for (int i = 0; i < STG; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], EPI_WARPS * CG); }
+    sched.init_barriers();
     fence_barrier_init();
   }
   if (warp == 1) { if (CG == 2) tmem_alloc_pair(&ctl->tmem_base, 512); else tmem_alloc(&ctl->tmem_base, 512); }
@@ -210,10 +271,22 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
   const uint32_t tmem_base = ctl->tmem_base;
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------------ TMA producer (+ tile scheduler in the leader CTA)
     if (elect_one()) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = group; tile < num_tiles; tile += num_groups) {
+      int next = (sched.dyn() && rank == 0) ? sched.fetch() : 0;
+      for (int k = 0;; ++k) {
+        int tile;
+        if (sched.dyn() && rank == 0) {
+          tile = next < num_tiles ? next : -1;
+          sched.publish(k, tile);
+          if (tile >= 0) next = sched.fetch();   // in flight while this tile's loads are issued
+        } else if (sched.dyn()) {
+          tile = sched.take_armed(k);
+        } else {
+          tile = sched.take(k);
+        }
+        if (tile < 0) break;
         const int tm = (tile / p.tiles_n) * CG + rank, tn = tile % p.tiles_n;
         int n0, h0, w0;
         tile_origin(p.tg, tm, n0, h0, w0);
@@ -242,11 +315,15 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
     const uint32_t idesc = make_idesc(128 * CG, p.block_n, 0, 0);
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int tile = group; tile < num_tiles && rank == 0; tile += num_groups) {
+    for (int k = 0; rank == 0; ++k) {
+      const int tile = sched.take(k);
+      __syncwarp();
+      if (lane == 0) sched.release(k);
+      if (tile < 0) break;
       mbar_wait(&ctl->tempty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * 256;
-      for (int k = 0; k < k_iters; ++k) {
+      for (int ki = 0; ki < k_iters; ++ki) {
         mbar_wait(&ctl->full[stage], phase);
         tc_fence_after();
         if (elect_one()) {
@@ -256,15 +333,15 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
           for (int kk = 0; kk < BLOCK_K / 16; ++kk) {
             const uint64_t da = make_desc(sa + kk * 32, 16, 1024);
             const uint64_t db = make_desc(sb + kk * 32, 16, 1024);
-            if (CG == 2) umma_bf16_pair(tmem_d, da, db, idesc, (k | kk) != 0);
-            else umma_bf16(tmem_d, da, db, idesc, (k | kk) != 0);
+            if (CG == 2) umma_bf16_pair(tmem_d, da, db, idesc, (ki | kk) != 0);
+            else umma_bf16(tmem_d, da, db, idesc, (ki | kk) != 0);
           }
           if (CG == 2) {
             umma_commit_pair(&ctl->empty[stage]);
-            if (k == k_iters - 1) umma_commit_pair(&ctl->tfull[acc]);
+            if (ki == k_iters - 1) umma_commit_pair(&ctl->tfull[acc]);
           } else {
             umma_commit(&ctl->empty[stage]);
-            if (k == k_iters - 1) umma_commit(&ctl->tfull[acc]);
+            if (ki == k_iters - 1) umma_commit(&ctl->tfull[acc]);
           }
         }
         __syncwarp();
@@ -278,7 +355,11 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
     const int r = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
     const TileGeom& t = p.tg;
-    for (int tile = group; tile < num_tiles; tile += num_groups) {
+    for (int k = 0;; ++k) {
+      const int tile = sched.take(k);
+      __syncwarp();
+      if (lane == 0) sched.release(k);
+      if (tile < 0) break;
       const int tm = (tile / p.tiles_n) * CG + rank, tn = tile % p.tiles_n;
       int n0, h0, w0;
       tile_origin(t, tm, n0, h0, w0);
@@ -477,6 +558,7 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();   // the peer may still signal this CTA's barriers until here
   if (warp == 1) { if (CG == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
+  if (threadIdx.x == 0 && rank == 0) sched.finish();
 }
 
 // =========================================================================================== wgrad
@@ -491,6 +573,7 @@ struct WgradParams {
   float* part;       // split-K partials: [split][tap][tci][tco][block_n columns (ci)][128 rows (co)] fp32
   float* dW;         // direct mode (splits == 1, linear layer): the epilogue writes dW [Cout][Cin] itself
   int direct;
+  int* tile_counter; // dynamic work scheduler (null: static partition)
 };
 
 // CG = 2: a CTA pair owns a 256 (co) x block_n (ci) output tile (cta_group::2): each CTA stages its own 128 dY channels
@@ -511,12 +594,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   const int chunks_per_split = p.chunks_per_split;
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
   const int group = blockIdx.x / CG, num_groups = gridDim.x / CG;
+  const TileSched sched{ctl, p.tile_counter, group, num_groups, num_work, rank, CG, CG * 4 + 1 + (CG - 1)};
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmY);
     tma_prefetch_desc(&tmX);
     for (int i = 0; i < STG; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tfull[i], 1); mbar_init(&ctl->tempty[i], 4 * CG); }
+    sched.init_barriers();
     fence_barrier_init();
   }
   if (warp == 1) { if (CG == 2) tmem_alloc_pair(&ctl->tmem_base, 512); else tmem_alloc(&ctl->tmem_base, 512); }
@@ -537,7 +622,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   if (warp == 0) {
     if (elect_one()) {
       int stage = 0; uint32_t phase = 0;
-      for (int wi = group; wi < num_work; wi += num_groups) {
+      int next = (sched.dyn() && rank == 0) ? sched.fetch() : 0;
+      for (int k = 0;; ++k) {
+        int wi;
+        if (sched.dyn() && rank == 0) {
+          wi = next < num_work ? next : -1;
+          sched.publish(k, wi);
+          if (wi >= 0) next = sched.fetch();
+        } else if (sched.dyn()) {
+          wi = sched.take_armed(k);
+        } else {
+          wi = sched.take(k);
+        }
+        if (wi < 0) break;
         int split, tap, tci, tco;
         decode(wi, split, tap, tci, tco);
         const int co0 = (tco * CG + rank) * 128;
@@ -568,7 +665,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
     const uint32_t idesc = make_idesc(128 * CG, p.block_n, 1, 1);
     int stage = 0; uint32_t phase = 0;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int wi = group; wi < num_work && rank == 0; wi += num_groups) {
+    for (int k = 0; rank == 0; ++k) {
+      const int wi = sched.take(k);
+      __syncwarp();
+      if (lane == 0) sched.release(k);
+      if (wi < 0) break;
       int split, tap, tci, tco;
       decode(wi, split, tap, tci, tco);
       const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
@@ -606,7 +707,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   } else {
     const int q = warp & 3;
     int acc = 0; uint32_t acc_phase = 0;
-    for (int wi = group; wi < num_work; wi += num_groups) {
+    for (int k = 0;; ++k) {
+      const int wi = sched.take(k);
+      __syncwarp();
+      if (lane == 0) sched.release(k);
+      if (wi < 0) break;
       int split, tap, tci, tco;
       decode(wi, split, tap, tci, tco);
       const int c_begin = split * chunks_per_split, c_end = min(p.chunks_total, c_begin + chunks_per_split);
@@ -647,6 +752,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) umma_wgrad_kernel(const __grid
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 1) { if (CG == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
+  if (threadIdx.x == 0 && rank == 0) sched.finish();
 }
 
 // Deterministic split-K reduction + layout change: dW[co*so + ci*si + tap*st] = sum_split part[split][tap][tci][tco][ci][co]
@@ -733,6 +839,21 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 int g_num_sms = 148;
+// dynamic tile scheduler: a ring of {next tile, finished groups} counter pairs, one per launch; each kernel leaves its pair
+// zeroed (TileSched::finish), so the ring never needs clearing again.  OFF by default (S4G_DYN_TILES=1 turns it on): measured
+// on B200 it costs 0.3 ms per step alone (one atomic round trip before the first load of each of ~230 launches) and, against
+// expectation, 2 ms per step next to NCCL at N = 2 -- kept as an experiment knob with its parity tests.
+constexpr int TILE_COUNTER_RING = 256;
+constexpr int MAX_DEV = 64;
+int* g_tile_counters[MAX_DEV] = {};
+unsigned g_tile_counter_next = 0;
+int g_dyn_tiles = 0;
+int* next_tile_counter() {
+  if (!g_dyn_tiles) return nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV || !g_tile_counters[dev]) return nullptr;
+  return g_tile_counters[dev] + 2 * (g_tile_counter_next++ % TILE_COUNTER_RING);
+}
 int g_pdl = 1;  // programmatic dependent launch of the tcgen05 kernels (S4G_PDL=0 turns it off)
 
 int make_map(CUtensorMap* map, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
@@ -841,6 +962,11 @@ int umma_init() {
   S4G_CUDA(cudaGetDevice(&dev));
   S4G_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   if (const char* e = getenv("S4G_PDL")) g_pdl = atoi(e) != 0;
+  if (const char* e = getenv("S4G_DYN_TILES")) g_dyn_tiles = atoi(e) != 0;
+  if (dev >= 0 && dev < MAX_DEV && !g_tile_counters[dev]) {
+    S4G_CUDA(cudaMalloc(&g_tile_counters[dev], sizeof(int) * 2 * TILE_COUNTER_RING));
+    S4G_CUDA(cudaMemset(g_tile_counters[dev], 0, sizeof(int) * 2 * TILE_COUNTER_RING));
+  }
   // S4G_SM_LIMIT: persistent grids leave SMs free for a concurrently running collective (experiment knob)
   if (const char* lim = getenv("S4G_SM_LIMIT")) { const int v = atoi(lim); if (v >= 2 && v < g_num_sms) g_num_sms = v & ~1; }
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -883,6 +1009,7 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     S4G_TRY(make_map(&tmB, W, 3, dims, strides, box));
   }
   p.M = (long long)g.Nimg * g.Hi * g.Wi;
+  p.tile_counter = next_tile_counter();
   p.tma_epi = !(e.out_f32 || e.res || e.accumulate) && e.ldo % 8 == 0 && (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 &&
               (!e.out2 || (reinterpret_cast<uintptr_t>(e.out2) & 15) == 0);
   p.f32_epi = matrix && e.out_f32 && !e.accumulate && (!e.res || e.res_f32) && !e.out2 &&
@@ -1010,6 +1137,7 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   p.tiles_ci = w.tiles_ci;
   p.chunks_total = w.chunks_total;
   p.splits = w.splits;
+  p.tile_counter = next_tile_counter();
   p.stages = w.stages;
   p.chunks_per_split = w.cps;
   p.part = scratch;
