@@ -33,7 +33,8 @@ def _mae_gflop_per_img():
     return 3.0 * fwd / 1e9
 
 
-GFLOP_PER_IMG["mae"] = _mae_gflop_per_img()
+GFLOP_PER_IMG["mae"] = 58.69   # BASELINE.md §2 (hooks on the reference modules, which embed all 196 patches; _mae_gflop_per_img()
+#                                   = 58.17 counts the 49 visible ones this schedule embeds)
 METRIC = "ViT-B/DPT seg train img/s @1/2/4/8 B200; % tensor-pipe peak; CPU baseline"
 
 

@@ -147,3 +147,39 @@ def adjust_learning_rate(optimizer, epoch, lr, warmup_epochs=40, epochs=800, min
     for group in optimizer.param_groups:
         group["lr"] = cur * group["lr_scale"] if "lr_scale" in group else cur
     return cur
+
+
+def train_one_epoch(model, data_loader, optimizer, device, epoch, loss_scaler=None, log_writer=None, args=None, grad_sync=None):
+    """Drop-in for Models/mae/engine_pretrain.py:20-81 without its two host synchronisations per step (`loss.item()` at :50,
+    `torch.cuda.synchronize()` at :62): the per-iteration LR schedule (:42-43), the bf16 forward (`torch.cuda.amp.autocast`
+    at :47), backward and the optimizer step are enqueued back to back, the loss is accumulated on the device and read once at
+    the end of the epoch (a non-finite loss is reported then, not at the step that produced it).
+
+    args needs .lr, .warmup_epochs, .epochs, .min_lr, .mask_ratio and .accum_iter == 1 (gradient accumulation would need the
+    flat gradient arena to add instead of overwrite).  loss_scaler is accepted for signature compatibility and unused: bf16
+    needs no loss scaling.  grad_sync: a ddp.GradientAllReduce when training data-parallel.  Returns {"loss": mean, "lr": last}."""
+    if getattr(args, "accum_iter", 1) != 1:
+        raise NotImplementedError("ssl4gie_b200 MAE pretraining: accum_iter must be 1")
+    model.train(True)
+    core = model.module if hasattr(model, "module") else model
+    n = len(data_loader)
+    total = torch.zeros((), dtype=torch.float32, device=device)
+    lr = 0.0
+    for it, (samples, _) in enumerate(data_loader):
+        lr = adjust_learning_rate(optimizer, it / n + epoch, args.lr, args.warmup_epochs, args.epochs, getattr(args, "min_lr", 0.0))
+        samples = samples.to(device, non_blocking=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss, _, _ = core(samples, mask_ratio=args.mask_ratio)
+        loss.backward()
+        if grad_sync is not None:
+            grad_sync.reduce()
+        optimizer.step()
+        optimizer.zero_grad()
+        total += loss.detach()
+        if log_writer is not None and (it + 1) % 20 == 0:
+            log_writer.add_scalar("lr", lr, int((it / n + epoch) * 1000))
+    mean = (total / max(n, 1)).item()
+    if not math.isfinite(mean):
+        raise FloatingPointError("Loss is {}, stopping training".format(mean))
+    print("Averaged stats: lr: {:.6f}  loss: {:.4f}".format(lr, mean))
+    return {"loss": mean, "lr": lr}

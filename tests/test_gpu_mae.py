@@ -168,3 +168,24 @@ def test_pretrain_steps_follow_the_reference_optimizer():
     moved = max(_l2(p.detach() - sd[n].cuda(), params[n].detach() - sd[n].cuda()) for n, p in m.named_parameters() if p.requires_grad)
     print(f"[mae fp32 {steps} optimizer steps] worst loss deviation {worst:.2e}, worst relative error of a parameter's total update {moved:.2e}")
     assert worst < 1e-3 and moved < 2e-2
+
+
+def test_train_one_epoch_loop():
+    """ssl4gie_b200.mae.train_one_epoch (engine_pretrain.py:20-81 without its per-step host syncs): bf16 under autocast, the
+    per-iteration schedule, a falling loss on a repeated batch, and the same result from a second identical run."""
+    import types
+
+    from ssl4gie_b200 import FusedAdamW, add_weight_decay
+    from ssl4gie_b200.mae import train_one_epoch
+    args = types.SimpleNamespace(lr=3e-4, warmup_epochs=1, epochs=10, min_lr=0.0, mask_ratio=0.75, accum_iter=1)
+    x, _ = _inputs(8, seed=31)
+    loader = [(x, None)] * 6
+    out = []
+    for _ in range(2):
+        torch.manual_seed(0)            # the masking noise is drawn from torch's CUDA generator, as in the reference
+        m = _model(ref_port.mae_make_state(seed=42), "auto", "auto")
+        opt = FusedAdamW(m, lr=args.lr, betas=(0.9, 0.95), param_groups=add_weight_decay(m, 0.05))
+        stats = [train_one_epoch(m, loader, opt, torch.device("cuda"), ep, None, None, args) for ep in range(3)]
+        out.append([s["loss"] for s in stats])
+        assert abs(stats[-1]["lr"] - ref_port.mae_lr(2 * 6 + 5, 6, args.lr, 1, 10)) < 1e-12
+    assert out[0][2] < out[0][0] and out[0] == out[1], out
