@@ -407,6 +407,28 @@ def side_measurements(task, B, roof):
                             "images_per_gpu": d["config"]["images_per_gpu"], "model_tflops_per_gpu": d["model_tflops_per_gpu"], "steps": 20}
         except Exception as e:  # noqa: BLE001
             extra[other] = {"error": repr(e)[:200]}
+    # §8f rows built in round 2: the MAE pretraining step (BASELINE.json configs[4]) and the GPU input pipeline
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--task", "mae", "--steps", "20", "--warmup", "5",
+                            "--no-cpu-baseline", "--no-extras"], capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        extra["mae"] = {"value": d["value"], "unit": "img/s", "ms_per_step": d["ms_per_step"], "e2e": d["e2e"]["value"],
+                        "images_per_gpu": d["config"]["images_per_gpu"], "model_tflops_per_gpu": d["model_tflops_per_gpu"], "steps": 20,
+                        "workload": d["config"]["workload"]}
+    except Exception as e:  # noqa: BLE001
+        extra["mae"] = {"error": repr(e)[:200]}
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "bench_augment.py"), "64"], capture_output=True, text=True,
+                           timeout=600, cwd=ROOT)
+        g = re.search(r"GPU pipeline: ([0-9.]+) img/s.*kernels alone ([0-9.]+) ms per batch = ([0-9.]+) img/s", r.stdout)
+        c = re.search(r"one host core: ([0-9.]+) img/s", r.stdout)
+        extra["input_pipeline"] = {"gpu_img_s_from_host_arrays": float(g.group(1)), "gpu_kernels_ms_per_batch64": float(g.group(2)),
+                                   "gpu_kernels_img_s": float(g.group(3)),
+                                   "reference_transforms_img_s_per_host_core": float(c.group(1)) if c else None,
+                                   "note": "64 images of 531x622 + masks: resize, ColorJitter, GaussianBlur 25x25, Normalize, flips + affine "
+                                           "(ssl4gie_b200.GpuInputPipeline vs Pillow / torchvision as the reference's DataLoader workers run them)"}
+    except Exception as e:  # noqa: BLE001
+        extra["input_pipeline"] = {"error": repr(e)[:200]}
     try:
         r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "eager_gpu_baseline.py"), task if task != "cls" else "seg", str(min(B, 64)), "5"],
                            capture_output=True, text=True, timeout=600, cwd=ROOT)

@@ -103,14 +103,14 @@ def test_fp32_step_matches_reference_fixture(golden_dir):
         assert (g.flatten()[:k].cpu() - torch.from_numpy(fix["grad_head"][i][:k])).abs().max().item() < 2e-3 * max(g.abs().max().item(), floor), n
 
 
-@pytest.mark.parametrize("B", [2, 16])
+@pytest.mark.parametrize("B", [2, 16, 64])
 def test_bf16_step_against_oracle(B):
     """bf16 tensor-core path (tcgen05 GEMMs, tensor-core attention incl. the padded 32-dim decoder heads): pred 2e-2 of its
     range, loss 1e-2, the whole gradient AND every single tensor within relative L2 2e-2 / cosine 0.999 of the fp32 oracle
     (measured: 0.7e-2 whole, 1.1e-2 worst tensor); a second run is bit-identical."""
     sd = ref_port.mae_make_state(seed=42)
     m = _model(sd, "bf16", "tensor")
-    x, noise = _inputs(B, seed=5 if B == 2 else 21)
+    x, noise = _inputs(B, seed=5 if B == 2 else 21 + B)
     loss, pred, mask = m(x.cuda(), noise=noise.cuda())
     loss.backward()
     grads = {n: p.grad.clone() for n, p in m.named_parameters() if p.requires_grad}
