@@ -149,6 +149,16 @@ int s4g_layernorm_fwd(const float* x, const float* gamma, const float* beta, voi
 int s4g_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
                       const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, int dtype,
                       void* stream);
+/* Allocation-free variant of s4g_layernorm_bwd (same arguments, same results).  It has no counterpart in the reference: it
+ * was added for callers that cannot call cudaMalloc (CUDA graph capture, serving loops,
+ * harnesses that forbid allocation).  The partial rows of the dgamma / dbeta reduction go into a file-scope __device__ array of
+ * 1 363 968 bytes (148 blocks x 3 x 768 floats) that every GPU loading the library holds until exit, so neither the call nor
+ * any set-up it needs (s4g_init is not required) allocates.  Limit: C <= 768 (kernels exist for C = 512, 768), any row count;
+ * larger shapes return S4G_ERR_WORKSPACE.  All calls on a device share the array (it keeps the last call's rows; nothing has to
+ * start at zero): calls that overlap on the GPU -- different streams without an ordering between them -- race. */
+int s4g_layernorm_bwd_static(const void* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                             const float* dres, float* dx, float* dgamma, float* dbeta, int rows, int C, int dtype,
+                             void* stream);
 /* timm Attention core: qkv [B*N, 3*H*64] -> o [B*N, H*64], lse [B,H,N] */
 int s4g_attention_fwd(const void* qkv, void* o, float* lse, int B, int N, int H, int dtype, int backend, void* stream);
 int s4g_attention_bwd(const void* qkv, const void* o, const void* dout, const float* lse, void* dqkv, int B, int N,

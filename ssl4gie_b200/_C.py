@@ -53,6 +53,7 @@ SIGNATURES = {
     "s4g_wgrad_scratch_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "s4g_layernorm_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _i, _vp]),
     "s4g_layernorm_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "s4g_layernorm_bwd_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "s4g_attention_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "s4g_attention_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "s4g_bilinear2x_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

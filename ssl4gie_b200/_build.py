@@ -7,7 +7,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libssl4gie_b200.so")
-SOURCES = ["api.cu", "engine.cu", "simt.cu", "umma.cu", "elementwise.cu", "attention.cu", "attention_mma.cu", "attention_umma.cu", "loss.cu", "optim.cu", "cls_head.cu", "peer.cu", "reduce.cu", "mae.cu", "augment.cu"]
+SOURCES = ["api.cu", "engine.cu", "simt.cu", "umma.cu", "elementwise.cu", "attention.cu", "attention_mma.cu", "attention_umma.cu", "loss.cu", "optim.cu", "cls_head.cu", "peer.cu", "reduce.cu", "mae.cu", "augment.cu", "no_alloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
          "--expt-relaxed-constexpr", "-Xptxas", "-v"]
