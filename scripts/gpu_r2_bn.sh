@@ -1,0 +1,9 @@
+#!/bin/bash
+# BN statistics fused into the conv epilogue: parity, then A/B against the separate statistics pass
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_model.py tests/test_gpu_determinism.py tests/test_gpu_fullsize.py tests/test_gpu_ops.py -m gpu -q -x > gpurun_out/pytest_bn.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_bn.log | cut -c1-300
+for v in fused pass fused pass; do
+S4G_BN_STATS=$v timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-extras > gpurun_out/bench_bn_$v.json 2> gpurun_out/bench_bn_$v.err; echo "$v rc=$?"
+python -c "
+import json; d=json.loads(open('gpurun_out/bench_bn_$v.json').read().strip().splitlines()[-1]); print('bn_stats=$v', round(d['ms_per_step'],3), 'ms', round(d['value']), 'img/s', d['loss'], d['gpu_launches'])"
+done

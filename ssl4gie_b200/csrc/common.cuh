@@ -175,6 +175,11 @@ struct EpiParams {
   const void* dot_aux;   // bf16 [M, ldo] or null
   float* dot_out;
   int dot_rows, dot_groups;
+  // optional fused COLUMN statistics of the same epilogue (BatchNorm statistics of a conv output, N <= 256 in one column tile),
+  // taken from the bf16-rounded values it stores: every CTA writes ONE row [2 N] = (sum | sum of squares) over all the rows it
+  // produced: stat_part[cta * 2 N + ...], umma_fprop_stat_rows(geometry) rows in total, then summed in a fixed order by
+  // finalize_kernel (reduce.cu): deterministic, no atomics, and the separate statistics pass over the tensor disappears
+  float* stat_part;
 };
 
 template <typename T>

@@ -708,44 +708,78 @@ __device__ __forceinline__ void bil_taps(int i, int in_size, float scale, float 
     wt[k] = (o >= 0 && o < 2 * in_size) ? bil_w(o, i, in_size, scale) : 0.f;
   }
 }
-// grid.y = input row (b * H + h); the separable weights are computed once per thread
+// A thread owns (b, input row h, 8 channels) and walks the output columns ow = 0 .. 2W-1 once: the (up to 5 of 7 candidate) output
+// rows that touch h are combined vertically per column, and the column's value is added to the two input columns w0(ow), w0 + 1 it
+// interpolates between -- w0 never decreases, so two running accumulators suffice and each dx element is written exactly once.
+// Every dy element is loaded by the two input rows it belongs to (the second time from cache); the earlier gather form loaded it
+// ~16 times (7 x 7 candidate window per input pixel) and ran at L1 / L2 speed: 220 us for the 112 x 112 map against ~100 us of
+// HBM time.  Deterministic (fixed order, no atomics).
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int B, int H, int W, int C) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
-  const int idx = blockIdx.x * 256 + threadIdx.x;
-  if (idx >= W * c8) return;
-  const int g = idx % c8, w = idx / c8;
-  const int h = blockIdx.y % H, b = blockIdx.y / H;
-  float wh[7], ww[7];
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)B * H * c8) return;
+  const int g = (int)(idx % c8), h = (int)((idx / c8) % H), b = (int)(idx / ((long long)c8 * H));
+  float wh[7];
   bil_taps(h, H, sh, wh);
-  bil_taps(w, W, sw, ww);
-  float acc[8];
+  const T* base = dy + ((size_t)b * Ho * Wo) * C + g * 8;
+  T* out = dx + (((size_t)b * H + h) * W) * C + g * 8;
+  float a0[8], a1[8];   // accumulators of input columns cur and cur + 1
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  const T* base = dy + (size_t)b * Ho * Wo * C + g * 8;
+  for (int i = 0; i < 8; ++i) a0[i] = a1[i] = 0.f;
+  int cur = 0;
+  for (int ow0 = 0; ow0 < Wo; ow0 += 2) {   // Wo is even
+    Raw8<T> v[2][7];
 #pragma unroll
-  for (int kh = 0; kh < 7; ++kh) {
-    if (wh[kh] == 0.f) continue;
-    const T* rowp = base + (size_t)((2 * h - 3 + kh) * Wo + 2 * w - 3) * C;
+    for (int u = 0; u < 2; ++u)
 #pragma unroll
-    for (int kw = 0; kw < 7; ++kw) {
-      if (ww[kw] == 0.f) continue;
-      Vec8<T> v;
-      v.load(rowp + (size_t)kw * C);
-      const float f = wh[kh] * ww[kw];
+      for (int kh = 0; kh < 7; ++kh)
+        if (wh[kh] != 0.f) v[u][kh].load(base + ((size_t)(2 * h - 3 + kh) * Wo + ow0 + u) * C);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) acc[i] += f * v.v[i];
+    for (int u = 0; u < 2; ++u) {
+      float col[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) col[i] = 0.f;
+#pragma unroll
+      for (int kh = 0; kh < 7; ++kh) {
+        if (wh[kh] != 0.f) {
+          float f[8];
+          v[u][kh].get(f);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) col[i] = fmaf(wh[kh], f[i], col[i]);
+        }
+      }
+      int w0, w1; float l0, l1;
+      bil_src(ow0 + u, W, sw, w0, w1, l0, l1);
+      if (w0 > cur) {   // column `cur` is complete
+        Vec8<T> o;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { o.v[i] = a0[i]; a0[i] = a1[i]; a1[i] = 0.f; }
+        o.store(out + (size_t)cur * C);
+        ++cur;
+      }
+      if (w1 == w0) l0 += l1;   // last input column: both taps are the same element
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        a0[i] = fmaf(l0, col[i], a0[i]);
+        if (w1 != w0) a1[i] = fmaf(l1, col[i], a1[i]);
+      }
     }
   }
   Vec8<T> o;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) o.v[i] = acc[i];
-  o.store(dx + ((size_t)blockIdx.y * W + w) * C + g * 8);
+  for (int i = 0; i < 8; ++i) o.v[i] = a0[i];
+  o.store(out + (size_t)cur * C);
+  if (cur + 1 < W) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o.v[i] = a1[i];
+    o.store(out + (size_t)(cur + 1) * C);
+  }
 }
 template <typename T> int k_bilinear2x_bwd(const T* dy, T* dx, int B, int H, int W, int C, cudaStream_t st) {
-  S4G_CUDA(launch_dep(bilinear2x_bwd_kernel<T>, dim3(dim3(cdiv(W * (C / 8), 256), B * H)), dim3(256), 0, st, dy, dx, B, H, W, C));
+  S4G_CUDA(launch_dep(bilinear2x_bwd_kernel<T>, dim3(cdiv((long long)B * H * (C / 8), 256)), dim3(256), 0, st, dy, dx, B, H, W, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -977,10 +1011,10 @@ int k_bn_eval_prepare(const float* rm, const float* rv, float* mean, float* rstd
 // Block = 256 threads = (C/8) channel groups x (2048/C) row lanes; a thread keeps its 8 channels' constants in
 // registers and walks rows with a 4-deep unroll (4 x 16 B loads in flight per operand).
 template <typename T>
-__global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ mean,
-                                                       const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                                       const float* __restrict__ beta, const T* __restrict__ skip,
-                                                       T* __restrict__ y, int relu, long long M, int C) {
+__global__ void __launch_bounds__(256, 3) bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ mean,
+                                                          const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, const T* __restrict__ skip,
+                                                          T* __restrict__ y, int relu, long long M, int C) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   const int c8 = C / 8, lanes = 256 / c8;
@@ -992,42 +1026,49 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, 
     sc[i] = rstd[c] * gamma[c];
     sh[i] = beta[c] - mean[c] * sc[i];
   }
+  // loads stay packed (Raw8: 4 registers per 16 B for bf16) until they are used, so that three blocks fit on an SM with 4 (+ 4
+  // with a skip operand) loads in flight per thread: the fp32-unpacked version held 2 blocks per SM and ran at 2.3-3.2 TB/s
   const long long stride = (long long)gridDim.x * lanes;
+  const T* px = x + g * 8;
+  const T* ps = skip ? skip + g * 8 : nullptr;
+  T* py = y + g * 8;
   for (long long rb = (long long)blockIdx.x * lanes + rl; rb < M; rb += 4 * stride) {
-    Vec8<T> v[4], sk[4];
+    Raw8<T> v[4], sk[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const long long r = rb + u * stride;
-      if (r < M) {
-        v[u].load(x + r * C + g * 8);
-        if (skip) sk[u].load(skip + r * C + g * 8);
-      }
+      const long long r = min(rb + u * stride, M - 1);
+      v[u].load(px + r * C);
+      if (ps) sk[u].load(ps + r * C);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long r = rb + u * stride;
       if (r < M) {
+        float a[8], b[8];
+        v[u].get(a);
+        if (ps) sk[u].get(b);
+        Vec8<T> o;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float o = fmaf(v[u].v[i], sc[i], sh[i]);
-          if (relu) o = fmaxf(o, 0.f);
-          if (skip) o += sk[u].v[i];
-          v[u].v[i] = o;
+          float t = fmaf(a[i], sc[i], sh[i]);
+          if (relu) t = fmaxf(t, 0.f);
+          if (ps) t += b[i];
+          o.v[i] = t;
         }
-        v[u].store(y + r * C + g * 8);
+        o.store(py + r * C);
       }
     }
   }
 }
-static inline unsigned bn_grid(long long M, int C) {
+static inline unsigned bn_grid(long long M, int C, int per_sm = 8) {
   const int lanes = 256 / (C / 8);
-  return (unsigned)std::min<long long>(cdiv(M, (long long)lanes * 4), 148 * 8);
+  return (unsigned)std::min<long long>(cdiv(M, (long long)lanes * 4), 148 * per_sm);   // grid-stride beyond
 }
 template <typename T>
 int k_bn_apply(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta, const T* skip,
                T* y, int relu, long long M, int C, cudaStream_t st) {
   if (C % 8 || 256 % (C / 8)) { s4g_set_error("bn: unsupported C"); return S4G_ERR_SHAPE; }
-  S4G_CUDA(launch_dep(bn_apply_kernel<T>, dim3(bn_grid(M, C)), dim3(256), 0, st, x, mean, rstd, gamma, beta, skip, y, relu, M, C));
+  S4G_CUDA(launch_dep(bn_apply_kernel<T>, dim3(bn_grid(M, C, 6)), dim3(256), 0, st, x, mean, rstd, gamma, beta, skip, y, relu, M, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1431,9 +1472,15 @@ template <typename T> int k_pack_linear(const float* w, T* wp, T* wt, int N, int
 }
 // All nn.Linear / 1x1-conv weights of the model in ONE launch (the per-layer launches are latency-bound: 58 of them
 // took 0.44 ms for 0.1 ms worth of HBM traffic).  The job table travels in kernel-parameter space.
+__device__ __forceinline__ void store2(bf16* p, float a, float b) { *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b); }
+__device__ __forceinline__ void store2(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+
+// 64 x 64 tiles (PACK_TILE, kernels.h): 16 B loads of the fp32 master weights (a warp reads two 256 B row segments), 8 B stores
+// of the bf16 copy, and the transposed copy written as 128 B row segments -- 680 MB per step move at HBM speed instead of in
+// 64 / 128 B pieces (the 32 x 32 scalar version ran at 2.5 TB/s)
 template <typename T> __global__ void __launch_bounds__(256) pack_linear_grouped_kernel(const __grid_constant__ PackLinearJobs jobs) {
   pdl_trigger();  // the next kernel of the stream, if launched programmatically dependent, may start its prologue now
-  __shared__ float tile[32][33];
+  __shared__ float tile[PACK_TILE][PACK_TILE + 1];
   int lo = 0, hi = jobs.n - 1;
   while (lo < hi) {   // last job whose first tile is <= blockIdx.x
     const int mid = (lo + hi + 1) >> 1;
@@ -1441,25 +1488,42 @@ template <typename T> __global__ void __launch_bounds__(256) pack_linear_grouped
   }
   const PackLinearJob& jb = jobs.job[lo];
   const int t = blockIdx.x - jb.tile0;
-  const int tiles_k = (jb.K + 31) >> 5;
-  const int k0 = (t % tiles_k) * 32, n0 = (t / tiles_k) * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int N = jb.N, K = jb.K;
+  const int tiles_k = (K + PACK_TILE - 1) / PACK_TILE;
+  const int k0 = (t % tiles_k) * PACK_TILE, n0 = (t / tiles_k) * PACK_TILE;
   const float* w = jb.src;
   T* wp = reinterpret_cast<T*>(jb.wp);
   T* wt = reinterpret_cast<T*>(jb.wt);
-  const int N = jb.N, K = jb.K;
-  for (int j = ty; j < 32; j += 8) {
-    const int n = n0 + j, k = k0 + tx;
-    float v = 0.f;
-    if (n < N && k < K) { v = w[(long long)n * K + k]; wp[(long long)n * K + k] = from_f<T>(v); }
-    tile[j][tx] = v;
+  const bool vec_k = (K & 3) == 0;
+  const int c4 = (threadIdx.x & 15) * 4, r0 = threadIdx.x >> 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int j = r0 + 16 * i, n = n0 + j, k = k0 + c4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n < N) {
+      const long long o = (long long)n * K + k;
+      if (vec_k && k + 3 < K) {
+        v = *reinterpret_cast<const float4*>(w + o);
+        store4(wp + o, v);
+      } else {
+        float* f = &v.x;
+        for (int e = 0; e < 4; ++e)
+          if (k + e < K) { f[e] = w[o + e]; wp[o + e] = from_f<T>(f[e]); }
+      }
+    }
+    tile[j][c4] = v.x; tile[j][c4 + 1] = v.y; tile[j][c4 + 2] = v.z; tile[j][c4 + 3] = v.w;
   }
   if (!wt) return;
   __syncthreads();
-  const int n = n0 + tx;
-  for (int j = ty; j < 32; j += 8) {
-    const int kk = k0 + j;
-    if (n < N && kk < K) wt[(long long)kk * N + n] = from_f<T>(tile[tx][j]);
+  const int nl = (threadIdx.x & 31) * 2, n = n0 + nl;
+  const bool vec_n = (N & 1) == 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int j = (threadIdx.x >> 5) + 8 * i, kk = k0 + j;
+    if (kk >= K || n >= N) continue;
+    const long long o = (long long)kk * N + n;
+    if (vec_n) store2(wt + o, tile[nl][j], tile[nl + 1][j]);   // N even and n even: n + 1 < N, 4 B aligned
+    else { wt[o] = from_f<T>(tile[nl][j]); if (n + 1 < N) wt[o + 1] = from_f<T>(tile[nl + 1][j]); }
   }
 }
 template <typename T> int k_pack_linear_grouped(const PackLinearJobs& jobs, int total_tiles, cudaStream_t st) {

@@ -205,15 +205,31 @@ struct Builder {
   }
   std::vector<Conv> conv_jobs;
   // out = conv3x3(in) (+bias) (epilogue mode); pushes forward and backward closures
-  void conv3_layer(const Conv& c, int in, int out, int mode = EPI_NONE, bool in_grad = true) {
+  // stats_into (tcgen05 path, training): offset of a BatchNorm's [2 Co] double accumulator; the conv epilogue then also produces
+  // the per-channel sum / sum of squares of its (bf16-rounded) output, so the BatchNorm that follows needs no statistics pass
+  static bool bn_stats_fused() {
+    static const bool v = [] { const char* e = getenv("S4G_BN_STATS"); return !(e && std::string(e) == "pass"); }();
+    return v;
+  }
+  void conv3_layer(const Conv& c, int in, int out, int mode = EPI_NONE, bool in_grad = true, size_t stats_into = 0) {
     Builder* self = this;
     S4GModel* mm = m;
     const Act ai = m->acts[in];
     note_wgrad(conv3_geom(ai.B, ai.H, ai.W, c.Ci, c.Co));
     m->fwd.push_back([=](cudaStream_t st) {
       const Act& a = mm->acts[in];
+      const ConvGeom g = conv3_geom(a.B, a.H, a.W, c.Ci, c.Co);
       EpiParams e = epi(self->V(out), c.Co, c.b ? c.b->p : nullptr, mode);
-      return self->fprop(conv3_geom(a.B, a.H, a.W, c.Ci, c.Co), self->V(in), mm->template at<T>(c.wf), e, st);
+      if (stats_into && mm->training && self->umma_path() && bn_stats_fused()) {
+        const Reducer r = self->red(self->shared_red, false);
+        const int rows = umma_fprop_stat_rows(g);
+        e.stat_part = reinterpret_cast<float*>(reduce_scratch(&r, sizeof(float) * (size_t)rows * 2 * c.Co));
+        if (!e.stat_part) return (int)S4G_ERR_WORKSPACE;
+        S4G_TRY(self->fprop(g, self->V(in), mm->template at<T>(c.wf), e, st));
+        mm->launches++;
+        return k_finalize(&r, e.stat_part, mm->template at<double>(stats_into), rows, 2 * c.Co, 2 * c.Co, 0, 1, st);
+      }
+      return self->fprop(g, self->V(in), mm->template at<T>(c.wf), e, st);
     });
     bwd->push_back([=](cudaStream_t st) {
       const Act& a = mm->acts[in];
@@ -282,14 +298,15 @@ struct Builder {
   }
   void need_shared_red(size_t bytes) { if (shared_red.bytes < bytes) shared_red = red_alloc(bytes); }
   // statistics of x (forward): fills mean/rstd, updates running stats when training
-  int bn_forward_stats(const BN& n, const T* x, long long M, cudaStream_t st) const {
+  int bn_forward_stats(const BN& n, const T* x, long long M, cudaStream_t st, bool stats_done = false) const {
     float* mean = m->template at<float>(n.mean);
     float* rstd = m->template at<float>(n.rstd);
     if (!m->training) { m->launches++; return k_bn_eval_prepare(n.rm->p, n.rv->p, mean, rstd, 1e-5f, 256, st); }
     double* stats = m->template at<double>(n.stats);
-    m->launches += 3;
+    m->launches += stats_done ? 1 : 3;
     const Reducer r = red(shared_red, false);
-    S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st, &r));
+    // stats_done: the producing conv's epilogue already left sum / sum of squares in `stats` (conv3_layer, stats_into)
+    if (!stats_done) S4G_TRY(k_bn_stats<T>(x, stats, M, 256, st, &r));
     if (m->d.world_size > 1) S4G_TRY(m->exchange(stats, 512, st));
     return k_bn_finalize(stats, (double)M * m->d.world_size, mean, rstd, n.rm->p, n.rv->p,
                          reinterpret_cast<long long*>(n.nbt->p), 0.1f, 1e-5f, 256, st);
@@ -324,10 +341,11 @@ struct Builder {
       mm->launches++;
       return k_relu_bwd_add<T>(self->G(r), self->V(x), self->G(out), self->G(x), n, st);
     });
-    conv3_layer(k1, r, c1);
+    const bool fuse_stats = use_bn && umma_path() && bn_stats_fused();
+    conv3_layer(k1, r, c1, EPI_NONE, true, fuse_stats ? b1.stats : 0);
     if (use_bn) {
       m->fwd.push_back([=](cudaStream_t st) {
-        S4G_TRY(self->bn_forward_stats(b1, self->V(c1), M, st));
+        S4G_TRY(self->bn_forward_stats(b1, self->V(c1), M, st, fuse_stats));
         mm->launches++;
         return k_bn_apply<T>(self->V(c1), mm->template at<float>(b1.mean), mm->template at<float>(b1.rstd), b1.w->p, b1.b->p,
                              nullptr, self->V(r2), 1, M, 256, st);
@@ -340,10 +358,10 @@ struct Builder {
         return k_relu_bwd_add<T>(self->G(r2), self->V(c1), nullptr, self->G(c1), n, st);
       });
     }
-    conv3_layer(k2, r2, c2);
+    conv3_layer(k2, r2, c2, EPI_NONE, true, fuse_stats ? b2.stats : 0);
     if (use_bn) {
       m->fwd.push_back([=](cudaStream_t st) {
-        S4G_TRY(self->bn_forward_stats(b2, self->V(c2), M, st));
+        S4G_TRY(self->bn_forward_stats(b2, self->V(c2), M, st, fuse_stats));
         mm->launches++;
         return k_bn_apply<T>(self->V(c2), mm->template at<float>(b2.mean), mm->template at<float>(b2.rstd), b2.w->p, b2.b->p,
                              self->V(x), self->V(out), 0, M, 256, st);
@@ -641,12 +659,13 @@ struct Builder {
     head_dsmall = alloc(sizeof(float) * M1);
     if (seg) {
       const int c = act(B, 112, 112, 256);
-      conv3_layer(conv3(d + "output_conv.0", 256, 256), p1, c);
       BN n = bn(d + "output_conv.1");
+      const bool fuse_stats = umma_path() && bn_stats_fused();
+      conv3_layer(conv3(d + "output_conv.0", 256, 256), p1, c, EPI_NONE, true, fuse_stats ? n.stats : 0);
       Param* w4 = P(d + "output_conv.4.weight");
       Param* b4 = P(d + "output_conv.4.bias");
       m->fwd.push_back([=](cudaStream_t st) {
-        S4G_TRY(self->bn_forward_stats(n, self->V(c), M1, st));
+        S4G_TRY(self->bn_forward_stats(n, self->V(c), M1, st, fuse_stats));
         mm->launches += 2;
         float* small = mm->template at<float>(self->head_small);
         S4G_TRY(k_seghead_fwd<T>(self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p, b4->p,
@@ -1084,7 +1103,7 @@ struct Builder {
             PackLinearJob& j = jobs.job[n++];
             j.src = l.w->p; j.wp = mm->template at<T>(l.wf); j.wt = l.wd ? (void*)mm->template at<T>(l.wd) : nullptr;
             j.N = l.N; j.K = l.K; j.tile0 = tiles; j.pad = 0;
-            tiles += cdiv(l.N, 32) * cdiv(l.K, 32);
+            tiles += cdiv(l.N, PACK_TILE) * cdiv(l.K, PACK_TILE);
           }
           jobs.n = n;
           mm->launches++;

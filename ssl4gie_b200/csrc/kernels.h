@@ -46,6 +46,7 @@ template <typename T> int simt_conv_wgrad(const ConvGeom& g, const T* dY, const 
 
 // ---- tcgen05 contractions (bf16 in, fp32 accumulate in TMEM): umma.cu
 int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiParams& e, cudaStream_t st);
+int umma_fprop_stat_rows(const ConvGeom& g);   // rows of EpiParams::stat_part that call writes (its grid size)
 // dW layout: packed [Cout][tap][Cin] (torch_layout = 0) or torch's [Cout][Cin][R][S] (torch_layout = 1)
 int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW, float* scratch, size_t scratch_bytes,
                     cudaStream_t st, int torch_layout = 0);
@@ -104,6 +105,7 @@ template <typename T>
 int k_cls_head_bwd(const float* dout, const float* pooled, const float* W, float* dW, float* db, T* dhn, int B, int N,
                    int C, int spatial, cudaStream_t st);
 // grouped weight packing: every job is one [N, K] fp32 weight -> bf16/fp32 copy wp [N, K] and (optional) transpose wt [K, N]
+constexpr int PACK_TILE = 64;   // k_pack_linear_grouped works in PACK_TILE x PACK_TILE tiles: tile0 counts those
 struct PackLinearJob { const float* src; void* wp; void* wt; int N, K, tile0, pad; };
 struct PackLinearJobs { PackLinearJob job[80]; int n; };
 template <typename T> int k_pack_linear_grouped(const PackLinearJobs& jobs, int total_tiles, cudaStream_t st);

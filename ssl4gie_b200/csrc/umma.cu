@@ -232,7 +232,7 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
 // CG = 1: one CTA per 128 x N tile.  CG = 2: a CTA pair (cluster of 2, one TPC) computes a 256 x N tile with
 // tcgen05.mma.cta_group::2 -- each CTA stages its own 128 rows of A and HALF of the B tile, so the L2 -> smem operand
 // traffic per FLOP drops by a third and the smaller stages give a deeper ring for the same shared memory.
-template <int CG>
+template <int CG, int STATS = 0>
 __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                     const __grid_constant__ CUtensorMap tmB,
                                                                     const __grid_constant__ CUtensorMap tmO,
@@ -355,6 +355,7 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
     const int r = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
     const TileGeom& t = p.tg;
+    float st_acc[STATS ? 8 : 1] = {};   // [slab of this warp (2)][sum col 2l, sum col 2l+1, sumsq col 2l, sumsq col 2l+1]
     for (int k = 0;; ++k) {
       const int tile = sched.take(k);
       __syncwarp();
@@ -482,6 +483,23 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
                 tma_store_commit();
               }
             }
+            if (STATS) {
+              // column sums of the staged bf16 slab (32 rows x 64 columns): lane l owns columns 2l, 2l + 1 -- conflict-free 4-byte
+              // reads of the swizzled rows; rows outside the tensor are skipped
+              const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+              float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+              for (int rr = 0; rr < 32; ++rr) {
+                if ((vmask >> rr) & 1) {
+                  const uint32_t w = *reinterpret_cast<const uint32_t*>(buf + rr * 128 + (((lane >> 2) ^ (rr & 7)) << 4) + (lane & 3) * 4);
+                  const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xffff0000u);
+                  s0 += a; s1 += b;
+                  q0 = fmaf(a, a, q0); q1 = fmaf(b, b, q1);
+                }
+              }
+              if (((sl - half) >> 1) == 0) { st_acc[0] += s0; st_acc[1] += s1; st_acc[2] += q0; st_acc[3] += q1; }
+              else { st_acc[4] += s0; st_acc[5] += s1; st_acc[6] += q0; st_acc[7] += q1; }
+            }
           }
         }
       } else if (p.f32_epi) {
@@ -554,10 +572,30 @@ __global__ void __launch_bounds__(FPROP_THREADS, 1) umma_fprop_kernel(const __gr
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (p.tma_epi && lane == 0) tma_store_wait_all();
+    if (STATS) {
+      // park this warp's sums in its (now idle) staging slab: [8 values][32 lanes]; combined across the warps below
+      __syncwarp();
+      float* mine = reinterpret_cast<float*>(epi_smem + (warp - 2) * EPI_WARP_BYTES);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mine[k * 32 + lane] = st_acc[k];
+    }
   }
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();   // the peer may still signal this CTA's barriers until here
   if (warp == 1) { if (CG == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
+  if (STATS) {
+    // one row [2 N] per CTA: column c lives in slab c / 64, owned by the four warps (row quarters 0..3) of half (c / 64) & 1;
+    // fixed summation order => deterministic
+    float* row = p.e.stat_part + (size_t)blockIdx.x * 2 * p.N;
+    for (int i = threadIdx.x; i < 2 * p.N; i += blockDim.x) {
+      const int sq = i >= p.N, c = sq ? i - p.N : i;
+      const int sl = c >> 6, hf = sl & 1, j = sl >> 1, ln = (c & 63) >> 1, k = j * 4 + sq * 2 + (c & 1);
+      float tsum = 0.f;
+#pragma unroll
+      for (int qq = 0; qq < 4; ++qq) tsum += reinterpret_cast<const float*>(epi_smem + (hf * 4 + qq) * EPI_WARP_BYTES)[k * 32 + ln];
+      row[i] = tsum;
+    }
+  }
   if (threadIdx.x == 0 && rank == 0) sched.finish();
 }
 
@@ -772,17 +810,31 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReducePara
   const size_t tile_elems = (size_t)128 * p.block_n;
   const size_t split_stride = (size_t)p.taps * p.tiles_ci * p.tiles_co * tile_elems;
   const float* base = p.part + (((size_t)tap * p.tiles_ci + tci) * p.tiles_co + tco) * tile_elems + (co0 & 127) + tx;
+  // the four columns of a thread advance together through the splits: 4 (x 2 splits) independent loads per trip
+  float acc4[4] = {0.f, 0.f, 0.f, 0.f};
+  const float* src4[4];
+  bool ok[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const int cil = ty + j * 8;                       // ci within this 32-block
     const int col = ci0 - tci * p.block_n + cil;      // column inside the tile
-    float acc = 0.f;
-    if (ci0 + cil < p.Cin) {
-      const float* src = base + (size_t)col * 128;
-      for (int s = 0; s < p.splits; ++s) acc += src[(size_t)s * split_stride];
-    }
-    tile[cil][tx] = acc;
+    ok[j] = ci0 + cil < p.Cin;
+    src4[j] = base + (size_t)(ok[j] ? col : 0) * 128;
   }
+  int s = 0;
+  for (; s + 2 <= p.splits; s += 2) {
+    float v0[4], v1[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { v0[j] = src4[j][(size_t)s * split_stride]; v1[j] = src4[j][(size_t)(s + 1) * split_stride]; }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { acc4[j] += v0[j]; acc4[j] += v1[j]; }
+  }
+  if (s < p.splits) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc4[j] += src4[j][(size_t)s * split_stride];
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) tile[ty + j * 8][tx] = ok[j] ? acc4[j] : 0.f;
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -809,11 +861,30 @@ __global__ void __launch_bounds__(256) wgrad_reduce_linear_kernel(const WgradRed
   float acc[16];
 #pragma unroll
   for (int it = 0; it < 16; ++it) acc[it] = 0.f;
-  for (int s = 0; s < p.splits; ++s) {
+  // four splits per trip: 64 independent loads in flight per thread (with one split per trip the loop ran at one memory
+  // latency per split: 108 us for the 74 splits of the 112 x 112 out_conv); the summation order stays s = 0, 1, 2, ...
+  int s = 0;
+  for (; s + 4 <= p.splits; s += 4) {
+    float v[4][16];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const float* src = base + (size_t)(s + u) * split_stride;
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        const int item = it * 8 + warp;            // 128 items = 32 columns x 4 groups of 32 rows
+        v[u][it] = src[(item >> 2) * 128 + (item & 3) * 32 + lane];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int it = 0; it < 16; ++it) acc[it] += v[u][it];
+  }
+  for (; s < p.splits; ++s) {
     const float* src = base + (size_t)s * split_stride;
 #pragma unroll
     for (int it = 0; it < 16; ++it) {
-      const int item = it * 8 + warp;            // 128 items = 32 columns x 4 groups of 32 rows
+      const int item = it * 8 + warp;
       acc[it] += src[(item >> 2) * 128 + (item & 3) * 32 + lane];
     }
   }
@@ -971,9 +1042,25 @@ int umma_init() {
   if (const char* lim = getenv("S4G_SM_LIMIT")) { const int v = atoi(lim); if (v >= 2 && v < g_num_sms) g_num_sms = v & ~1; }
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  S4G_CUDA(cudaFuncSetAttribute(umma_fprop_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   S4G_CUDA(cudaFuncSetAttribute(umma_wgrad_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   return 0;
+}
+
+// number of partial rows umma_conv_fprop writes into EpiParams::stat_part for this geometry (= its grid size)
+int umma_fprop_stat_rows(const ConvGeom& g) {
+  if (umma_init() != 0) return 0;
+  const bool matrix = g.Hi == 1 && g.Wi == 1;
+  const TileGeom tg = matrix ? matrix_tiles(g.Nimg, 128) : make_tiles(g.Nimg, g.Hi, g.Wi, 128);
+  const int row_tiles = tg.tw * tg.th * tg.tn;
+  static const int forced_cg = getenv("S4G_FPROP_CG") ? atoi(getenv("S4G_FPROP_CG")) : 0;
+  int cg = forced_cg ? forced_cg : (row_tiles >= 2 ? 2 : 1);
+  const int block_n = pick_block_n(g.Cout, row_tiles, cg);
+  if (block_n % 32) cg = 1;
+  const int tiles = cdiv(row_tiles, cg) * cdiv(g.Cout, block_n);
+  return cg == 2 ? 2 * std::min(tiles, g_num_sms / 2) : std::min(tiles, g_num_sms);
 }
 
 int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiParams& e, cudaStream_t st) {
@@ -1016,6 +1103,10 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
               (e.mode == EPI_NONE || e.mode == EPI_RELU) && e.ldo % 4 == 0 && (!e.res || e.ldr % 4 == 0) && g.Cout % 4 == 0 &&
               (reinterpret_cast<uintptr_t>(e.out) & 15) == 0 && (reinterpret_cast<uintptr_t>(e.res) & 15) == 0 &&
               (!e.bias || (reinterpret_cast<uintptr_t>(e.bias) & 15) == 0);
+  if (e.stat_part && (!p.tma_epi || p.tiles_n != 1 || g.Cout > 256 || g.Cout % 64 || e.out2 || e.mode != EPI_NONE)) {
+    s4g_set_error("umma_conv_fprop: fused column statistics need the bf16 TMA-store epilogue, one column tile and Cout a multiple of 64 (<= 256)");
+    return S4G_ERR_SHAPE;
+  }
   if (e.dot_aux && (!p.tma_epi || p.block_n % 64 || !matrix || e.out2)) {
     s4g_set_error("umma_conv_fprop: the fused row-dot needs the bf16 TMA-store epilogue of a plain matrix with 64-column slabs");
     return S4G_ERR_SHAPE;
@@ -1038,7 +1129,8 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = g_pdl ? 2 : 1;
-    S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<2>, tmA, tmB, tmO, tmO2, p));
+    if (e.stat_part) S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<2, 1>, tmA, tmB, tmO, tmO2, p));
+    else S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<2>, tmA, tmB, tmO, tmO2, p));
   } else {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(std::min(p.tiles_m * p.tiles_n, g_num_sms));
@@ -1049,7 +1141,8 @@ int umma_conv_fprop(const ConvGeom& g, const bf16* X, const bf16* W, const EpiPa
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = g_pdl ? 1 : 0;
-    S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<1>, tmA, tmB, tmO, tmO2, p));
+    if (e.stat_part) S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<1, 1>, tmA, tmB, tmO, tmO2, p));
+    else S4G_CUDA(cudaLaunchKernelEx(&cfg, umma_fprop_kernel<1>, tmA, tmB, tmO, tmO2, p));
   }
   S4G_KERNEL_CHECK();
   return 0;
