@@ -7,4 +7,4 @@ timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-extras 
 python -c "
 import json; d=json.loads(open('gpurun_out/bench_ew_$v.json').read().strip().splitlines()[-1]); print('run $v', round(d['ms_per_step'],3), 'ms', round(d['value']), 'img/s', d['loss'], d['gpu_launches'])"
 done
-timeout 300 python scripts/bench_shapes.py 64 2>&1 | grep -E "out_conv|TOTAL|layer1_rn wgrad|post1x1_96 wgrad"
+

@@ -649,43 +649,51 @@ __device__ __forceinline__ void bil_src(int o, int in_size, float scale, int& i0
   l1 = s - i0;
   l0 = 1.f - l1;
 }
-// grid.y = group of 4 output rows (b * Ho/4 + oh/4), grid.x * 256 threads cover (ow, channel group): 32-bit index math,
-// 16 independent 16 B loads in flight per thread
+// A thread owns (b, output row oh, 8 channels) and walks the output columns: the two source rows are blended once per SOURCE column
+// (c(w) = lh0 x[h0, w] + lh1 x[h1, w]) and every output column is lw0 c(w0) + lw1 c(w0 + 1); w0 never decreases, so each x element
+// is loaded once per output row (2 loads per 2 output columns instead of 8) and the kernel is bound by its 16 B stores.
 template <typename T> __global__ void __launch_bounds__(256) bilinear2x_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int H, int W, int C) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   const int c8 = C / 8, Ho = 2 * H, Wo = 2 * W;
   const float sh = (float)(H - 1) / (float)(Ho - 1), sw = (float)(W - 1) / (float)(Wo - 1);
-  const int idx = blockIdx.x * 256 + threadIdx.x;
-  if (idx >= Wo * c8) return;
-  const int g = idx % c8, ow = idx / c8;
-  const int hq = (Ho + 3) / 4;   // the last group of an Ho that is not a multiple of 4 is cut by the guard below
-  const int oh0 = (blockIdx.y % hq) * 4, b = blockIdx.y / hq;
-  int w0, w1; float lw0, lw1;
-  bil_src(ow, W, sw, w0, w1, lw0, lw1);
-  const T* base = x + (size_t)b * H * W * C + g * 8;
-  Raw8<T> v[4][4];
-  float lh[4][2];
+  const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (long long)B * Ho * c8) return;
+  const int g = (int)(idx % c8), oh = (int)((idx / c8) % Ho), b = (int)(idx / ((long long)c8 * Ho));
+  int h0, h1; float lh0, lh1;
+  bil_src(oh, H, sh, h0, h1, lh0, lh1);
+  const T* r0 = x + (((size_t)b * H + h0) * W) * C + g * 8;
+  const T* r1 = x + (((size_t)b * H + h1) * W) * C + g * 8;
+  T* out = y + (((size_t)b * Ho + oh) * Wo) * C + g * 8;
+  auto column = [&](int w, float (&c)[8]) {
+    Raw8<T> a, bq;
+    a.load(r0 + (size_t)w * C); bq.load(r1 + (size_t)w * C);
+    float fa[8], fb[8];
+    a.get(fa); bq.get(fb);
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    int h0, h1;
-    bil_src(min(oh0 + r, Ho - 1), H, sh, h0, h1, lh[r][0], lh[r][1]);
-    v[r][0].load(base + (size_t)(h0 * W + w0) * C); v[r][1].load(base + (size_t)(h0 * W + w1) * C);
-    v[r][2].load(base + (size_t)(h1 * W + w0) * C); v[r][3].load(base + (size_t)(h1 * W + w1) * C);
-  }
+    for (int i = 0; i < 8; ++i) c[i] = lh0 * fa[i] + lh1 * fb[i];
+  };
+  float c0[8], c1[8];
+  column(0, c0);
+  column(min(1, W - 1), c1);
+  int cur = 0;
+  for (int ow = 0; ow < Wo; ++ow) {
+    int w0, w1; float lw0, lw1;
+    bil_src(ow, W, sw, w0, w1, lw0, lw1);
+    if (w0 > cur) {
+      ++cur;
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    if (oh0 + r >= Ho) break;
-    float a[8], bq[8], c[8], d[8];
-    v[r][0].get(a); v[r][1].get(bq); v[r][2].get(c); v[r][3].get(d);
+      for (int i = 0; i < 8; ++i) c0[i] = c1[i];
+      column(min(cur + 1, W - 1), c1);
+    }
     Vec8<T> o;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o.v[i] = lh[r][0] * (lw0 * a[i] + lw1 * bq[i]) + lh[r][1] * (lw0 * c[i] + lw1 * d[i]);
-    o.store(y + (((size_t)b * Ho + oh0 + r) * Wo + ow) * C + g * 8);
+    for (int i = 0; i < 8; ++i) o.v[i] = lw0 * c0[i] + lw1 * (w1 == w0 ? c0[i] : c1[i]);
+    o.store(out + (size_t)ow * C);
   }
 }
 template <typename T> int k_bilinear2x_fwd(const T* x, T* y, int B, int H, int W, int C, cudaStream_t st) {
-  S4G_CUDA(launch_dep(bilinear2x_fwd_kernel<T>, dim3(dim3(cdiv(2 * W * (C / 8), 256), B * cdiv(2 * H, 4))), dim3(256), 0, st, x, y, B, H, W, C));
+  S4G_CUDA(launch_dep(bilinear2x_fwd_kernel<T>, dim3(cdiv((long long)B * 2 * H * (C / 8), 256)), dim3(256), 0, st, x, y, B, H, W, C));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1176,7 +1184,7 @@ __device__ __forceinline__ void drop_scale8(const uint8_t* mask, float p, uint64
   }
 }
 template <typename T>
-__global__ void __launch_bounds__(256, 2) seghead_fwd_kernel(const T* __restrict__ x, const float* __restrict__ mean,
+__global__ void __launch_bounds__(256, 3) seghead_fwd_kernel(const T* __restrict__ x, const float* __restrict__ mean,
                                                              const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                              const float* __restrict__ beta, const float* __restrict__ w,
                                                              const float* __restrict__ b, const uint8_t* __restrict__ mask,
@@ -1193,12 +1201,12 @@ __global__ void __launch_bounds__(256, 2) seghead_fwd_kernel(const T* __restrict
   const float b0 = b[0];
   const long long stride = (long long)gridDim.x * 8;
   const T* px = x + lane * 8;
-  for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 8 * stride) {
-    Raw8<T> v[8];
+  for (long long rb = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); rb < M; rb += 4 * stride) {
+    Raw8<T> v[4];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) v[u].load(px + min(rb + u * stride, M - 1) * 256);
+    for (int u = 0; u < 4; ++u) v[u].load(px + min(rb + u * stride, M - 1) * 256);
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+    for (int u = 0; u < 4; ++u) {
       const long long row = rb + u * stride;
       if (row < M) {
         float k[8], f[8];
@@ -1307,7 +1315,7 @@ int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, con
   return k_finalize_flush(&q, st);
 }
 template <typename T>
-__global__ void __launch_bounds__(256, 2) seghead_bwd_apply_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
+__global__ void __launch_bounds__(256, 3) seghead_bwd_apply_kernel(const float* __restrict__ dsmall, const T* __restrict__ x,
                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                    const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                    const float* __restrict__ w, const uint8_t* __restrict__ mask,
