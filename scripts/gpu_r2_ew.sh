@@ -8,3 +8,4 @@ python -c "
 import json; d=json.loads(open('gpurun_out/bench_ew_$v.json').read().strip().splitlines()[-1]); print('run $v', round(d['ms_per_step'],3), 'ms', round(d['value']), 'img/s', d['loss'], d['gpu_launches'])"
 done
 
+timeout 300 python scripts/bench_shapes.py 64 2>&1 | grep -E "out_conv(14|28|56) wgrad|proj wgrad|TOTAL"

@@ -799,6 +799,8 @@ struct WgradReduceParams {
   float* dW;
   int Cout, Cin, taps, tiles_co, tiles_ci, block_n, splits;
   long long so, si, st;
+  int groups;     // linear form: the split range is cut into `groups` parts (gridDim.y), combined in a second stage (see the kernel)
+  int* tickets;   // one arrival counter per blockIdx.x (zero between launches)
 };
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgradReduceParams p) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
@@ -851,23 +853,28 @@ __global__ void __launch_bounds__(256) wgrad_reduce_linear_kernel(const WgradRed
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
   __shared__ float tile[32][129];
+  __shared__ int is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int subs = p.block_n >> 5;
   const int t = blockIdx.x / subs, sub = blockIdx.x % subs;
   const int tco = t % p.tiles_co, tci = t / p.tiles_co;
   const size_t tile_elems = (size_t)128 * p.block_n;
   const size_t split_stride = (size_t)p.tiles_ci * p.tiles_co * tile_elems;
-  const float* base = p.part + ((size_t)tci * p.tiles_co + tco) * tile_elems + (size_t)sub * 32 * 128;
+  float* base = const_cast<float*>(p.part) + ((size_t)tci * p.tiles_co + tco) * tile_elems + (size_t)sub * 32 * 128;
+  // A layer with few output tiles is split many ways (the 56 x 56 out_conv: 74 splits of ONE 256 x 256 tile), and 16 blocks
+  // walking 74 splits each are bound by memory latency (104 us for 19 MB).  The split range is therefore cut into gridDim.y
+  // groups: every block sums its group (in split order) and leaves the sum in the slot of the group's first split; the block
+  // that arrives last (ticket counter, integer) adds the group sums in group order.  Fixed partition and order: deterministic.
+  const int G = p.groups, per = (p.splits + G - 1) / G;
+  const int s_begin = blockIdx.y * per, s_end = min(p.splits, s_begin + per);
   float acc[16];
 #pragma unroll
   for (int it = 0; it < 16; ++it) acc[it] = 0.f;
-  // four splits per trip: 64 independent loads in flight per thread (with one split per trip the loop ran at one memory
-  // latency per split: 108 us for the 74 splits of the 112 x 112 out_conv); the summation order stays s = 0, 1, 2, ...
-  int s = 0;
-  for (; s + 4 <= p.splits; s += 4) {
-    float v[4][16];
+  int s = s_begin;
+  for (; s + 2 <= s_end; s += 2) {   // two splits per trip: 32 independent loads in flight per thread
+    float v[2][16];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 2; ++u) {
       const float* src = base + (size_t)(s + u) * split_stride;
 #pragma unroll
       for (int it = 0; it < 16; ++it) {
@@ -876,16 +883,46 @@ __global__ void __launch_bounds__(256) wgrad_reduce_linear_kernel(const WgradRed
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 2; ++u)
 #pragma unroll
       for (int it = 0; it < 16; ++it) acc[it] += v[u][it];
   }
-  for (; s < p.splits; ++s) {
+  if (s < s_end) {
     const float* src = base + (size_t)s * split_stride;
 #pragma unroll
     for (int it = 0; it < 16; ++it) {
       const int item = it * 8 + warp;
       acc[it] += src[(item >> 2) * 128 + (item & 3) * 32 + lane];
+    }
+  }
+  if (G > 1) {
+    if (s_begin < p.splits) {
+      float* dst = base + (size_t)s_begin * split_stride;   // only this block reads or writes the slots of its group
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        const int item = it * 8 + warp;
+        dst[(item >> 2) * 128 + (item & 3) * 32 + lane] = acc[it];
+      }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const int ticket = atomicAdd(p.tickets + blockIdx.x, 1);
+      is_last = ticket == G - 1;
+      if (is_last) p.tickets[blockIdx.x] = 0;   // ready for the next launch
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+#pragma unroll
+    for (int it = 0; it < 16; ++it) acc[it] = 0.f;
+    for (int g = 0; g * per < p.splits; ++g) {
+      const float* src = base + (size_t)(g * per) * split_stride;
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        const int item = it * 8 + warp;
+        acc[it] += __ldcg(src + (item >> 2) * 128 + (item & 3) * 32 + lane);
+      }
     }
   }
 #pragma unroll
@@ -917,6 +954,8 @@ int g_num_sms = 148;
 constexpr int TILE_COUNTER_RING = 256;
 constexpr int MAX_DEV = 64;
 int* g_tile_counters[MAX_DEV] = {};
+constexpr int REDUCE_TICKETS = 1024;   // arrival counters of the two-level split-K reduce (wgrad_reduce_linear_kernel), zero at rest
+int* g_reduce_tickets[MAX_DEV] = {};
 unsigned g_tile_counter_next = 0;
 int g_dyn_tiles = 0;
 int* next_tile_counter() {
@@ -1037,6 +1076,10 @@ int umma_init() {
   if (dev >= 0 && dev < MAX_DEV && !g_tile_counters[dev]) {
     S4G_CUDA(cudaMalloc(&g_tile_counters[dev], sizeof(int) * 2 * TILE_COUNTER_RING));
     S4G_CUDA(cudaMemset(g_tile_counters[dev], 0, sizeof(int) * 2 * TILE_COUNTER_RING));
+  }
+  if (dev >= 0 && dev < MAX_DEV && !g_reduce_tickets[dev]) {
+    S4G_CUDA(cudaMalloc(&g_reduce_tickets[dev], sizeof(int) * REDUCE_TICKETS));
+    S4G_CUDA(cudaMemset(g_reduce_tickets[dev], 0, sizeof(int) * REDUCE_TICKETS));
   }
   // S4G_SM_LIMIT: persistent grids leave SMs free for a concurrently running collective (experiment knob)
   if (const char* lim = getenv("S4G_SM_LIMIT")) { const int v = atoi(lim); if (v >= 2 && v < g_num_sms) g_num_sms = v & ~1; }
@@ -1273,8 +1316,15 @@ int umma_conv_wgrad(const ConvGeom& g, const bf16* dY, const bf16* X, float* dW,
   r.splits = p.splits;
   if (torch_layout) { r.so = (long long)g.Cin * p.taps; r.si = p.taps; r.st = 1; }   // [Cout][Cin][R][S]
   else { r.so = p.K; r.si = 1; r.st = g.Cin; }                                        // packed [Cout][tap][Cin]
-  if (p.taps == 1 && r.si == 1)
-    S4G_CUDA(launch_dep(wgrad_reduce_linear_kernel, dim3(r.tiles_co * r.tiles_ci * (r.block_n / 32)), dim3(256), 0, st, r));
+  if (p.taps == 1 && r.si == 1) {
+    const int bx = r.tiles_co * r.tiles_ci * (r.block_n / 32);
+    // enough blocks to cover the memory latency: ~4 splits per block once a layer is split more than 8 ways
+    int dev = 0;
+    S4G_CUDA(cudaGetDevice(&dev));
+    r.tickets = (dev >= 0 && dev < MAX_DEV) ? g_reduce_tickets[dev] : nullptr;
+    r.groups = (r.splits > 8 && bx <= REDUCE_TICKETS && r.tickets) ? std::min(16, cdiv(r.splits, 4)) : 1;
+    S4G_CUDA(launch_dep(wgrad_reduce_linear_kernel, dim3(bx, r.groups), dim3(256), 0, st, r));
+  }
   else
     S4G_CUDA(launch_dep(wgrad_reduce_kernel, dim3(dim3(cdiv(g.Cout, 32), cdiv(g.Cin, 32), p.taps)), dim3(dim3(32, 8)), 0, st, r));
   S4G_KERNEL_CHECK();
