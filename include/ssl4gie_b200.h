@@ -87,6 +87,9 @@ int s4g_model_forward(S4GModel* m, const float* images, float* out, int training
  * (Models/mae/models_mae.py:132; smallest 49 per image are kept); mask_out [B,196] float (0 keep, 1 remove, :141-145) and
  * ids_restore_out [B,196] int32 (:136) are optional.  The pointers are read / written by every later forward. */
 int s4g_model_set_mae_io(S4GModel* m, const float* noise, float* mask_out, int* ids_restore_out);
+/* CUDA-graph support: read the seg head's dropout seed (Models/DPT_decoder.py:494) from device memory instead of the by-value
+ * `seed` of s4g_model_forward, which a captured graph would replay unchanged.  NULL restores the by-value seed. */
+int s4g_model_set_seed_device(S4GModel* m, const unsigned long long* seed_dev);
 /* dout: gradient w.r.t. `out`.  Writes (overwrites) the gradient of every bound parameter that has one. */
 int s4g_model_backward(S4GModel* m, const float* dout, void* stream);
 /* Cross-rank sum used by SyncBatchNorm statistics (forward: sum/sumsq, backward: sum dy / sum dy*xhat).  Called
@@ -196,6 +199,17 @@ int s4g_mae_loss_bwd(const float* pred, const float* images, const float* mask, 
 int s4g_ce_fwd(const float* logits, const long long* labels, const float* class_weight, float* loss, float* dlogits_unit,
                int B, int num_classes, void* stream);
 int s4g_ce_bwd(const float* dlogits_unit, const float* grad_out, float* dlogits, int B, int num_classes, void* stream);
+
+/* The same step with its scalars in device memory, for capture in a CUDA graph (train_segmentation.py:204 + the per-iteration LR
+ * of Models/mae/engine_pretrain.py:42-43): hyper_dev[8] = {lr, beta1, beta2, eps, weight_decay, grad_scale, -, -} is written by
+ * s4g_device_hyper_set (a 1-thread kernel with by-value arguments: stream-ordered, no host buffer to race with); step_dev counts
+ * completed steps (the kernel applies step_dev + 1) and is advanced, together with an optional dropout seed, by
+ * s4g_device_counter_advance.  weight_decay_per_slot as in s4g_adamw_step_groups, or NULL. */
+int s4g_adamw_step_device(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n,
+                          const float* hyper_dev, const int* step_dev, const float* weight_decay_per_slot, void* stream);
+int s4g_device_hyper_set(float* hyper_dev, float lr, float beta1, float beta2, float eps, float weight_decay,
+                         float grad_scale, void* stream);
+int s4g_device_counter_advance(int* step_dev, unsigned long long* seed_dev, void* stream);
 
 /* ---- GPU-side input pipeline: the per-sample Pillow / torchvision work of the reference's DataLoader workers
  * (Binary_segmentation/Data/dataset.py:34-64, Data/dataloaders.py:62-76) on a batch of decoded 8-bit images.  Every entry

@@ -34,6 +34,7 @@ SIGNATURES = {
     "s4g_model_forward": (_i, [_vp, _vp, _vp, _i, _u64, _vp, _vp]),
     "s4g_model_backward": (_i, [_vp, _vp, _vp]),
     "s4g_model_set_mae_io": (_i, [_vp, _vp, _vp, _vp]),
+    "s4g_model_set_seed_device": (_i, [_vp, _vp]),
     "s4g_model_set_allreduce": (_i, [_vp, ALLREDUCE_FN, _vp]),
     "s4g_peer_mailbox_bytes": (_sz, []),
     "s4g_peer_alloc": (_i, [_sz, ctypes.POINTER(_vp), ctypes.c_char_p]),
@@ -73,6 +74,9 @@ SIGNATURES = {
     "s4g_aug_blur_normalize": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "s4g_aug_mask_to_tensor": (_i, [_vp, _vp, _i, _i, _vp]),
     "s4g_aug_geometric": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp]),
+    "s4g_adamw_step_device": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _vp, _vp, _vp]),
+    "s4g_device_hyper_set": (_i, [_vp, _f, _f, _f, _f, _f, _f, _vp]),
+    "s4g_device_counter_advance": (_i, [_vp, _vp, _vp]),
     "s4g_adamw_step_groups": (_i, [_vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _vp, _i, _f, _vp]),
     "s4g_mae_loss_scratch_bytes": (_sz, [_i]),
     "s4g_mae_loss_fwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),

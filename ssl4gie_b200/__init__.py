@@ -8,6 +8,7 @@ every compute call raises if libssl4gie_b200.so is missing or the device is not 
 from . import utils  # noqa: F401
 from .augment import GpuInputPipeline  # noqa: F401
 from .dpt_decoder import DPT_decoder  # noqa: F401
+from .graph import GraphedStep  # noqa: F401
 from .losses import CrossEntropyLoss, ScaleAndShiftInvariantLoss, SoftDiceLoss  # noqa: F401
 from .mae import MaskedAutoencoderViT, add_weight_decay, adjust_learning_rate, mae_vit_base_patch16  # noqa: F401
 from .models import ViT_from_MAE, ViT_from_MoCoV3, VisionTransformer_from_Any  # noqa: F401

@@ -226,4 +226,17 @@ int s4g_aug_geometric(const float* x, const float* y, float* xo, float* yo, cons
   return k_aug_geometric(x, y, xo, yo, params, fill_x, fill_y, B, ST(stream));
 }
 
+int s4g_adamw_step_device(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, const float* hyper_dev,
+                          const int* step_dev, const float* weight_decay_per_slot, void* stream) {
+  if (!params || !grads || !exp_avg || !exp_avg_sq || !hyper_dev || !step_dev) { s4g_set_error("adamw_step_device: null argument"); return S4G_ERR_STATE; }
+  return k_adamw_dev(params, grads, exp_avg, exp_avg_sq, n, hyper_dev, step_dev, weight_decay_per_slot, ST(stream));
+}
+int s4g_device_hyper_set(float* hyper_dev, float lr, float beta1, float beta2, float eps, float weight_decay, float grad_scale, void* stream) {
+  if (!hyper_dev) { s4g_set_error("device_hyper_set: null argument"); return S4G_ERR_STATE; }
+  return k_device_hyper_set(hyper_dev, lr, beta1, beta2, eps, weight_decay, grad_scale, ST(stream));
+}
+int s4g_device_counter_advance(int* step_dev, unsigned long long* seed_dev, void* stream) {
+  return k_device_counter_advance(step_dev, seed_dev, ST(stream));
+}
+
 }  // extern "C"

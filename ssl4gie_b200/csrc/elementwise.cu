@@ -1188,9 +1188,11 @@ __global__ void __launch_bounds__(256, 3) seghead_fwd_kernel(const T* __restrict
                                                              const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                              const float* __restrict__ beta, const float* __restrict__ w,
                                                              const float* __restrict__ b, const uint8_t* __restrict__ mask,
-                                                             float p, uint64_t seed, float* __restrict__ small, long long M) {
+                                                             float p, uint64_t seed, float* __restrict__ small, long long M,
+                                                             const unsigned long long* __restrict__ seed_dev) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
+  if (seed_dev) seed = *seed_dev;   // device-resident dropout seed (CUDA-graph replays: a by-value seed would be baked in)
   const int lane = threadIdx.x & 31;
   float sc[8], sh[8], wv[8];
 #pragma unroll
@@ -1224,9 +1226,9 @@ __global__ void __launch_bounds__(256, 3) seghead_fwd_kernel(const T* __restrict
 template <typename T>
 int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
                   const float* w, const float* b, const uint8_t* mask, float p, uint64_t seed, float* small,
-                  long long M, int C, cudaStream_t st) {
+                  long long M, int C, cudaStream_t st, const unsigned long long* seed_dev) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
-  S4G_CUDA(launch_dep(seghead_fwd_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 16)), dim3(256), 0, st, x, mean, rstd, gamma, beta, w, b, mask, p, seed, small, M));
+  S4G_CUDA(launch_dep(seghead_fwd_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 16)), dim3(256), 0, st, x, mean, rstd, gamma, beta, w, b, mask, p, seed, small, M, seed_dev));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1237,9 +1239,11 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_reduce_kernel(const float*
                                                                     const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                     const float* __restrict__ w, const uint8_t* __restrict__ mask,
-                                                                    float p, uint64_t seed, double* __restrict__ sums, long long M) {
+                                                                    float p, uint64_t seed, double* __restrict__ sums, long long M,
+                                                                    const unsigned long long* __restrict__ seed_dev) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
+  if (seed_dev) seed = *seed_dev;
   __shared__ float sm[3][8][256];
   __shared__ float sdb[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1299,12 +1303,13 @@ __global__ void __launch_bounds__(256, 2) seghead_bwd_reduce_kernel(const float*
 template <typename T>
 int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                          const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
-                         float* dw, float* db, long long M, int C, cudaStream_t st, const Reducer* red) {
+                         float* dw, float* db, long long M, int C, cudaStream_t st, const Reducer* red,
+                         const unsigned long long* seed_dev) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
   const int nb = (int)min((long long)cdiv(M, 8), (long long)148 * 4);
   double* part = reinterpret_cast<double*>(reduce_scratch(red, seghead_scratch_bytes()));
   if (!part) return S4G_ERR_WORKSPACE;
-  S4G_CUDA(launch_dep(seghead_bwd_reduce_kernel<T>, dim3(nb), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, part, M));
+  S4G_CUDA(launch_dep(seghead_bwd_reduce_kernel<T>, dim3(nb), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, part, M, seed_dev));
   S4G_KERNEL_CHECK();
   // one grouped combine for the three outputs (the BN sums are consumed by the very next kernel: never left queued)
   FinalizeJobs q; q.n = 0; q.total_blocks = 0; q.launches = 0;
@@ -1321,9 +1326,10 @@ __global__ void __launch_bounds__(256, 3) seghead_bwd_apply_kernel(const float* 
                                                                    const float* __restrict__ w, const uint8_t* __restrict__ mask,
                                                                    float p, uint64_t seed, const double* __restrict__ sums,
                                                                    double count, T* __restrict__ dx, float* dgamma, float* dbeta,
-                                                                   long long M) {
+                                                                   long long M, const unsigned long long* __restrict__ seed_dev) {
   pdl_wait();  // launched programmatically dependent: nothing in global memory is touched before this
   pdl_trigger();
+  if (seed_dev) seed = *seed_dev;
   const int lane = threadIdx.x & 31;
   if (blockIdx.x == 0) {  // global sums / world under SyncBatchNorm, see bn_bwd_apply_kernel
     const double gs = (double)M / count;
@@ -1375,9 +1381,9 @@ template <typename T>
 int k_seghead_bwd_apply(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                         const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed,
                         const double* sums, double count, T* dx, float* dgamma, float* dbeta, long long M, int C,
-                        cudaStream_t st) {
+                        cudaStream_t st, const unsigned long long* seed_dev) {
   if (C != 256) { s4g_set_error("seghead: C must be 256"); return S4G_ERR_SHAPE; }
-  S4G_CUDA(launch_dep(seghead_bwd_apply_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 16)), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, count, dx, dgamma, dbeta, M));
+  S4G_CUDA(launch_dep(seghead_bwd_apply_kernel<T>, dim3((unsigned)min((long long)cdiv(M, 8), (long long)148 * 16)), dim3(256), 0, st, dsmall, x, mean, rstd, gamma, beta, w, mask, p, seed, sums, count, dx, dgamma, dbeta, M, seed_dev));
   S4G_KERNEL_CHECK();
   return 0;
 }
@@ -1669,9 +1675,9 @@ int k_unpack_convT_grad(const float* dwp, float* dw, int Ci, int Co, int k, cuda
   template int k_bn_apply<T>(const T*, const float*, const float*, const float*, const float*, const T*, T*, int, long long, int, cudaStream_t); \
   template int k_bn_bwd_reduce<T>(const T*, const T*, const float*, const float*, const float*, const float*, double*, int, long long, int, cudaStream_t, const Reducer*); \
   template int k_bn_bwd_apply<T>(const T*, const T*, const float*, const float*, const float*, const float*, const double*, double, T*, float*, float*, int, long long, int, cudaStream_t); \
-  template int k_seghead_fwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, float*, long long, int, cudaStream_t); \
-  template int k_seghead_bwd_reduce<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, double*, float*, float*, long long, int, cudaStream_t, const Reducer*); \
-  template int k_seghead_bwd_apply<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, const double*, double, T*, float*, float*, long long, int, cudaStream_t); \
+  template int k_seghead_fwd<T>(const T*, const float*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, float*, long long, int, cudaStream_t, const unsigned long long*); \
+  template int k_seghead_bwd_reduce<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, double*, float*, float*, long long, int, cudaStream_t, const Reducer*, const unsigned long long*); \
+  template int k_seghead_bwd_apply<T>(const float*, const T*, const float*, const float*, const float*, const float*, const float*, const uint8_t*, float, uint64_t, const double*, double, T*, float*, float*, long long, int, cudaStream_t, const unsigned long long*); \
   template int k_depthhead_fwd<T>(const T*, const float*, const float*, float*, long long, int, cudaStream_t);         \
   template int k_depthhead_bwd<T>(const float*, const float*, const T*, const float*, T*, float*, float*, long long, int, cudaStream_t, const Reducer*); \
   template int k_pack_linear<T>(const float*, T*, T*, int, int, cudaStream_t);                                         \

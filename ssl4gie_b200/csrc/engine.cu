@@ -77,6 +77,7 @@ struct S4GModel {
   const float* dout = nullptr;
   int training = 1;
   uint64_t seed = 0;
+  const unsigned long long* seed_dev = nullptr;   // device-resident dropout seed (s4g_model_set_seed_device): overrides `seed`
   const uint8_t* dropout_mask = nullptr;
   // MAE pretraining step (S4G_DENSE_MAE): masking noise in, mask / ids_restore out (s4g_model_set_mae_io)
   const float* mae_noise = nullptr;
@@ -669,7 +670,7 @@ struct Builder {
         mm->launches += 2;
         float* small = mm->template at<float>(self->head_small);
         S4G_TRY(k_seghead_fwd<T>(self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p, b4->p,
-                                 mm->training ? mm->dropout_mask : nullptr, mm->training ? mm->d.dropout_p : 0.f, mm->seed, small, M1, 256, st));
+                                 mm->training ? mm->dropout_mask : nullptr, mm->training ? mm->d.dropout_p : 0.f, mm->seed, small, M1, 256, st, mm->seed_dev));
         return k_bilinear2x_f32_fwd(small, mm->out, self->B, 112, 112, st);
       });
       bwd->push_back([=](cudaStream_t st) {
@@ -679,11 +680,11 @@ struct Builder {
         S4G_TRY(k_bilinear2x_f32_bwd(mm->dout, ds, self->B, 112, 112, st));
         const Reducer rs = self->red(self->shared_red, false);
         S4G_TRY(k_seghead_bwd_reduce<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
-                                        mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, w4->g, b4->g, M1, 256, st, &rs));
+                                        mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, w4->g, b4->g, M1, 256, st, &rs, mm->seed_dev));
         if (mm->d.world_size > 1) S4G_TRY(mm->exchange(sums, 512, st));
         return k_seghead_bwd_apply<T>(ds, self->V(c), mm->template at<float>(n.mean), mm->template at<float>(n.rstd), n.w->p, n.b->p, w4->p,
                                       mm->dropout_mask, mm->d.dropout_p, mm->seed, sums, (double)M1 * mm->d.world_size, self->G(c),
-                                      n.w->g, n.b->g, M1, 256, st);
+                                      n.w->g, n.b->g, M1, 256, st, mm->seed_dev);
       });
     } else {
       const int c = act(B, 112, 112, 128);
@@ -1275,6 +1276,11 @@ int s4g_model_forward(S4GModel* m, const float* images, float* out, int training
     if (m->mae_mask_out) S4G_CUDA(cudaMemcpyAsync(m->mae_mask_out, m->at<float>(m->mae_mask_off), sizeof(float) * n, cudaMemcpyDeviceToDevice, st));
     if (m->mae_ids_restore_out) S4G_CUDA(cudaMemcpyAsync(m->mae_ids_restore_out, m->at<int>(m->mae_ids_restore_off), sizeof(int) * n, cudaMemcpyDeviceToDevice, st));
   }
+  return 0;
+}
+int s4g_model_set_seed_device(S4GModel* m, const unsigned long long* seed_dev) {
+  if (!m) { s4g_set_error("model_set_seed_device: null model"); return S4G_ERR_STATE; }
+  m->seed_dev = seed_dev;
   return 0;
 }
 int s4g_model_set_mae_io(S4GModel* m, const float* noise, float* mask_out, int* ids_restore_out) {

@@ -149,17 +149,18 @@ int k_bn_bwd_apply(const T* dy, const T* x, const float* mean, const float* rstd
 template <typename T>
 int k_seghead_fwd(const T* x, const float* mean, const float* rstd, const float* gamma, const float* beta,
                   const float* w, const float* b, const uint8_t* mask, float p, uint64_t seed, float* small,
-                  long long M, int C, cudaStream_t st);
+                  long long M, int C, cudaStream_t st, const unsigned long long* seed_dev = nullptr);   // seed_dev: device-resident seed, overrides `seed`
 // pass 1: reductions (BN sums + dw[C] + db) ; pass 2: dx
 template <typename T>
 int k_seghead_bwd_reduce(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                          const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed, double* sums,
-                         float* dw, float* db, long long M, int C, cudaStream_t st, const Reducer* red = nullptr);
+                         float* dw, float* db, long long M, int C, cudaStream_t st, const Reducer* red = nullptr,
+                         const unsigned long long* seed_dev = nullptr);
 template <typename T>
 int k_seghead_bwd_apply(const float* dsmall, const T* x, const float* mean, const float* rstd, const float* gamma,
                         const float* beta, const float* w, const uint8_t* mask, float p, uint64_t seed,
                         const double* sums, double count, T* dx, float* dgamma, float* dbeta, long long M, int C,
-                        cudaStream_t st);
+                        cudaStream_t st, const unsigned long long* seed_dev = nullptr);
 // depth head tail: (already ReLU'd) h[M,C] . w + b -> sigmoid => out [M] fp32 ; bwd gives dh and dw/db
 template <typename T>
 int k_depthhead_fwd(const T* h, const float* w, const float* b, float* out, long long M, int C, cudaStream_t st);
@@ -210,6 +211,9 @@ size_t ssi_scratch_floats(int B);
 // ---- optimizer: optim.cu
 int k_adamw(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2, float eps, float wd,
             int step, float grad_scale, cudaStream_t st, const float* wd_slot = nullptr);
+int k_adamw_dev(float* p, const float* g, float* m, float* v, long long n, const float* hyper, const int* step_dev, const float* wd_slot, cudaStream_t st);
+int k_device_hyper_set(float* hyper, float lr, float b1, float b2, float eps, float wd, float gs, cudaStream_t st);
+int k_device_counter_advance(int* step_dev, unsigned long long* seed_dev, cudaStream_t st);
 
 // peer.cu: SyncBN statistic exchange over NVLink peer memory
 size_t k_peer_mailbox_bytes();

@@ -60,6 +60,7 @@ class Engine:
         self._cb_keepalive = []
         self.world_size_override = None
         self.bucket_events = None
+        self.seed_dev = None   # device-resident dropout seed (enable_device_seed): CUDA-graph replays
 
     # ------------------------------------------------------------------------------------------ arenas
     def _needs_materialize(self, model):
@@ -118,6 +119,17 @@ class Engine:
         self.handles = {}
         if self.direct_grads:
             self.enable_direct_grads()
+
+    def enable_device_seed(self):
+        """Dropout seed of the seg head read from device memory (advanced by FusedAdamW's device-state step), so that a captured
+        graph of the step draws a new mask at every replay."""
+        if self.seed_dev is None:
+            self.materialize()
+            seed = (torch.initial_seed() * 1000003 + 12345) & 0x7FFFFFFFFFFFFFFF
+            self.seed_dev = torch.tensor([seed], dtype=torch.int64, device=self.flat_params.device)
+            for h in self.handles.values():
+                _C.check(_C.lib().s4g_model_set_seed_device(h.ptr, _C.ptr(self.seed_dev)))
+        return self
 
     def enable_direct_grads(self):
         """Fast path used by FusedAdamW / DataParallelStep: p.grad aliases the flat gradient arena."""
@@ -194,6 +206,8 @@ class _Handle:
         self.ws_off = (-base) % 256
         _C.check(lib.s4g_model_set_workspace(self.ptr, ctypes.c_void_p(base + self.ws_off), nbytes))
         self.buffers = [b for _, b in model.named_buffers()]
+        if engine.seed_dev is not None:
+            _C.check(lib.s4g_model_set_seed_device(self.ptr, _C.ptr(engine.seed_dev)))
         self.syncbn_via = None  # "peer" (NVLink mailboxes, csrc/peer.cu) | "nccl" (callback) when world_size > 1
         if world_size > 1:
             self._install_allreduce()

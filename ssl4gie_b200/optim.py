@@ -34,6 +34,10 @@ class FusedAdamW(torch.optim.Optimizer):
         self.exp_avg_sq = torch.zeros_like(self.exp_avg)
         self.step_count = 0
         self.grad_scale = grad_scale
+        # device-resident scalars (enable_device_state): what a CUDA graph of the step needs (graph.GraphedStep)
+        self._hyper_dev = None
+        self._step_dev = None
+        self._hyper_written = None
 
     def _build_wd_slots(self):
         """One weight decay per 64-float arena slot (every parameter starts on a slot boundary)."""
@@ -84,11 +88,44 @@ class FusedAdamW(torch.optim.Optimizer):
                                              g["lr"], g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"], self.step_count,
                                              self.grad_scale, _C.stream_ptr()))
 
+    # ---- device-resident lr / betas / step count (CUDA-graph capture of the step) ----
+    def enable_device_state(self):
+        """Keep lr, betas, eps, weight decay, grad_scale and the step count in device memory: step() then launches kernels whose
+        arguments never change, so the step can be captured once and replayed (ssl4gie_b200.graph.GraphedStep).  Per-group weight
+        decay still comes from the slot table.  Same arithmetic except that the bias corrections are evaluated on the device."""
+        if self._hyper_dev is None:
+            dev = self.engine.flat_params.device
+            self._hyper_dev = torch.zeros(8, dtype=torch.float32, device=dev)
+            self._step_dev = torch.full((1,), self.step_count, dtype=torch.int32, device=dev)
+        return self
+
+    def sync_device_hyper(self):
+        """Push lr / betas / eps / weight_decay / grad_scale to the device if they changed (a 1-thread kernel with by-value
+        arguments; call outside graph capture: GraphedStep does before every replay)."""
+        g = self.param_groups[0]
+        cur = (float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), float(g["weight_decay"]), float(self.grad_scale))
+        if cur != self._hyper_written:
+            _C.check(_C.lib().s4g_device_hyper_set(_C.ptr(self._hyper_dev), *cur, _C.stream_ptr()))
+            self._hyper_written = cur
+
+    def _step_device(self):
+        e = self.engine
+        if not torch.cuda.is_current_stream_capturing():
+            self.sync_device_hyper()
+        wd = _C.ptr(self.wd_slots) if self.wd_slots is not None else None
+        _C.check(_C.lib().s4g_adamw_step_device(_C.ptr(e.flat_params), _C.ptr(e.flat_grads), _C.ptr(self.exp_avg), _C.ptr(self.exp_avg_sq),
+                                                e.n_active, _C.ptr(self._hyper_dev), _C.ptr(self._step_dev), wd, _C.stream_ptr()))
+        seed = getattr(e, "seed_dev", None)
+        _C.check(_C.lib().s4g_device_counter_advance(_C.ptr(self._step_dev), _C.ptr(seed), _C.stream_ptr()))
+
     @torch.no_grad()
     def step(self, closure=None):
         if getattr(self, "_external", False):   # already applied bucket by bucket during the gradient exchange
             self._external = False
             return
+        if self._hyper_dev is not None:
+            self.step_count += 1
+            return self._step_device()
         g = self.param_groups[0]
         self.step_count += 1
         e = self.engine
