@@ -70,18 +70,21 @@ class _LaggedScalar:
 
 
 def train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer, epoch, loss_fn, log_path, scaler=None,
-                grad_sync=None, log_every=10):
+                grad_sync=None, log_every=10, graph_step=None):
     """One training epoch; returns the epoch-mean of the rank-averaged loss (reference train_segmentation.py:25-81).
 
     ``scaler`` is accepted for signature compatibility and ignored.  ``grad_sync`` is the
-    ``ssl4gie_b200.ddp.GradientAllReduce`` of the model when world_size > 1 (the reference wraps the model in DDP)."""
+    ``ssl4gie_b200.ddp.GradientAllReduce`` of the model when world_size > 1 (the reference wraps the model in DDP).
+    ``graph_step`` (one GPU, constant batch shape -- the reference's loaders drop the last batch): a
+    ``ssl4gie_b200.GraphedStep(model, loss_fn, optimizer)`` kept by the caller across epochs; every step is then one CUDA-graph
+    replay instead of ~600 kernel launches from Python."""
     with _bf16_by_default(model):
         return _train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer, epoch, loss_fn, log_path,
-                            grad_sync, log_every)
+                            grad_sync, log_every, graph_step)
 
 
 def _train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer, epoch, loss_fn, log_path, grad_sync,
-                 log_every):
+                 log_every, graph_step=None):
     t = time.time()
     model.train()
     if train_sampler is not None:
@@ -96,12 +99,15 @@ def _train_epoch(model, rank, world_size, train_loader, train_sampler, optimizer
     for batch_idx, (data, target) in enumerate(DevicePrefetcher(train_loader, device=torch.device("cuda", rank))):
         if losses is None:
             losses = torch.zeros(n_batches, dtype=torch.float32, device=data.device)
-        optimizer.zero_grad()
-        loss = loss_fn(model(data), target)
-        loss.backward()
-        if grad_sync is not None:
-            grad_sync.reduce()
-        optimizer.step()
+        if graph_step is not None:
+            loss = graph_step(data, target)
+        else:
+            optimizer.zero_grad()
+            loss = loss_fn(model(data), target)
+            loss.backward()
+            if grad_sync is not None:
+                grad_sync.reduce()
+            optimizer.step()
         losses[batch_idx] = loss.detach()
         seen += len(data) * world_size
         if rank == 0 and batch_idx + 1 < n_batches and (batch_idx + 1) % log_every == 0:

@@ -112,3 +112,20 @@ def test_graphed_mae_step():
     worst = max(abs(a - b) / abs(a) for a, b in zip(eager, graphed))
     print(f"[graph] MAE eager vs graphed: worst loss deviation {worst:.2e}")
     assert worst < 1e-5
+
+
+def test_train_epoch_with_a_graphed_step():
+    """train.train_epoch(..., graph_step=GraphedStep(...)) (reference loop train_segmentation.py:25-81): same epoch means as the
+    launch-by-launch loop over two epochs."""
+    from ssl4gie_b200 import FusedAdamW, GraphedStep, SoftDiceLoss, train
+    loader = [tuple(v.cpu() for v in _batch(2, k)) for k in range(4)]
+    loss_fn = SoftDiceLoss()
+    m_e = _seg_model(0.0)
+    o_e = FusedAdamW(m_e, lr=1e-4)
+    eager = [train.train_epoch(m_e, 0, 1, loader, None, o_e, ep, loss_fn, None) for ep in (1, 2)]
+    m_g = _seg_model(0.0)
+    o_g = FusedAdamW(m_g, lr=1e-4)
+    gs = GraphedStep(m_g, loss_fn, o_g)
+    graphed = [train.train_epoch(m_g, 0, 1, loader, None, o_g, ep, loss_fn, None, graph_step=gs) for ep in (1, 2)]
+    assert gs.graph is not None and o_g.step_count == 8
+    assert all(abs(a - b) < 1e-6 * abs(a) for a, b in zip(eager, graphed)), (eager, graphed)
