@@ -352,30 +352,15 @@ def run_ours(args):
             enq.append(launch_host[-1])
         torch.cuda.synchronize()
         host_enqueue_ms = 1e3 * sorted(enq)[len(enq) // 2]
-        # the same step captured in a CUDA graph (ssl4gie_b200.GraphedStep): GPU time per step and host time per replay
-        graph_extra = None
-        try:
-            from ssl4gie_b200 import GraphedStep
-            gs = GraphedStep(model, loss_fn, opt, eager_steps=1)
-            for _ in range(4):
-                gs(x_d, t_d)
-            torch.cuda.synchronize()
-            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            hosts = []
-            g0.record()
-            for _ in range(20):
-                th = time.perf_counter()
-                gs(x_d, t_d)
-                hosts.append(time.perf_counter() - th)
-            g1.record()
-            torch.cuda.synchronize()
-            graph_extra = {"ms_per_step": g0.elapsed_time(g1) / 20, "host_ms_per_replay": 1e3 * sorted(hosts)[10], "steps": 20,
-                           "note": "fwd + loss + bwd + AdamW replayed from one CUDA graph; lr / step count / dropout seed live in device memory"}
-        except Exception as e:  # noqa: BLE001
-            graph_extra = {"error": repr(e)[:200]}
         extra = side_measurements(task, B, roof)
         extra["host_enqueue_ms_per_step"] = host_enqueue_ms
-        extra["cuda_graph"] = graph_extra
+        # the same step captured in a CUDA graph (ssl4gie_b200.GraphedStep), in a process of its own (scripts/bench_graphed.py)
+        try:
+            r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "bench_graphed.py"), task, str(B)], capture_output=True,
+                               text=True, timeout=600, cwd=ROOT)
+            extra["cuda_graph"] = json.loads(r.stdout.strip().splitlines()[-1])
+        except Exception as e:  # noqa: BLE001
+            extra["cuda_graph"] = {"error": repr(e)[:200]}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sec, cores = cpu_step_time(task, 8, 2)

@@ -274,7 +274,10 @@ class _Handle:
 
     def backward(self, gout):
         ev = self.engine.bucket_events
-        if ev is not None:
+        if ev is not None and torch.cuda.is_current_stream_capturing():
+            # a captured single-GPU step (graph.GraphedStep) has no exchange to signal: record no bucket events into the graph
+            _C.check(_C.lib().s4g_model_set_bucket_events(self.ptr, None, 0))
+        elif ev is not None:
             arr = (ctypes.c_void_p * len(ev))(*[ctypes.c_void_p(e.cuda_event) for e in ev])
             _C.check(_C.lib().s4g_model_set_bucket_events(self.ptr, arr, len(ev)))
         _C.check(_C.lib().s4g_model_backward(self.ptr, _C.ptr(gout), _C.stream_ptr()))

@@ -129,3 +129,25 @@ def test_train_epoch_with_a_graphed_step():
     graphed = [train.train_epoch(m_g, 0, 1, loader, None, o_g, ep, loss_fn, None, graph_step=gs) for ep in (1, 2)]
     assert gs.graph is not None and o_g.step_count == 8
     assert all(abs(a - b) < 1e-6 * abs(a) for a, b in zip(eager, graphed)), (eager, graphed)
+
+
+def test_graphed_step_with_bucket_events_installed():
+    """bench.py builds a GradientAllReduce even on one GPU (its bucket events are then installed in the C schedule); capturing the
+    step must not record them into the graph."""
+    from ssl4gie_b200 import FusedAdamW, GraphedStep, SoftDiceLoss
+    from ssl4gie_b200.ddp import GradientAllReduce
+    m = _seg_model(0.1)
+    opt = FusedAdamW(m, lr=1e-4)
+    sync = GradientAllReduce(m)
+    sync.attach(opt)
+    sync.prepare(2)
+    x, t = _batch(2, 0)
+    loss_fn = SoftDiceLoss()
+    for _ in range(2):     # eager steps with the events in place, as the bench runs before it builds the graph
+        loss_fn(m(x), t).backward()
+        sync.reduce()
+        opt.step()
+    gs = GraphedStep(m, loss_fn, opt, eager_steps=1)
+    losses = [gs(x, t).item() for _ in range(4)]
+    assert gs.graph is not None and all(l == l for l in losses)
+    torch.rand(4, device="cuda")   # torch's generator is usable after the capture
