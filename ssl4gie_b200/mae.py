@@ -86,18 +86,21 @@ class MaskedAutoencoderViT(nn.Module):
                 nn.init.constant_(m.weight, 1.0)
 
     def patchify(self, imgs):
-        """models_mae.py:95-107 (host-side view; the loss kernel reads the image directly)."""
+        """[N, 3, H, W] -> [N, L, p*p*3], element order (row in patch, column in patch, channel) as models_mae.py:95-107.
+        Host-side convenience only: the loss kernel builds the target from the image itself."""
         p = self.patch_embed.patch_size[0]
-        h = w = imgs.shape[2] // p
-        x = imgs.reshape(imgs.shape[0], 3, h, p, w, p)
-        return torch.einsum("nchpwq->nhwpqc", x).reshape(imgs.shape[0], h * w, p ** 2 * 3)
+        n, c, hh, ww = imgs.shape
+        gh, gw = hh // p, ww // p
+        tiles = imgs.view(n, c, gh, p, gw, p).permute(0, 2, 4, 3, 5, 1)        # n, gh, gw, row, col, channel
+        return tiles.reshape(n, gh * gw, p * p * c)
 
     def unpatchify(self, x):
-        """models_mae.py:109-121."""
+        """Inverse of patchify (models_mae.py:109-121): [N, L, p*p*3] -> [N, 3, H, W]."""
         p = self.patch_embed.patch_size[0]
-        h = w = int(x.shape[1] ** .5)
-        x = x.reshape(x.shape[0], h, w, p, p, 3)
-        return torch.einsum("nhwpqc->nchpwq", x).reshape(x.shape[0], 3, h * p, h * p)
+        n, L, _ = x.shape
+        g = int(round(L ** 0.5))
+        tiles = x.view(n, g, g, p, p, 3).permute(0, 5, 1, 3, 2, 4)             # n, channel, gh, row, gw, col
+        return tiles.reshape(n, 3, g * p, g * p)
 
     def forward_loss(self, imgs, pred, mask):
         """models_mae.py:198-214."""
