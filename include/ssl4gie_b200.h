@@ -231,6 +231,10 @@ int s4g_aug_blur_normalize(const unsigned char* img, const float* sigma, float* 
                            const float* std3_host, int B, void* stream);
 /* ToTensor + Grayscale of the masks (dataloaders.py:72-74): [B,224,224,C] u8 -> [B,1,224,224] f32. */
 int s4g_aug_mask_to_tensor(const unsigned char* img, float* out, int B, int C, void* stream);
+/* Depth target (Depth_estimation/Data/dataset.py:47-53): packed 16-bit depth images (already padded to squares, make_square :9-16;
+ * desc as for s4g_aug_resize, byte offsets even) -> nearest resize to 224 x 224 as the pinned Pillow 9.1.0 does for "I;16"
+ * (source index floor((i + 0.5) * in / 224)) -> / 65535: out [B,1,224,224] f32. */
+int s4g_aug_depth_target(const void* src, const long long* desc_dev, float* out, int B, void* stream);
 /* TF.hflip, TF.vflip, TF.affine(interpolation=NEAREST, fill) applied jointly to x [B,3,224,224] and y [B,1,224,224] (y, yo
  * may be NULL) (dataset.py:46-63).  params (device) [B] of {int hflip, vflip, affine; float m[6]} with m = torchvision's
  * _get_inverse_affine_matrix((0, 0), angle, translate, scale, (shear, 0)). */

@@ -246,3 +246,39 @@ def geometric(x, hflip, vflip, matrix, fill):
     iy, ix = affine_source_index(matrix, x.shape[-1])
     out = x[:, np.clip(iy, 0, None), np.clip(ix, 0, None)]
     return np.where((iy < 0)[None], np.float32(fill), out).astype(np.float32)
+
+
+# ----------------------------------------------------------------------------------------------- depth dataset (C3VD-style pairs)
+def make_square(img):
+    """Depth_estimation/Data/dataset.py:9-16: paste the image centred on a zero square of side max(h, w)
+    (offsets int((size - w) / 2), int((size - h) / 2)).  img: [h, w, 3] uint8 or [h, w] uint16."""
+    h, w = img.shape[:2]
+    size = max(h, w)
+    out = np.zeros((size, size) + img.shape[2:], dtype=img.dtype)
+    oy, ox = int((size - h) / 2), int((size - w) / 2)
+    out[oy:oy + h, ox:ox + w] = img
+    return out
+
+
+def pil_resize_nearest(img, out=224):
+    """Image.resize((224, 224)) of an "I;16" image under the reference's pinned Pillow 9.1.0 (requirements.txt:3), whose default
+    filter for the special modes is NEAREST (Image.py: `resample = NEAREST if ";" in mode else BICUBIC`; newer Pillow versions
+    resample I;16 with BICUBIC): source index = floor((i + 0.5) * in / out) on both axes."""
+    iy = np.floor((np.arange(out) + 0.5) * img.shape[0] / out).astype(np.int64)
+    ix = np.floor((np.arange(out) + 0.5) * img.shape[1] / out).astype(np.int64)
+    return img[np.ix_(iy, ix)]
+
+
+def depth_target(depth_u16):
+    """dataset.py:47-53: make_square(I;16) -> resize 224 -> np.array(y) / 65535 (float64) -> ToTensor -> .float(): [1, 224, 224]."""
+    y = pil_resize_nearest(make_square(depth_u16)).astype(np.float64) / 65535
+    return y.astype(np.float32)[None]
+
+
+def depth_input(rgb, order=None, factors=None):
+    """dataset.py:46 + Data/dataloaders.py:55-63: make_square -> bicubic resize 224 -> (training: ColorJitter) -> ToTensor ->
+    Normalize.  No GaussianBlur in the depth transforms."""
+    x = pil_resize_bicubic(make_square(rgb))
+    if order is not None:
+        x = color_jitter(x, order, factors)
+    return to_tensor_normalize(x)

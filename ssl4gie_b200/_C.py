@@ -73,6 +73,7 @@ SIGNATURES = {
     "s4g_aug_color_jitter": (_i, [_vp, _vp, _i, _vp]),
     "s4g_aug_blur_normalize": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "s4g_aug_mask_to_tensor": (_i, [_vp, _vp, _i, _i, _vp]),
+    "s4g_aug_depth_target": (_i, [_vp, _vp, _vp, _i, _vp]),
     "s4g_aug_geometric": (_i, [_vp, _vp, _vp, _vp, _vp, _f, _f, _i, _vp]),
     "s4g_adamw_step_device": (_i, [_vp, _vp, _vp, _vp, _ll, _vp, _vp, _vp, _vp]),
     "s4g_device_hyper_set": (_i, [_vp, _f, _f, _f, _f, _f, _f, _vp]),

@@ -45,7 +45,15 @@ class GpuInputPipeline:
     train=False is the evaluation transform (resize + ToTensor + Normalize; masks are returned resized only if given)."""
 
     def __init__(self, train=True, hflip=True, vflip=True, affine=True, brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01,
-                 blur_sigma=(0.001, 2.0), device=None):
+                 blur_sigma=(0.001, 2.0), device=None, task="seg"):
+        """task="depth": the transforms of Depth_estimation/Data/dataset.py:43-70 + Data/dataloaders.py:55-74 instead -- sources
+        padded to squares (make_square), no GaussianBlur, no affine, and `masks` are 16-bit depth maps ([h, w] uint16) resized with
+        the nearest filter (Pillow 9.1.0's default for "I;16", the version the reference pins) and divided by 65535."""
+        if task not in ("seg", "depth"):
+            raise ValueError("task must be 'seg' or 'depth'")
+        self.task = task
+        if task == "depth":
+            affine, blur_sigma = False, None
         self.train, self.hflip, self.vflip, self.affine = train, hflip, vflip, affine
         self.ranges = ((1 - brightness, 1 + brightness), (1 - contrast, 1 + contrast), (1 - saturation, 1 + saturation), (-hue, hue))
         self.blur_sigma = blur_sigma
@@ -60,7 +68,7 @@ class GpuInputPipeline:
         p = SampleParams()
         p.order = torch.randperm(4).tolist()
         p.brightness, p.contrast, p.saturation, p.hue = (float(torch.empty(1).uniform_(lo, hi)) for lo, hi in self.ranges)
-        p.sigma = torch.empty(1).uniform_(self.blur_sigma[0], self.blur_sigma[1]).item()
+        p.sigma = torch.empty(1).uniform_(self.blur_sigma[0], self.blur_sigma[1]).item() if self.blur_sigma is not None else None
         p.hflip = bool(self.hflip and random.uniform(0.0, 1.0) > 0.5)
         p.vflip = bool(self.vflip and random.uniform(0.0, 1.0) > 0.5)
         p.affine = None
@@ -74,24 +82,40 @@ class GpuInputPipeline:
         return p
 
     # ------------------------------------------------------------------------------------------ device stages
-    def _resize(self, arrays, channels):
-        return self._resize_dev(*self._pack(arrays, channels))
+    def _resize(self, arrays, channels, square=False):
+        return self._resize_dev(*self._pack(arrays, channels, square=square))
 
-    def _pack(self, arrays, channels):
-        """Host side: one pinned buffer with every image's bytes + the descriptor table, copied asynchronously."""
+    def _depth_target(self, arrays):
+        src, _, desc_d, B, _ = self._pack(arrays, 1, dtype=np.uint16, square=True)
+        out = torch.empty((B, 1, 224, 224), dtype=torch.float32, device=self.device)
+        _C.check(_C.lib().s4g_aug_depth_target(_C.ptr(src), _C.ptr(desc_d), _C.ptr(out), B, _C.stream_ptr()))
+        return out
+
+    def _pack(self, arrays, channels, dtype=np.uint8, square=False):
+        """Host side: one pinned buffer with every image's bytes + the descriptor table, copied asynchronously.  square: every image
+        is pasted centred on a zero square of side max(h, w) while it is packed (Depth_estimation/Data/dataset.py:9-16)."""
         B = len(arrays)
+        item = np.dtype(dtype).itemsize
         desc = np.zeros((B, 5), dtype=np.int64)
         off = tmp = 0
         for i, a in enumerate(arrays):
-            if a.dtype != np.uint8 or a.ndim != (3 if channels == 3 else 2) or (channels == 3 and a.shape[2] != 3):
-                raise ValueError("images must be uint8 [h, w, 3]; masks uint8 [h, w] or [h, w, 3], alike within a batch")
-            desc[i] = (off, a.shape[0], a.shape[1], channels, tmp)
-            off += (a.size + 15) // 16 * 16
-            tmp += (a.shape[0] * 224 * channels + 15) // 16 * 16
+            if a.dtype != dtype or a.ndim != (3 if channels == 3 else 2) or (channels == 3 and a.shape[2] != 3):
+                raise ValueError("images must be uint8 [h, w, 3]; masks uint8 [h, w] or [h, w, 3] (depth maps uint16 [h, w]), alike within a batch")
+            h, w = (max(a.shape[:2]),) * 2 if square else a.shape[:2]
+            desc[i] = (off, h, w, channels, tmp)
+            off += (h * w * channels * item + 15) // 16 * 16
+            tmp += (h * 224 * channels + 15) // 16 * 16
         host = torch.empty(off, dtype=torch.uint8).pin_memory()
         hv = host.numpy()
         for i, a in enumerate(arrays):
-            hv[desc[i, 0]:desc[i, 0] + a.size] = np.ascontiguousarray(a).reshape(-1)
+            o, h, w = int(desc[i, 0]), int(desc[i, 1]), int(desc[i, 2])
+            view = hv[o:o + h * w * channels * item].view(dtype).reshape((h, w, channels) if channels == 3 else (h, w))
+            if square:
+                view[...] = 0
+                oy, ox = int((h - a.shape[0]) / 2), int((w - a.shape[1]) / 2)
+                view[oy:oy + a.shape[0], ox:ox + a.shape[1]] = a
+            else:
+                view[...] = a
         src = host.to(self.device, non_blocking=True)
         desc_t = torch.from_numpy(desc)
         return src, desc_t, desc_t.to(self.device), B, channels
@@ -152,9 +176,12 @@ class GpuInputPipeline:
         _C.init(self.device.index or 0)
         B = len(images)
         with torch.cuda.device(self.device):
-            x8 = self._resize(list(images), 3)
+            depth = self.task == "depth"
+            x8 = self._resize(list(images), 3, square=depth)
             y = None
-            if masks is not None:
+            if masks is not None and depth:
+                y = self._depth_target(list(masks))
+            elif masks is not None:
                 masks = list(masks)
                 y8 = self._resize(masks, 3 if masks[0].ndim == 3 else 1)
                 y = self._mask_to_tensor(y8)
@@ -168,7 +195,7 @@ class GpuInputPipeline:
             self._jitter(x8, params)
             if stages is not None:
                 stages["jittered"] = x8.clone()
-            x = self._blur_normalize(x8, [p.sigma for p in params])
+            x = self._blur_normalize(x8, [p.sigma for p in params] if self.blur_sigma is not None else None)
             if stages is not None:
                 stages["blurred"] = x
             return self._geometric(x, y, params)

@@ -220,6 +220,10 @@ int s4g_aug_mask_to_tensor(const unsigned char* img, float* out, int B, int C, v
   if (!img || !out || B < 1) { s4g_set_error("aug_mask_to_tensor: bad argument"); return S4G_ERR_STATE; }
   return k_aug_mask_to_tensor(img, out, B, C, ST(stream));
 }
+int s4g_aug_depth_target(const void* src, const long long* desc_dev, float* out, int B, void* stream) {
+  if (!src || !desc_dev || !out || B < 1) { s4g_set_error("aug_depth_target: bad argument"); return S4G_ERR_STATE; }
+  return k_aug_depth_target(src, desc_dev, out, B, ST(stream));
+}
 int s4g_aug_geometric(const float* x, const float* y, float* xo, float* yo, const void* params, float fill_x, float fill_y,
                       int B, void* stream) {
   if (!x || !xo || !params || (y && !yo) || B < 1) { s4g_set_error("aug_geometric: bad argument"); return S4G_ERR_STATE; }

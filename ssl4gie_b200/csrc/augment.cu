@@ -305,6 +305,22 @@ __global__ void geometric_kernel(const float* __restrict__ x, const float* __res
   }
 }
 
+// ------------------------------------------------------------------------------------------------ depth target (I;16 -> float)
+// Depth_estimation/Data/dataset.py:47-53 on the (already square-padded) 16-bit depth image: nearest resize as Pillow 9.1.0 does
+// for "I;16" (source index floor((i + 0.5) * in / 224)), then / 65535 in double, stored as float: out [B, 1, 224, 224]
+__global__ void depth_target_kernel(const uint16_t* __restrict__ src, const long long* __restrict__ desc, float* __restrict__ out, int B) {
+  const long long n = (long long)B * OUT * OUT;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(t % OUT), y = (int)((t / OUT) % OUT), b = (int)(t / (OUT * OUT));
+    const long long off = desc[b * 5];
+    const int h = (int)desc[b * 5 + 1], w = (int)desc[b * 5 + 2];
+    const int sy = min((int)floor(__ddiv_rn(__dmul_rn((double)y + 0.5, (double)h), (double)OUT)), h - 1);
+    const int sx = min((int)floor(__ddiv_rn(__dmul_rn((double)x + 0.5, (double)w), (double)OUT)), w - 1);
+    const uint16_t v = *reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(src) + off + ((size_t)sy * w + sx) * 2);
+    out[t] = (float)__ddiv_rn((double)v, 65535.0);
+  }
+}
+
 }  // namespace
 
 // ================================================================================================ host entry points
@@ -370,6 +386,12 @@ int k_aug_geometric(const float* x, const float* y, float* xo, float* yo, const 
   const long long n = (long long)B * OUT * OUT;
   geometric_kernel<<<(unsigned)std::min<long long>(cdiv(n, 256), 148 * 8), 256, 0, st>>>(x, y, xo, yo, reinterpret_cast<const GeoParams*>(params),
                                                                                           fill_x, fill_y, B);
+  S4G_KERNEL_CHECK();
+  return 0;
+}
+int k_aug_depth_target(const void* src, const long long* desc_dev, float* out, int B, cudaStream_t st) {
+  const long long n = (long long)B * OUT * OUT;
+  depth_target_kernel<<<(unsigned)std::min<long long>(cdiv(n, 256), 148 * 8), 256, 0, st>>>(reinterpret_cast<const uint16_t*>(src), desc_dev, out, B);
   S4G_KERNEL_CHECK();
   return 0;
 }

@@ -79,6 +79,7 @@ int k_aug_resize(const uint8_t* src, const long long* desc_dev, const long long*
 int k_aug_color_jitter(uint8_t* img, const void* params, int B, cudaStream_t st);
 int k_aug_blur_normalize(const uint8_t* img, const float* sigma, float* out, const float* mean3, const float* std3, int B, cudaStream_t st);
 int k_aug_mask_to_tensor(const uint8_t* img, float* out, int B, int C, cudaStream_t st);
+int k_aug_depth_target(const void* src, const long long* desc_dev, float* out, int B, cudaStream_t st);
 int k_aug_geometric(const float* x, const float* y, float* xo, float* yo, const void* params, float fill_x, float fill_y, int B, cudaStream_t st);
 // MAE pretraining step (mae.cu; Models/mae/models_mae.py:123-214)
 int k_mae_masking(const float* noise, int* ids_restore, int* ids_keep, float* mask, int B, int L, int keep, cudaStream_t st);

@@ -104,3 +104,24 @@ def test_flips_and_affine_nearest():
         tot += 224 * 224
     assert bad <= 1e-5 * tot + 2, (bad, tot)
     assert np.array_equal(TF.hflip(x).numpy(), A.geometric(x.numpy(), True, False, None, 0.0))
+
+
+def test_depth_dataset_helpers():
+    """make_square and the I;16 resize of Depth_estimation/Data/dataset.py:9-16,46-50.  The reference pins Pillow 9.1.0, whose
+    default filter for "I;16" is NEAREST; the installed Pillow defaults to BICUBIC for that mode, so NEAREST is requested here."""
+    rng = np.random.default_rng(11)
+    for h, w in ((1080, 1350), (480, 640), (224, 224), (100, 150), (720, 540)):
+        d = rng.integers(0, 65536, (h, w), dtype=np.uint16)
+        im = Image.fromarray(d)
+        size = max(im.size)
+        sq = Image.new("I;16", (size, size), 0)
+        sq.paste(im, (int((size - im.size[0]) / 2), int((size - im.size[1]) / 2)))
+        assert np.array_equal(np.array(sq), A.make_square(d))
+        ref = np.array(sq.resize((224, 224), Image.NEAREST))
+        assert np.array_equal(ref, A.pil_resize_nearest(A.make_square(d)))
+        assert np.array_equal(torch.from_numpy(ref / 65535).float().numpy()[None], A.depth_target(d))
+        rgb = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        sq3 = Image.new("RGB", (size, size), (0, 0, 0))
+        sq3.paste(Image.fromarray(rgb), (int((size - w) / 2), int((size - h) / 2)))
+        want = T.Normalize([0.485, 0.456, 0.406], [0.229, 0.224, 0.225])(T.ToTensor()(sq3.resize((224, 224)))).numpy()
+        assert np.array_equal(want, A.depth_input(rgb))

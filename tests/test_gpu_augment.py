@@ -83,3 +83,28 @@ def test_rejects_bad_input():
         pipe([np.zeros((10, 10, 4), dtype=np.uint8)])
     with pytest.raises(RuntimeError, match="too long"):
         pipe([np.zeros((8, 6000, 3), dtype=np.uint8)])
+
+
+def test_depth_pipeline_matches_oracle():
+    """GpuInputPipeline(task="depth") (Depth_estimation/Data/dataset.py:43-70, Data/dataloaders.py:55-74): square padding + bicubic
+    resize + ColorJitter + Normalize of the image and nearest resize / 65535 of the 16-bit depth map are all exact; flips exact."""
+    from ssl4gie_b200 import GpuInputPipeline
+    rng = np.random.default_rng(21)
+    sizes = [(1080, 1350), (480, 640), (224, 224), (100, 150), (720, 540), (531, 531)]
+    imgs = [_photo(30 + i, h, w) for i, (h, w) in enumerate(sizes)]
+    depths = [rng.integers(0, 65536, (h, w), dtype=np.uint16) for h, w in sizes]
+    pipe = GpuInputPipeline(train=True, task="depth")
+    torch.manual_seed(5)
+    random.seed(5)
+    params = [pipe.draw() for _ in imgs]
+    assert all(p.sigma is None and p.affine is None for p in params)
+    params[0].hflip, params[0].vflip, params[1].hflip, params[1].vflip = True, True, False, True
+    x, y = pipe(imgs, depths, params=params)
+    for i, (img, d, p) in enumerate(zip(imgs, depths, params)):
+        want_x = A.geometric(A.depth_input(img, p.order, (p.brightness, p.contrast, p.saturation, p.hue)), p.hflip, p.vflip, None, -1.0)
+        want_y = A.geometric(A.depth_target(d), p.hflip, p.vflip, None, 0.0)
+        assert np.array_equal(x[i].cpu().numpy(), want_x), ("image", sizes[i])
+        assert np.array_equal(y[i].cpu().numpy(), want_y), ("depth", sizes[i])
+    xe, ye = GpuInputPipeline(train=False, task="depth")(imgs, depths)
+    for i, (img, d) in enumerate(zip(imgs, depths)):
+        assert np.array_equal(xe[i].cpu().numpy(), A.depth_input(img)) and np.array_equal(ye[i].cpu().numpy(), A.depth_target(d))

@@ -277,3 +277,24 @@ def test_input_pipeline_draws_like_the_reference():
                    random.uniform(0.5, 1.5), random.uniform(-22.5, 22.5))
             assert q.affine == ref
             assert inverse_affine_matrix(*ref) == _get_inverse_affine_matrix([0.0, 0.0], ref[0], list(ref[1]), ref[2], [ref[3], 0.0])
+
+
+def test_depth_input_pipeline_draws():
+    """task="depth" (Depth_estimation/Data/dataloaders.py:55-63, dataset.py:55-63): ColorJitter.get_params, then the two flips;
+    no blur, no affine draw."""
+    import random
+
+    T = pytest.importorskip("torchvision.transforms")
+    from ssl4gie_b200 import GpuInputPipeline
+    pipe = GpuInputPipeline(train=True, task="depth")
+    jit = T.ColorJitter(brightness=0.4, contrast=0.5, saturation=0.25, hue=0.01)
+    torch.manual_seed(3)
+    random.seed(3)
+    ps = [pipe.draw() for _ in range(3)]
+    torch.manual_seed(3)
+    random.seed(3)
+    for q in ps:
+        order, b, c, s_, h = T.ColorJitter.get_params(jit.brightness, jit.contrast, jit.saturation, jit.hue)
+        assert (q.order, q.brightness, q.contrast, q.saturation, q.hue) == (order.tolist(), b, c, s_, h)
+        assert q.hflip == (random.uniform(0.0, 1.0) > 0.5) and q.vflip == (random.uniform(0.0, 1.0) > 0.5)
+        assert q.sigma is None and q.affine is None
