@@ -1,7 +1,7 @@
 """Developer diagnostic: per-step deviation of the 200-step loss curve (bf16 product vs fp32 oracle).
-Usage: python scripts/dev_curve.py [seg|depth|cls ...]"""
+Usage: python tests/tools/dev_curve.py [seg|depth|cls ...]"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from tests import test_gpu_train as T
 from oracle import ref_port

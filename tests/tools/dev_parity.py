@@ -1,6 +1,6 @@
 """Developer diagnostic: per-tensor error of our step vs an fp64 oracle run, next to the oracle's own fp32 / bf16-autocast error."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 from oracle import ref_port
 from tests.test_gpu_model import _inputs, _build, _loss, _rel, _l2

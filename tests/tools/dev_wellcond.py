@@ -1,11 +1,11 @@
 """Developer diagnostic: per-tensor bf16 gradient error on the warmed-up states of tests/_states.py, next to the
-reference's own bf16-autocast error.  Usage: python scripts/dev_wellcond.py [seg|depth] [B] [warm steps ...]"""
+reference's own bf16-autocast error.  Usage: python tests/tools/dev_wellcond.py [seg|depth] [B] [warm steps ...]"""
 import os
 import sys
 
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from oracle import ref_port  # noqa: E402
 from ssl4gie_b200 import ScaleAndShiftInvariantLoss, SoftDiceLoss, utils  # noqa: E402
 from tests import _states  # noqa: E402
