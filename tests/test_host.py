@@ -298,3 +298,13 @@ def test_depth_input_pipeline_draws():
         assert (q.order, q.brightness, q.contrast, q.saturation, q.hue) == (order.tolist(), b, c, s_, h)
         assert q.hflip == (random.uniform(0.0, 1.0) > 0.5) and q.vflip == (random.uniform(0.0, 1.0) > 0.5)
         assert q.sigma is None and q.affine is None
+
+
+def test_checkpoint_scaler_state_loads_into_an_enabled_gradscaler():
+    """save_checkpoint(scaler=None) stores the state of a fresh, enabled GradScaler: the reference's build() loads
+    "scaler_state_dict" unconditionally (train_segmentation.py:205-207) and torch refuses an empty dict there."""
+    from ssl4gie_b200 import train
+    sc = torch.amp.GradScaler("cpu")
+    assert sc.is_enabled() and sc.state_dict() == train._default_scaler_state()
+    sc.load_state_dict(train._default_scaler_state())
+    assert sc.get_scale() == 65536.0
